@@ -1,0 +1,393 @@
+// GPIS fit: covariance assembly (gpis.py:33-40) and the in-house blocked FP64 factorisation that replaces the
+// reference's per-call LU (gpis.py:53) / explicit inverse (gpis.py:77):
+//   E11 = L L^T (right-looking, 64-wide panels, DMMA SYRK trailing updates)
+//   U = L^-1 (block-recursive doubling, DMMA GEMMs),  P = U^T U = E11^-1,  alpha = U^T (U y1).
+#include <stdarg.h>
+#include "cdx_internal.cuh"
+
+static thread_local char g_err[512] = "";
+void cdx_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* cdx_last_error(void) { return g_err; }
+extern "C" int cdx_version(void) { return 100; }
+
+namespace {
+
+__global__ void pairmax_kernel(const double* __restrict__ X, int N, unsigned long long* out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double best = 0.0;
+  if (i < N) {
+    double x = X[3 * i], y = X[3 * i + 1], z = X[3 * i + 2];
+    for (int j = 0; j < N; j++) {
+      double dx = x - X[3 * j], dy = y - X[3 * j + 1], dz = z - X[3 * j + 2];
+      best = fmax(best, fma(dx, dx, fma(dy, dy, dz * dz)));
+    }
+  }
+  for (int o = 16; o; o >>= 1) best = fmax(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(best));  // >= 0: ordered as u64
+}
+
+template <int KERNEL>
+__global__ void assemble_kernel(const double* __restrict__ X, const double* __restrict__ noise, double noise_scalar,
+                                int N, int Np, cdx_kparams kp, double* __restrict__ E) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= Np) return;
+  double v;
+  if (i < N && j < N) {
+    double dx = X[3 * i] - X[3 * j], dy = X[3 * i + 1] - X[3 * j + 1], dz = X[3 * i + 2] - X[3 * j + 2];
+    double k, c;
+    cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, c);
+    v = k;
+    if (i == j) {
+      double n = noise ? noise[i] : noise_scalar;
+      v += n * n;
+    }
+  } else {
+    v = (i == j) ? 1.0 : 0.0;
+  }
+  E[(int64_t)i * Np + j] = v;
+}
+
+__global__ void pad_copy_kernel(const double* __restrict__ src, int N, int Np, double* __restrict__ dst) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= Np) return;
+  dst[(int64_t)i * Np + j] = (i < N && j < N) ? src[(int64_t)i * N + j] : ((i == j) ? 1.0 : 0.0);
+}
+
+__global__ void unpad_copy_kernel(const double* __restrict__ src, int N, int Np, double* __restrict__ dst) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j < N) dst[(int64_t)i * N + j] = src[(int64_t)i * Np + j];
+}
+
+// Cholesky of one 64x64 diagonal block in shared memory + its triangular inverse.
+__global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A, int64_t ld, double* __restrict__ Dinv,
+                                                         double* __restrict__ Udiag, int* flag, int col0) {
+  extern __shared__ double potrf_smem[];
+  double (*a)[65] = reinterpret_cast<double (*)[65]>(potrf_smem);
+  double (*x)[65] = a + 64;
+  const int t = threadIdx.x;
+  for (int e = t; e < 4096; e += 256) a[e >> 6][e & 63] = A[(int64_t)(e >> 6) * ld + (e & 63)];
+  __syncthreads();
+  for (int j = 0; j < 64; j++) {
+    if (t == 0) {
+      double d = a[j][j];
+      if (!(d > 0.0)) atomicCAS(flag, 0, col0 + j + 1);
+      a[j][j] = sqrt(d);
+    }
+    __syncthreads();
+    if (t > j && t < 64) a[t][j] /= a[j][j];
+    __syncthreads();
+    for (int e = t; e < 4096; e += 256) {
+      int r = e >> 6, c = e & 63;
+      if (c > j && r >= c) a[r][c] = fma(-a[r][j], a[c][j], a[r][c]);
+    }
+    __syncthreads();
+  }
+  for (int e = t; e < 4096; e += 256) {
+    int r = e >> 6, c = e & 63;
+    if (c > r) a[r][c] = 0.0;
+    x[r][c] = 0.0;
+  }
+  __syncthreads();
+  if (t < 64) {  // column t of the inverse by forward substitution
+    const int c = t;
+    x[c][c] = 1.0 / a[c][c];
+    for (int i = c + 1; i < 64; i++) {
+      double s = 0.0;
+      for (int j = c; j < i; j++) s = fma(a[i][j], x[j][c], s);
+      x[i][c] = -s / a[i][i];
+    }
+  }
+  __syncthreads();
+  for (int e = t; e < 4096; e += 256) {
+    int r = e >> 6, c = e & 63;
+    A[(int64_t)r * ld + c] = a[r][c];
+    Dinv[e] = x[r][c];
+    Udiag[(int64_t)r * ld + c] = x[r][c];
+  }
+}
+
+__global__ void zero_upper_kernel(double* __restrict__ A, int Np) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j < Np && j > i) A[(int64_t)i * Np + j] = 0.0;
+}
+__global__ void mirror_lower_kernel(double* __restrict__ A, int Np) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j < Np && j > i) A[(int64_t)i * Np + j] = A[(int64_t)j * Np + i];
+}
+__global__ void fill_kernel(double* __restrict__ A, int64_t n, double v) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) A[i] = v;
+}
+
+// out[i] = sum_{j<=i} U[i][j] v[j]   (one warp per row)
+__global__ void trmv_lower_kernel(const double* __restrict__ U, int Np, const double* __restrict__ v,
+                                  double* __restrict__ out) {
+  int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= Np) return;
+  double s = 0.0;
+  for (int j = lane; j <= row; j += 32) s = fma(U[(int64_t)row * Np + j], v[j], s);
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) out[row] = s;
+}
+// out[j] = sum_{i>=j} U[i][j] v[i]   (one thread per column, coalesced over columns)
+__global__ void trmv_lower_t_kernel(const double* __restrict__ U, int Np, const double* __restrict__ v,
+                                    double* __restrict__ out) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= Np) return;
+  double s = 0.0;
+  for (int i = j; i < Np; i++) s = fma(U[(int64_t)i * Np + j], v[i], s);
+  out[j] = s;
+}
+__global__ void pack_xa_kernel(const double* __restrict__ X, const double* __restrict__ alpha, int N, int Np,
+                               double* __restrict__ Xa) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Np) return;
+  bool ok = i < N;
+  Xa[4 * i + 0] = ok ? X[3 * i] : 0.0;
+  Xa[4 * i + 1] = ok ? X[3 * i + 1] : 0.0;
+  Xa[4 * i + 2] = ok ? X[3 * i + 2] : 0.0;
+  Xa[4 * i + 3] = ok ? alpha[i] : 0.0;
+}
+__global__ void sub_bias_kernel(const double* __restrict__ y, int N, int Np, double bias, double* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < Np) out[i] = i < N ? y[i] - bias : 0.0;
+}
+__global__ void extract_alpha_kernel(const double* __restrict__ Xa, int N, double* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) out[i] = Xa[4 * i + 3];
+}
+__global__ void extract_x_kernel(const double* __restrict__ Xa, int N, double* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) { out[3 * i] = Xa[4 * i]; out[3 * i + 1] = Xa[4 * i + 1]; out[3 * i + 2] = Xa[4 * i + 2]; }
+}
+
+int gpis_reserve(cdx_ctx* ctx, int64_t N) {
+  cdx_gpis_state& g = ctx->g;
+  int64_t Np = (N + CDX_NPAD - 1) / CDX_NPAD * CDX_NPAD;
+  if (Np > g.cap) {
+    cudaFree(g.Xa); cudaFree(g.y1); cudaFree(g.E11); cudaFree(g.L); cudaFree(g.U); cudaFree(g.P);
+    cudaFree(g.Dinv); cudaFree(g.tmp);
+    g.cap = 0;
+    size_t mat = sizeof(double) * (size_t)Np * (size_t)Np;
+    if (cudaMalloc(&g.Xa, sizeof(double) * 4 * Np) != cudaSuccess || cudaMalloc(&g.y1, sizeof(double) * Np) != cudaSuccess ||
+        cudaMalloc(&g.E11, mat) != cudaSuccess || cudaMalloc(&g.L, mat) != cudaSuccess ||
+        cudaMalloc(&g.U, mat) != cudaSuccess || cudaMalloc(&g.P, mat) != cudaSuccess ||
+        cudaMalloc(&g.Dinv, sizeof(double) * 64 * Np) != cudaSuccess || cudaMalloc(&g.tmp, sizeof(double) * 2 * Np) != cudaSuccess) {
+      cudaGetLastError();
+      cdx_set_error("out of device memory for GPIS state N=%lld", (long long)N);
+      return CDX_ERR_ALLOC;
+    }
+    g.cap = Np;
+  }
+  if (!g.dR2) {
+    CDX_CUDA(cudaMalloc(&g.dR2, sizeof(double)));
+    CDX_CUDA(cudaMalloc(&g.flag, sizeof(int)));
+  }
+  g.N = N;
+  g.Np = Np;
+  g.ready = false;
+  return CDX_OK;
+}
+
+// factorise g.E11 (padded) -> L, U, P, alpha, Xa.  X1 is [N,3] device.
+int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
+  cdx_gpis_state& g = ctx->g;
+  const int Np = (int)g.Np, N = (int)g.N;
+  const int64_t ld = Np;
+  const size_t mat = sizeof(double) * (size_t)Np * (size_t)Np;
+  CDX_CUDA(cudaMemcpyAsync(g.L, g.E11, mat, cudaMemcpyDeviceToDevice, st));
+  CDX_CUDA(cudaMemsetAsync(g.U, 0, mat, st));
+  CDX_CUDA(cudaMemsetAsync(g.flag, 0, sizeof(int), st));
+  const int nb = Np / 64;
+  const size_t potrf_smem_bytes = sizeof(double) * 2 * 64 * 65;
+  CDX_CUDA(cudaFuncSetAttribute(potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)potrf_smem_bytes));
+  for (int kb = 0; kb < nb; kb++) {
+    double* Akk = g.L + (int64_t)kb * 64 * (ld + 1);
+    potrf_diag_kernel<<<1, 256, potrf_smem_bytes, st>>>(Akk, ld, g.Dinv + (int64_t)kb * 4096, g.U + (int64_t)kb * 64 * (ld + 1), g.flag,
+                                         kb * 64);
+    CDX_CHECK_LAUNCH(ctx);
+    int m = Np - (kb + 1) * 64;
+    if (m > 0) {
+      double* A21 = Akk + 64 * ld;
+      // L21 = A21 * inv(Lkk)^T   (in place: each CTA reads its own 64x64 row block completely before writing it)
+      int rc = cdx_dgemm(ctx, false, false, m, 64, 64, 1.0, A21, ld, g.Dinv + (int64_t)kb * 4096, 64, 0.0, A21, ld, false,
+                         0, 1, 0, 0, 0, st);
+      if (rc) return rc;
+      // A22 -= L21 L21^T  (lower tiles only)
+      rc = cdx_dgemm(ctx, false, false, m, m, 64, -1.0, A21, ld, A21, ld, 1.0, A21 + 64, ld, true, 0, 1, 0, 0, 0, st);
+      if (rc) return rc;
+    }
+  }
+  dim3 g2((Np + 255) / 256, Np);
+  zero_upper_kernel<<<g2, 256, 0, st>>>(g.L, Np);
+  CDX_CHECK_LAUNCH(ctx);
+  // U = L^-1 by doubling: inv([L11 0; L21 L22]) = [U11 0; -U22 L21 U11, U22]; P is scratch for T = L21 U11
+  for (int s = 64; s < Np; s *= 2) {
+    int npairs = (Np + 2 * s - 1) / (2 * s);
+    int nfull = 0;
+    for (int p = 0; p < npairs; p++) if (2 * p * s + 2 * s <= Np) nfull++;
+    auto level = [&](int p0, int batch, int r) -> int {
+      int64_t off11 = (int64_t)(2 * p0 * s) * (ld + 1);
+      int64_t off21 = off11 + (int64_t)s * ld;
+      int64_t off22 = off11 + (int64_t)s * (ld + 1);
+      int64_t stride = (int64_t)(2 * s) * (ld + 1);
+      int rc = cdx_dgemm(ctx, false, true, r, s, s, 1.0, g.L + off21, ld, g.U + off11, ld, 0.0, g.P + off21, ld, false, 1,
+                         batch, stride, stride, stride, st);
+      if (rc) return rc;
+      return cdx_dgemm(ctx, false, true, r, s, r, -1.0, g.U + off22, ld, g.P + off21, ld, 0.0, g.U + off21, ld, false, 2,
+                       batch, stride, stride, stride, st);
+    };
+    if (nfull > 0) { int rc = level(0, nfull, s); if (rc) return rc; }
+    if (nfull < npairs) {
+      int r = Np - (2 * nfull * s + s);
+      if (r > 0) { int rc = level(nfull, 1, r); if (rc) return rc; }
+    }
+  }
+  // P = U^T U (lower tiles, k >= m0), mirrored
+  int rc = cdx_dgemm(ctx, true, true, Np, Np, Np, 1.0, g.U, ld, g.U, ld, 0.0, g.P, ld, true, 3, 1, 0, 0, 0, st);
+  if (rc) return rc;
+  mirror_lower_kernel<<<g2, 256, 0, st>>>(g.P, Np);
+  CDX_CHECK_LAUNCH(ctx);
+  // alpha = U^T (U y1)
+  trmv_lower_kernel<<<(Np + 7) / 8, 256, 0, st>>>(g.U, Np, g.y1, g.tmp);
+  CDX_CHECK_LAUNCH(ctx);
+  trmv_lower_t_kernel<<<(Np + 127) / 128, 128, 0, st>>>(g.U, Np, g.tmp, g.tmp + Np);
+  CDX_CHECK_LAUNCH(ctx);
+  pack_xa_kernel<<<(Np + 255) / 256, 256, 0, st>>>(X1, g.tmp + Np, N, Np, g.Xa);
+  CDX_CHECK_LAUNCH(ctx);
+  cdx_kparams kp = cdx_make_kparams(g);
+  g.prior = g.kernel == CDX_KERNEL_TPS ? kp.R3 : (g.kernel == CDX_KERNEL_RBF ? 1.0 : 0.3 + 0.7 * kp.R3);
+  g.ready = true;
+  return CDX_OK;
+}
+
+}  // namespace
+
+extern "C" int cdx_create(int device, cdx_ctx** out) {
+  if (!out) { cdx_set_error("cdx_create: null out"); return CDX_ERR_ARG; }
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) {
+    cudaGetLastError();
+    cdx_set_error("cdx_create: no usable CUDA device %d (count %d); cdx has no CPU fallback", device, n);
+    return CDX_ERR_CUDA;
+  }
+  CDX_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CDX_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    cdx_set_error("cdx_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    return CDX_ERR_CUDA;
+  }
+  cdx_ctx* c = new cdx_ctx();
+  c->device = device;
+  c->sms = prop.multiProcessorCount;
+  *out = c;
+  return CDX_OK;
+}
+
+void cdx_pregrasp_free(cdx_ctx* ctx);
+
+extern "C" int cdx_destroy(cdx_ctx* ctx) {
+  if (!ctx) return CDX_OK;
+  cudaSetDevice(ctx->device);
+  cdx_gpis_state& g = ctx->g;
+  cudaFree(g.Xa); cudaFree(g.y1); cudaFree(g.E11); cudaFree(g.L); cudaFree(g.U); cudaFree(g.P);
+  cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.dR2); cudaFree(g.flag);
+  cudaFree(ctx->hx); cudaFree(ctx->hout);
+  cdx_pregrasp_free(ctx);
+  delete ctx;
+  return CDX_OK;
+}
+
+extern "C" int64_t cdx_launch_count(cdx_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int cdx_gpis_fit(cdx_ctx* ctx, const double* X1, const double* y1, const double* noise, double noise_scalar,
+                            int64_t N, double bias, int kernel, double sigma, void* stream) {
+  if (!ctx || !X1 || !y1 || N <= 0 || kernel < 0 || kernel > 2) { cdx_set_error("cdx_gpis_fit: bad argument"); return CDX_ERR_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  int rc = gpis_reserve(ctx, N);
+  if (rc) return rc;
+  cdx_gpis_state& g = ctx->g;
+  g.kernel = kernel; g.sigma = sigma; g.bias = bias; g.R = 0.0;
+  const int Np = (int)g.Np;
+  if (kernel != CDX_KERNEL_RBF) {  // gpis.py:35-36
+    CDX_CUDA(cudaMemsetAsync(g.dR2, 0, sizeof(double), st));
+    pairmax_kernel<<<((int)N + 127) / 128, 128, 0, st>>>(X1, (int)N, (unsigned long long*)g.dR2);
+    CDX_CHECK_LAUNCH(ctx);
+    double r2 = 0;
+    CDX_CUDA(cudaMemcpyAsync(&r2, g.dR2, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CDX_CUDA(cudaStreamSynchronize(st));
+    g.R = sqrt(r2);
+  }
+  sub_bias_kernel<<<(Np + 255) / 256, 256, 0, st>>>(y1, (int)N, Np, bias, g.y1);  // gpis.py:38
+  CDX_CHECK_LAUNCH(ctx);
+  cdx_kparams kp = cdx_make_kparams(g);
+  dim3 g2((Np + 255) / 256, Np);
+  if (kernel == CDX_KERNEL_TPS) assemble_kernel<CDX_KERNEL_TPS><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11);
+  else if (kernel == CDX_KERNEL_RBF) assemble_kernel<CDX_KERNEL_RBF><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11);
+  else assemble_kernel<CDX_KERNEL_JOINT><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11);
+  CDX_CHECK_LAUNCH(ctx);
+  return gpis_factorise(ctx, X1, st);
+}
+
+extern "C" int cdx_gpis_set_state(cdx_ctx* ctx, const double* X1, const double* y1, const double* E11, double R,
+                                  double bias, int64_t N, int kernel, double sigma, void* stream) {
+  if (!ctx || !X1 || !y1 || !E11 || N <= 0 || kernel < 0 || kernel > 2) { cdx_set_error("cdx_gpis_set_state: bad argument"); return CDX_ERR_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  int rc = gpis_reserve(ctx, N);
+  if (rc) return rc;
+  cdx_gpis_state& g = ctx->g;
+  g.kernel = kernel; g.sigma = sigma; g.bias = bias; g.R = R;
+  const int Np = (int)g.Np;
+  sub_bias_kernel<<<(Np + 255) / 256, 256, 0, st>>>(y1, (int)N, Np, 0.0, g.y1);
+  CDX_CHECK_LAUNCH(ctx);
+  dim3 g2((Np + 255) / 256, Np);
+  pad_copy_kernel<<<g2, 256, 0, st>>>(E11, (int)N, Np, g.E11);
+  CDX_CHECK_LAUNCH(ctx);
+  return gpis_factorise(ctx, X1, st);
+}
+
+extern "C" int cdx_gpis_info(cdx_ctx* ctx, int64_t* N, double* R, double* bias, double* prior, int* not_spd_col, void* stream) {
+  if (!ctx || !ctx->g.ready) { cdx_set_error("cdx_gpis_info: no fitted state"); return CDX_ERR_STATE; }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  int f = 0;
+  CDX_CUDA(cudaMemcpyAsync(&f, ctx->g.flag, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CDX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  if (N) *N = ctx->g.N;
+  if (R) *R = ctx->g.R;
+  if (bias) *bias = ctx->g.bias;
+  if (prior) *prior = ctx->g.prior;
+  if (not_spd_col) *not_spd_col = f - 1;
+  if (f) { cdx_set_error("E11 is not positive definite: Cholesky pivot at column %d <= 0", f - 1); return CDX_ERR_NOT_SPD; }
+  return CDX_OK;
+}
+
+extern "C" int cdx_gpis_get(cdx_ctx* ctx, int which, double* out, void* stream) {
+  if (!ctx || !ctx->g.ready || !out) { cdx_set_error("cdx_gpis_get: no fitted state / null out"); return CDX_ERR_STATE; }
+  cudaStream_t st = (cudaStream_t)stream;
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  cdx_gpis_state& g = ctx->g;
+  const int N = (int)g.N, Np = (int)g.Np;
+  dim3 g2((N + 255) / 256, N);
+  const double* src = nullptr;
+  switch (which) {
+    case CDX_MAT_E11: src = g.E11; break;
+    case CDX_MAT_CHOL: src = g.L; break;
+    case CDX_MAT_CHOL_INV: src = g.U; break;
+    case CDX_MAT_E11_INV: src = g.P; break;
+    case CDX_VEC_ALPHA: extract_alpha_kernel<<<(N + 255) / 256, 256, 0, st>>>(g.Xa, N, out); CDX_CHECK_LAUNCH(ctx); return CDX_OK;
+    case CDX_VEC_Y1: CDX_CUDA(cudaMemcpyAsync(out, g.y1, sizeof(double) * N, cudaMemcpyDeviceToDevice, st)); return CDX_OK;
+    case CDX_MAT_X1: extract_x_kernel<<<(N + 255) / 256, 256, 0, st>>>(g.Xa, N, out); CDX_CHECK_LAUNCH(ctx); return CDX_OK;
+    default: cdx_set_error("cdx_gpis_get: unknown selector %d", which); return CDX_ERR_ARG;
+  }
+  unpad_copy_kernel<<<g2, 256, 0, st>>>(src, N, Np, out);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}

@@ -1,0 +1,149 @@
+// Generic FP64 GEMM on the DMMA tensor path (mma.sync m8n8k4 f64) used by the one-time fit:
+// Cholesky trailing updates (SYRK), panel solves, the block-recursive triangular inverse and E11^-1 = U^T U.
+// 64x64x16 CTA tile, 4 warps (2x2), each warp a 32x32 tile = 4x4 DMMA blocks; operands staged in shared memory
+// as [row][k] with a 20-double row stride (conflict-free for the DMMA fragment pattern row=T/4, k=T%4).
+#include "cdx_internal.cuh"
+
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16, LDS = 20;
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(128) dgemm_kernel(int M, int N, int K, double alpha, const double* __restrict__ A,
+                                                    int64_t lda, const double* __restrict__ B, int64_t ldb, double beta,
+                                                    double* __restrict__ C, int64_t ldc, int lower_only, int ktri,
+                                                    int64_t sA, int64_t sB, int64_t sC) {
+  const int tm = blockIdx.y, tn = blockIdx.x;
+  if (lower_only && tn > tm) return;
+  A += (int64_t)blockIdx.z * sA;
+  B += (int64_t)blockIdx.z * sB;
+  C += (int64_t)blockIdx.z * sC;
+  __shared__ double As[BM * LDS];
+  __shared__ double Bs[BN * LDS];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int wm = warp >> 1, wn = warp & 1;
+  const int m0 = tm * BM, n0 = tn * BN;
+
+  double ra[8], rb[8];
+  auto load_tiles = [&](int k0) {
+    if (!TA) {  // A[M,K]: thread -> row t/2, 8 consecutive k
+      int r = t >> 1, kk = (t & 1) * 8;
+      const double* p = A + (int64_t)(m0 + r) * lda + k0 + kk;
+      bool rok = (m0 + r) < M;
+#pragma unroll
+      for (int i = 0; i < 8; i++) ra[i] = (rok && (k0 + kk + i) < K) ? p[i] : 0.0;
+    } else {  // A[K,M]: thread -> k = t/8, 8 consecutive m
+      int kk = t >> 3, mm = (t & 7) * 8;
+      const double* p = A + (int64_t)(k0 + kk) * lda + m0 + mm;
+      bool kok = (k0 + kk) < K;
+#pragma unroll
+      for (int i = 0; i < 8; i++) ra[i] = (kok && (m0 + mm + i) < M) ? p[i] : 0.0;
+    }
+    if (!TB) {  // B[N,K]
+      int r = t >> 1, kk = (t & 1) * 8;
+      const double* p = B + (int64_t)(n0 + r) * ldb + k0 + kk;
+      bool rok = (n0 + r) < N;
+#pragma unroll
+      for (int i = 0; i < 8; i++) rb[i] = (rok && (k0 + kk + i) < K) ? p[i] : 0.0;
+    } else {  // B[K,N]
+      int kk = t >> 3, nn = (t & 7) * 8;
+      const double* p = B + (int64_t)(k0 + kk) * ldb + n0 + nn;
+      bool kok = (k0 + kk) < K;
+#pragma unroll
+      for (int i = 0; i < 8; i++) rb[i] = (kok && (n0 + nn + i) < N) ? p[i] : 0.0;
+    }
+  };
+  auto store_tiles = [&]() {
+    if (!TA) {
+      int r = t >> 1, kk = (t & 1) * 8;
+#pragma unroll
+      for (int i = 0; i < 8; i++) As[r * LDS + kk + i] = ra[i];
+    } else {
+      int kk = t >> 3, mm = (t & 7) * 8;
+#pragma unroll
+      for (int i = 0; i < 8; i++) As[(mm + i) * LDS + kk] = ra[i];
+    }
+    if (!TB) {
+      int r = t >> 1, kk = (t & 1) * 8;
+#pragma unroll
+      for (int i = 0; i < 8; i++) Bs[r * LDS + kk + i] = rb[i];
+    } else {
+      int kk = t >> 3, nn = (t & 7) * 8;
+#pragma unroll
+      for (int i = 0; i < 8; i++) Bs[(nn + i) * LDS + kk] = rb[i];
+    }
+  };
+
+  double acc[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+  const int fr = lane >> 2, fk = lane & 3;
+  // triangular operands: skip k ranges known to be zero (ktri 1: k >= n0, 2: k < m0+BM, 3: k >= m0)
+  int kbeg = 0, kend = K;
+  if (ktri == 1) kbeg = n0;
+  if (ktri == 3) kbeg = m0;
+  if (ktri == 2) kend = min(K, m0 + BM);
+  load_tiles(kbeg);
+  const int Kfull = K;
+  K = kend;
+  (void)Kfull;
+  for (int k0 = kbeg; k0 < K; k0 += BK) {
+    __syncthreads();
+    store_tiles();
+    __syncthreads();
+    if (k0 + BK < K) load_tiles(k0 + BK);
+#pragma unroll
+    for (int ks = 0; ks < BK; ks += 4) {
+      double a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) a[i] = As[(wm * 32 + i * 8 + fr) * LDS + ks + fk];
+#pragma unroll
+      for (int j = 0; j < 4; j++) b[j] = Bs[(wn * 32 + j * 8 + fr) * LDS + ks + fk];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) cdx_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      int r = m0 + wm * 32 + i * 8 + fr;
+      int c = n0 + wn * 32 + j * 8 + 2 * fk;
+      if (r < M) {
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          if (c + e < N) {
+            double* p = C + (int64_t)r * ldc + c + e;
+            double v = alpha * acc[i][j][e];
+            if (beta != 0.0) v += beta * (*p);
+            *p = v;
+          }
+        }
+      }
+    }
+}
+
+}  // namespace
+
+int cdx_dgemm(cdx_ctx* ctx, bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int64_t lda,
+              const double* B, int64_t ldb, double beta, double* C, int64_t ldc, bool lower_only, int ktri, int batch,
+              int64_t sA, int64_t sB, int64_t sC, cudaStream_t st) {
+  if (M <= 0 || N <= 0 || batch <= 0) return CDX_OK;
+  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
+  int lo = lower_only ? 1 : 0;
+  if (!ta && !tb)
+    dgemm_kernel<false, false><<<grid, 128, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lo, ktri, sA, sB, sC);
+  else if (!ta && tb)
+    dgemm_kernel<false, true><<<grid, 128, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lo, ktri, sA, sB, sC);
+  else if (ta && !tb)
+    dgemm_kernel<true, false><<<grid, 128, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lo, ktri, sA, sB, sC);
+  else
+    dgemm_kernel<true, true><<<grid, 128, 0, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lo, ktri, sA, sB, sC);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}

@@ -1,0 +1,406 @@
+// GPIS posterior queries (gpis.py:43-59 pred, :63-87 compute_normal, and the autograd gradients the optimizers
+// take through pred).  Three kernels:
+//  * gpis_mean_kernel      mean + grad_mean only: training set (x,y,z,alpha) staged in shared memory by bulk TMA
+//                          (cp.async.bulk + mbarrier), 4 lanes per query, shuffle reduction.   24 N flop + N sqrt / query
+//  * gpis_var_kernel<EXT=0> unit query {mean, grad_mean, std}:  v = L^-1 k* as a triangular product with the
+//                          precomputed inverse factor U on the FP64 tensor path (DMMA), k* generated on the fly,
+//                          |v|^2 reduced in the epilogue; nothing of size N per query ever reaches HBM.   N^2 + 26 N flop
+//  * gpis_var_kernel<EXT=1> extended query (+ grad_std): w = E11^-1 k* with the full inverse, epilogue forms
+//                          var = k(x,x) - k*.w and grad var = -2 sum_i w_i c_i (x - x_i).                 2 N^2 + 34 N flop
+#include "cdx_internal.cuh"
+
+namespace {
+
+constexpr int TQ = 128;   // queries per CTA
+constexpr int TK = 16;    // training points per k-chunk
+constexpr int LDS = 20;   // shared-memory row stride (doubles): conflict-free for lane -> (row = T/4, k = T%4)
+constexpr int NA = 3, NB = 4;  // ring depths: generated k* tiles / cp.async tiles of U or P
+
+template <int KERNEL, int TN, bool EXT>
+__global__ void __launch_bounds__(512, 1)
+gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restrict__ Xa, const double* __restrict__ Bmat,
+                int N, int Np, cdx_kparams kp, double bias, double prior, double* __restrict__ mean,
+                double* __restrict__ gmean, double* __restrict__ stdv, double* __restrict__ gstd) {
+  constexpr int WN = TN / 4, NBW = WN / 8;
+  extern __shared__ __align__(16) double smem[];
+  double* As = smem;                          // [NA][TQ*LDS]
+  double* Bs = As + NA * TQ * LDS;            // [NB][TN*LDS]
+  double* sxq = Bs + NB * TN * LDS;           // [TQ][3]
+  double* red = sxq + TQ * 3;                 // [4][TQ][4]
+
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int fr = lane >> 2, fk = lane & 3;
+  const int wm = warp >> 2, wn = warp & 3;
+  const int64_t q0 = (int64_t)blockIdx.x * TQ;
+
+  for (int e = t; e < TQ * 3; e += 512) {
+    int64_t q = q0 + e / 3;
+    sxq[e] = q < M ? Xq[q * 3 + e % 3] : 0.0;
+  }
+  __syncthreads();
+  // generator role: query row 8*warp + lane/4, training points (lane%4) + 4 i of each chunk
+  const int qg = warp * 8 + fr;
+  const double xq = sxq[qg * 3], yq = sxq[qg * 3 + 1], zq = sxq[qg * 3 + 2];
+  double m_acc = 0.0, gx = 0.0, gy = 0.0, gz = 0.0;
+
+  double ss[4];          // !EXT: sum v^2 per owned row
+  double ev[4][4];       // EXT: (k.w, w c dx, w c dy, w c dz) per owned row
+#pragma unroll
+  for (int i = 0; i < 4; i++) { ss[i] = 0.0; ev[i][0] = ev[i][1] = ev[i][2] = ev[i][3] = 0.0; }
+
+  const int NT = (Np + TN - 1) / TN;
+  const double2* Xa2 = reinterpret_cast<const double2*>(Xa);
+
+  auto issueB = [&](int n0, int c, int buf) {
+    double* dst = Bs + buf * TN * LDS;
+    for (int p = t; p < TN * 8; p += 512) {
+      int row = p >> 3, seg = p & 7;
+      double* d = dst + row * LDS + seg * 2;
+      if (n0 + row < Np) cdx_cp_async16(d, Bmat + (int64_t)(n0 + row) * Np + c * TK + seg * 2);
+      else { d[0] = 0.0; d[1] = 0.0; }
+    }
+  };
+  auto genA = [&](int c, int buf, bool meanpass) {
+    double* dst = As + buf * TQ * LDS + qg * LDS + fk;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      int j = c * TK + fk + 4 * i;
+      double2 p0 = __ldg(Xa2 + 2 * j), p1 = __ldg(Xa2 + 2 * j + 1);
+      double dx = xq - p0.x, dy = yq - p0.y, dz = zq - p1.x;
+      double k, cc;
+      cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, cc);
+      if (j >= N) k = 0.0;
+      dst[4 * i] = k;
+      if (meanpass) {
+        double a = p1.y;  // alpha (0 on padded rows)
+        m_acc = fma(a, k, m_acc);
+        double ac = a * cc;
+        gx = fma(ac, dx, gx); gy = fma(ac, dy, gy); gz = fma(ac, dz, gz);
+      }
+    }
+  };
+
+  for (int nt = NT - 1; nt >= 0; nt--) {
+    const int n0 = nt * TN;
+    const int kmax = EXT ? Np : min(Np, n0 + TN);
+    const int nch = kmax / TK;
+    const bool meanpass = (nt == NT - 1);
+    double acc[4][NBW][2];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j = 0; j < NBW; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    issueB(n0, 0, 0);
+    cdx_cp_async_commit();
+    if (nch > 1) issueB(n0, 1, 1);
+    cdx_cp_async_commit();
+    genA(0, 0, meanpass);
+    for (int c = 0; c < nch; c++) {
+      if (c + 2 < nch) issueB(n0, c + 2, (c + 2) % NB);
+      cdx_cp_async_commit();
+      if (c + 1 < nch) genA(c + 1, (c + 1) % NA, meanpass);
+      cdx_cp_async_wait<2>();
+      __syncthreads();
+      const double* a_s = As + (c % NA) * TQ * LDS + (wm * 32 + fr) * LDS + fk;
+      const double* b_s = Bs + (c % NB) * TN * LDS + (wn * WN + fr) * LDS + fk;
+#pragma unroll
+      for (int ks = 0; ks < TK; ks += 4) {
+        double a[4], b[NBW];
+#pragma unroll
+        for (int i = 0; i < 4; i++) a[i] = a_s[i * 8 * LDS + ks];
+#pragma unroll
+        for (int j = 0; j < NBW; j++) b[j] = b_s[j * 8 * LDS + ks];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int j = 0; j < NBW; j++) cdx_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+      }
+    }
+    // epilogue of this n-tile
+    if (!EXT) {
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < NBW; j++) ss[i] = fma(acc[i][j][0], acc[i][j][0], fma(acc[i][j][1], acc[i][j][1], ss[i]));
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int r = wm * 32 + i * 8 + fr;
+        const double rx = sxq[r * 3], ry = sxq[r * 3 + 1], rz = sxq[r * 3 + 2];
+#pragma unroll
+        for (int j = 0; j < NBW; j++)
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            int col = n0 + wn * WN + j * 8 + 2 * fk + e;
+            if (col < N) {
+              double2 p0 = __ldg(Xa2 + 2 * col), p1 = __ldg(Xa2 + 2 * col + 1);
+              double dx = rx - p0.x, dy = ry - p0.y, dz = rz - p1.x;
+              double k, cc;
+              cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, cc);
+              double w = acc[i][j][e];
+              ev[i][0] = fma(k, w, ev[i][0]);
+              double wc = w * cc;
+              ev[i][1] = fma(wc, dx, ev[i][1]); ev[i][2] = fma(wc, dy, ev[i][2]); ev[i][3] = fma(wc, dz, ev[i][3]);
+            }
+          }
+      }
+    }
+    __syncthreads();  // all warps done with the rings before the next n-tile refills them
+  }
+
+  // mean / grad_mean: reduce over the 4 lanes that share a query row
+  m_acc += __shfl_xor_sync(0xffffffffu, m_acc, 1); m_acc += __shfl_xor_sync(0xffffffffu, m_acc, 2);
+  gx += __shfl_xor_sync(0xffffffffu, gx, 1); gx += __shfl_xor_sync(0xffffffffu, gx, 2);
+  gy += __shfl_xor_sync(0xffffffffu, gy, 1); gy += __shfl_xor_sync(0xffffffffu, gy, 2);
+  gz += __shfl_xor_sync(0xffffffffu, gz, 1); gz += __shfl_xor_sync(0xffffffffu, gz, 2);
+  if (fk == 0 && q0 + qg < M) {
+    if (mean) mean[q0 + qg] = m_acc + bias;
+    if (gmean) { gmean[(q0 + qg) * 3] = gx; gmean[(q0 + qg) * 3 + 1] = gy; gmean[(q0 + qg) * 3 + 2] = gz; }
+  }
+  // variance terms: quad reduce, then across the 4 column-warps through shared memory (fixed order: deterministic)
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int r = wm * 32 + i * 8 + fr;
+    if (!EXT) {
+      double s = ss[i];
+      s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
+      if (fk == 0) red[(wn * TQ + r) * 4] = s;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        double s = ev[i][e];
+        s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
+        if (fk == 0) red[(wn * TQ + r) * 4 + e] = s;
+      }
+    }
+  }
+  __syncthreads();
+  if (t < TQ && q0 + t < M) {
+    const int64_t q = q0 + t;
+    double v[4];
+#pragma unroll
+    for (int e = 0; e < (EXT ? 4 : 1); e++)
+      v[e] = (red[(0 * TQ + t) * 4 + e] + red[(1 * TQ + t) * 4 + e]) + (red[(2 * TQ + t) * 4 + e] + red[(3 * TQ + t) * 4 + e]);
+    double var = prior - v[0];
+    double sd = sqrt(fabs(var));  // gpis.py:59
+    if (stdv) stdv[q] = sd;
+    if (EXT && gstd) {
+      // d sqrt|var| = sign(var) dvar / (2 sd),  dvar = -2 sum_i w_i c_i (x - x_i)
+      double f = (var < 0.0 ? 1.0 : -1.0) / sd;
+      gstd[q * 3] = f * v[1]; gstd[q * 3 + 1] = f * v[2]; gstd[q * 3 + 2] = f * v[3];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ mean only
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned phase) {
+  unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(a), "r"(phase) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+
+constexpr int MQ = 64;  // queries per CTA pass (4 lanes each)
+
+template <int KERNEL>
+__global__ void __launch_bounds__(256)
+gpis_mean_kernel(const double* __restrict__ Xq, int64_t M, const double* __restrict__ Xa, int N, int Np, int tile_pts,
+                 cdx_kparams kp, double bias, double* __restrict__ mean, double* __restrict__ gmean) {
+  extern __shared__ __align__(16) double smem[];
+  double* sX = smem;                                              // [tile_pts][4]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + (size_t)tile_pts * 4);
+  const int t = threadIdx.x, jsub = t & 3;
+  if (t == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+  const int ntt = (Np + tile_pts - 1) / tile_pts;
+  const int64_t nqt = (M + MQ - 1) / MQ;
+  int staged = -1;
+  unsigned phase = 0;
+  const double2* s2 = reinterpret_cast<const double2*>(sX);
+  for (int64_t qt = blockIdx.x; qt < nqt; qt += gridDim.x) {
+    const int64_t q = qt * MQ + (t >> 2);
+    const bool ok = q < M;
+    const double xq = ok ? Xq[q * 3] : 0.0, yq = ok ? Xq[q * 3 + 1] : 0.0, zq = ok ? Xq[q * 3 + 2] : 0.0;
+    double m0 = 0, m1 = 0, gx0 = 0, gy0 = 0, gz0 = 0, gx1 = 0, gy1 = 0, gz1 = 0;
+    for (int tt = 0; tt < ntt; tt++) {
+      const int p0 = tt * tile_pts, cnt = min(tile_pts, Np - p0);
+      if (staged != tt) {
+        __syncthreads();  // previous tile no longer being read
+        if (t == 0) {
+          unsigned bytes = (unsigned)cnt * 32u;
+          mbar_expect_tx(bar, bytes);
+          for (unsigned off = 0; off < bytes; off += 16384u)
+            tma_bulk_g2s(reinterpret_cast<char*>(sX) + off, reinterpret_cast<const char*>(Xa + (size_t)p0 * 4) + off,
+                         min(16384u, bytes - off), bar);
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        staged = tt;
+      }
+      // padded rows carry alpha = 0, so no masking is needed; cnt is a multiple of 64
+      for (int j = jsub; j < cnt; j += 8) {
+        double2 a0 = s2[2 * j], a1 = s2[2 * j + 1];
+        double2 b0 = s2[2 * (j + 4)], b1 = s2[2 * (j + 4) + 1];
+        double dx = xq - a0.x, dy = yq - a0.y, dz = zq - a1.x, k, c;
+        cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, c);
+        m0 = fma(a1.y, k, m0);
+        double ac = a1.y * c;
+        gx0 = fma(ac, dx, gx0); gy0 = fma(ac, dy, gy0); gz0 = fma(ac, dz, gz0);
+        double ex = xq - b0.x, ey = yq - b0.y, ez = zq - b1.x, k2, c2;
+        cdx_kernel_eval<KERNEL>(fma(ex, ex, fma(ey, ey, ez * ez)), kp, k2, c2);
+        m1 = fma(b1.y, k2, m1);
+        double bc = b1.y * c2;
+        gx1 = fma(bc, ex, gx1); gy1 = fma(bc, ey, gy1); gz1 = fma(bc, ez, gz1);
+      }
+    }
+    double m = m0 + m1, gx = gx0 + gx1, gy = gy0 + gy1, gz = gz0 + gz1;
+    m += __shfl_xor_sync(0xffffffffu, m, 1); m += __shfl_xor_sync(0xffffffffu, m, 2);
+    gx += __shfl_xor_sync(0xffffffffu, gx, 1); gx += __shfl_xor_sync(0xffffffffu, gx, 2);
+    gy += __shfl_xor_sync(0xffffffffu, gy, 1); gy += __shfl_xor_sync(0xffffffffu, gy, 2);
+    gz += __shfl_xor_sync(0xffffffffu, gz, 1); gz += __shfl_xor_sync(0xffffffffu, gz, 2);
+    if (ok && jsub == 0) {
+      if (mean) mean[q] = m + bias;
+      if (gmean) { gmean[q * 3] = gx; gmean[q * 3 + 1] = gy; gmean[q * 3 + 2] = gz; }
+    }
+  }
+}
+
+__global__ void pack_weights_kernel(const double* __restrict__ Xa, const double* __restrict__ w, int N, int Np,
+                                    double* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Np) return;
+  out[4 * i] = Xa[4 * i]; out[4 * i + 1] = Xa[4 * i + 1]; out[4 * i + 2] = Xa[4 * i + 2];
+  out[4 * i + 3] = i < N ? w[i] : 0.0;
+}
+
+template <int KERNEL>
+int launch_mean(cdx_ctx* ctx, const double* Xa, const double* X, int64_t M, double bias, double* mean, double* gmean,
+                cudaStream_t st) {
+  cdx_gpis_state& g = ctx->g;
+  int tile = (int)min((int64_t)4096, g.Np);
+  size_t smem = (size_t)tile * 32 + 16;
+  static bool attr_set[3] = {false, false, false};
+  if (!attr_set[KERNEL]) {
+    CDX_CUDA(cudaFuncSetAttribute(gpis_mean_kernel<KERNEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 32 + 16));
+    attr_set[KERNEL] = true;
+  }
+  int per_sm = (int)max((size_t)1, min((size_t)8, (size_t)(200 * 1024) / smem));
+  int64_t nqt = (M + MQ - 1) / MQ;
+  int grid = (int)min(nqt, (int64_t)ctx->sms * per_sm);
+  gpis_mean_kernel<KERNEL><<<grid, 256, smem, st>>>(X, M, Xa, (int)g.N, (int)g.Np, tile, cdx_make_kparams(g), bias, mean, gmean);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}
+
+template <int KERNEL, int TN, bool EXT>
+int launch_var(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
+               cudaStream_t st) {
+  cdx_gpis_state& g = ctx->g;
+  size_t smem = sizeof(double) * (size_t)(NA * TQ * LDS + NB * TN * LDS + TQ * 3 + 4 * TQ * 4);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CDX_CUDA(cudaFuncSetAttribute(gpis_var_kernel<KERNEL, TN, EXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  int64_t grid = (M + TQ - 1) / TQ;
+  gpis_var_kernel<KERNEL, TN, EXT><<<(unsigned)grid, 512, smem, st>>>(X, M, g.Xa, EXT ? g.P : g.U, (int)g.N, (int)g.Np,
+                                                                      cdx_make_kparams(g), g.bias, g.prior, mean, gmean,
+                                                                      stdv, gstd);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}
+
+template <int KERNEL>
+int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
+                   cudaStream_t st) {
+  cdx_gpis_state& g = ctx->g;
+  const bool big = (g.Np % 128 == 0) && g.Np >= 512;
+  if (gstd) return big ? launch_var<KERNEL, 128, true>(ctx, X, M, mean, gmean, stdv, gstd, st)
+                       : launch_var<KERNEL, 64, true>(ctx, X, M, mean, gmean, stdv, gstd, st);
+  if (stdv) return big ? launch_var<KERNEL, 128, false>(ctx, X, M, mean, gmean, stdv, nullptr, st)
+                       : launch_var<KERNEL, 64, false>(ctx, X, M, mean, gmean, stdv, nullptr, st);
+  return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
+}
+
+}  // namespace
+
+extern "C" int cdx_gpis_query(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv,
+                              double* gstd, void* stream) {
+  if (!ctx || !ctx->g.ready) { cdx_set_error("cdx_gpis_query: no fitted state"); return CDX_ERR_STATE; }
+  if (M < 0 || (M > 0 && !X)) { cdx_set_error("cdx_gpis_query: bad argument"); return CDX_ERR_ARG; }
+  if (M == 0 || (!mean && !gmean && !stdv && !gstd)) return CDX_OK;
+  if (M > (int64_t)2147483647 * 64) { cdx_set_error("cdx_gpis_query: M too large"); return CDX_ERR_ARG; }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (ctx->g.kernel) {
+    case CDX_KERNEL_TPS: return query_dispatch<CDX_KERNEL_TPS>(ctx, X, M, mean, gmean, stdv, gstd, st);
+    case CDX_KERNEL_RBF: return query_dispatch<CDX_KERNEL_RBF>(ctx, X, M, mean, gmean, stdv, gstd, st);
+    default: return query_dispatch<CDX_KERNEL_JOINT>(ctx, X, M, mean, gmean, stdv, gstd, st);
+  }
+}
+
+extern "C" int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha, const double* X, int64_t M, double* mean,
+                                      double* gmean, void* stream) {
+  if (!ctx || !ctx->g.ready) { cdx_set_error("cdx_gpis_query_weights: no fitted state"); return CDX_ERR_STATE; }
+  if (!alpha || M < 0 || (M > 0 && !X)) { cdx_set_error("cdx_gpis_query_weights: bad argument"); return CDX_ERR_ARG; }
+  if (M == 0) return CDX_OK;
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  cdx_gpis_state& g = ctx->g;
+  double* Xw = nullptr;  // (x,y,z,w) copy of the training set with the caller's weights
+  CDX_CUDA(cudaMallocAsync((void**)&Xw, sizeof(double) * 4 * g.Np, st));
+  pack_weights_kernel<<<((int)g.Np + 255) / 256, 256, 0, st>>>(g.Xa, alpha, (int)g.N, (int)g.Np, Xw);
+  CDX_CHECK_LAUNCH(ctx);
+  int rc;
+  switch (g.kernel) {
+    case CDX_KERNEL_TPS: rc = launch_mean<CDX_KERNEL_TPS>(ctx, Xw, X, M, 0.0, mean, gmean, st); break;
+    case CDX_KERNEL_RBF: rc = launch_mean<CDX_KERNEL_RBF>(ctx, Xw, X, M, 0.0, mean, gmean, st); break;
+    default: rc = launch_mean<CDX_KERNEL_JOINT>(ctx, Xw, X, M, 0.0, mean, gmean, st); break;
+  }
+  cudaFreeAsync(Xw, st);
+  return rc;
+}
+
+extern "C" int cdx_gpis_query_host(cdx_ctx* ctx, const double* Xh, int64_t M, double* mean_h, double* gmean_h,
+                                   double* std_h, double* gstd_h, void* stream) {
+  if (!ctx || !ctx->g.ready) { cdx_set_error("cdx_gpis_query_host: no fitted state"); return CDX_ERR_STATE; }
+  if (M < 0 || (M > 0 && !Xh)) { cdx_set_error("cdx_gpis_query_host: bad argument"); return CDX_ERR_ARG; }
+  if (M == 0) return CDX_OK;
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (M > ctx->hcap) {
+    cudaFree(ctx->hx); cudaFree(ctx->hout);
+    ctx->hcap = 0;
+    CDX_CUDA(cudaMalloc(&ctx->hx, sizeof(double) * 3 * M));
+    CDX_CUDA(cudaMalloc(&ctx->hout, sizeof(double) * 8 * M));
+    ctx->hcap = M;
+  }
+  double* dm = mean_h ? ctx->hout : nullptr;
+  double* ds = std_h ? ctx->hout + M : nullptr;
+  double* dgm = gmean_h ? ctx->hout + 2 * M : nullptr;
+  double* dgs = gstd_h ? ctx->hout + 5 * M : nullptr;
+  CDX_CUDA(cudaMemcpyAsync(ctx->hx, Xh, sizeof(double) * 3 * M, cudaMemcpyHostToDevice, st));
+  int rc = cdx_gpis_query(ctx, ctx->hx, M, dm, dgm, ds, dgs, stream);
+  if (rc) return rc;
+  if (dm) CDX_CUDA(cudaMemcpyAsync(mean_h, dm, sizeof(double) * M, cudaMemcpyDeviceToHost, st));
+  if (ds) CDX_CUDA(cudaMemcpyAsync(std_h, ds, sizeof(double) * M, cudaMemcpyDeviceToHost, st));
+  if (dgm) CDX_CUDA(cudaMemcpyAsync(gmean_h, dgm, sizeof(double) * 3 * M, cudaMemcpyDeviceToHost, st));
+  if (dgs) CDX_CUDA(cudaMemcpyAsync(gstd_h, dgs, sizeof(double) * 3 * M, cudaMemcpyDeviceToHost, st));
+  CDX_CUDA(cudaStreamSynchronize(st));
+  return CDX_OK;
+}

@@ -1,0 +1,229 @@
+"""Drop-in `GPIS` (reference: gpis.py:4-168) backed by libcdx.so.
+
+Same constructor, method names, argument meaning, tensor shapes / dtypes and state layout as the reference
+class; the arithmetic runs in hand-written sm_100a kernels behind the C ABI of include/cdx.h:
+  fit / load_state_data  -> cdx_gpis_fit / cdx_gpis_set_state (assembly + blocked Cholesky + inverses, once)
+  pred                   -> cdx_gpis_query (mean, std and - when X2 requires grad - both spatial gradients)
+  compute_normal         -> cdx_gpis_query (grad of the mean), normalised as gpis.py:83
+There is no CPU path: tensors must live on a CUDA device.
+"""
+import ctypes
+import os
+
+import numpy as np
+import torch
+
+from . import _lib
+
+STATE_DIR = "gpis_states"  # gpis.py:160,163 hard-code this relative directory
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class _PredFn(torch.autograd.Function):
+    """pred's outputs stay differentiable w.r.t. X2 as in the reference (autograd through gpis.py:51-59)."""
+
+    @staticmethod
+    def forward(ctx, X2, gpis):
+        M = X2.shape[0]
+        mean = torch.empty(M, dtype=torch.float64, device=X2.device)
+        std = torch.empty(M, dtype=torch.float64, device=X2.device)
+        need_grad = bool(ctx.needs_input_grad[0])
+        gm = torch.empty(M, 3, dtype=torch.float64, device=X2.device) if need_grad else None
+        gs = torch.empty(M, 3, dtype=torch.float64, device=X2.device) if need_grad else None
+        gpis._query(X2, mean, gm, std, gs)
+        if need_grad:
+            ctx.save_for_backward(gm, gs)
+        ctx.has = need_grad
+        return mean, std
+
+    @staticmethod
+    def backward(ctx, g_mean, g_std):
+        if not ctx.has:
+            return None, None
+        gm, gs = ctx.saved_tensors
+        out = torch.zeros_like(gm)
+        if g_mean is not None:
+            out = out + g_mean.unsqueeze(1) * gm
+        if g_std is not None:
+            out = out + g_std.unsqueeze(1) * gs
+        return out, None
+
+
+class GPIS:
+    def __init__(self, sigma=0.6, bias=2, kernel="tps"):
+        # gpis.py:5-14
+        if kernel not in _lib.KERNEL_IDS:
+            raise ValueError(f"unknown kernel {kernel!r}")
+        self.sigma = sigma
+        self.bias = bias
+        self.fraction = None
+        self.kernel = kernel
+        self.kernel_function = getattr(self, {"tps": "thin_plate_spline", "rbf": "exponentiated_quadratic",
+                                              "joint": "joint_kernel"}[kernel])
+        self._ctx = None
+        self._device = None
+
+    # ---- covariance functions: API parity only (plain torch, never on the query path) ------------------
+    def exponentiated_quadratic(self, xa, xb):
+        return torch.exp(-0.5 * torch.cdist(xa, xb) ** 2 / self.sigma ** 2)          # gpis.py:16-19
+
+    def thin_plate_spline(self, xa, xb, R=None):
+        R = self.R if R is None else R
+        d = torch.cdist(xa, xb)
+        return 2 * d ** 3 - 3 * R * d ** 2 + R ** 3                                    # gpis.py:21-26
+
+    def joint_kernel(self, xa, xb):
+        return 0.3 * self.exponentiated_quadratic(xa, xb) + 0.7 * self.thin_plate_spline(xa, xb)  # gpis.py:28-29
+
+    # ---- helpers ---------------------------------------------------------------------------------------
+    def _ensure_ctx(self, device):
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("compliancedex_b200.GPIS runs on CUDA tensors only (no CPU fallback)")
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        if self._ctx is None or self._device != idx:
+            self._ctx = _lib.new_context(idx)
+            self._device = idx
+        return self._ctx
+
+    def _check_factorisation(self):
+        lib = _lib.load()
+        n, r, b, p, col = ctypes.c_int64(), ctypes.c_double(), ctypes.c_double(), ctypes.c_double(), ctypes.c_int()
+        _lib.check(lib.cdx_gpis_info(self._ctx, ctypes.byref(n), ctypes.byref(r), ctypes.byref(b), ctypes.byref(p),
+                                     ctypes.byref(col), _stream(self._device)))
+        self._prior = p.value
+        return r.value
+
+    def _query(self, X, mean, gmean, std, gstd):
+        if self._ctx is None:
+            raise RuntimeError("GPIS: fit() or load_state_data() first")
+        X = X.contiguous()
+        _lib.check(_lib.load().cdx_gpis_query(self._ctx, _ptr(X), X.shape[0], _ptr(mean), _ptr(gmean), _ptr(std),
+                                              _ptr(gstd), _stream(self._device)))
+
+    # ---- fit / state -----------------------------------------------------------------------------------
+    def fit(self, X1, y1, noise=0.0):
+        """gpis.py:33-40.  X1 [N,3], y1 [N,1] float64 CUDA; noise scalar or [N]."""
+        ctx = self._ensure_ctx(X1.device)
+        X1c = X1.detach().double().contiguous()
+        y1c = y1.detach().double().reshape(-1).contiguous()
+        N = X1c.shape[0]
+        if torch.is_tensor(noise) and noise.numel() > 1:
+            nz = noise.detach().double().to(X1c.device).reshape(-1).contiguous()
+            assert nz.numel() == N
+            nptr, nscalar = _ptr(nz), 0.0
+        else:
+            nz, nptr, nscalar = None, None, float(noise)
+        _lib.check(_lib.load().cdx_gpis_fit(ctx, _ptr(X1c), _ptr(y1c), nptr, nscalar, N, float(self.bias),
+                                            _lib.KERNEL_IDS[self.kernel], float(self.sigma), _stream(self._device)))
+        R = self._check_factorisation()
+        self.X1 = X1
+        self.y1 = y1 - self.bias
+        self.noise = noise
+        if self.kernel in ("tps", "joint"):
+            self.R = torch.tensor(R, dtype=torch.float64, device=X1.device)
+        E = torch.empty(N, N, dtype=torch.float64, device=X1.device)
+        _lib.check(_lib.load().cdx_gpis_get(ctx, _lib.MAT_E11, _ptr(E), _stream(self._device)))
+        self.E11 = E
+
+    def _adopt(self, R, X1, y1, E11, bias):
+        ctx = self._ensure_ctx(X1.device)
+        self.R, self.X1, self.y1, self.E11, self.bias = R, X1, y1, E11, bias
+        _lib.check(_lib.load().cdx_gpis_set_state(
+            ctx, _ptr(X1.contiguous()), _ptr(y1.reshape(-1).contiguous()), _ptr(E11.contiguous()), float(R),
+            float(bias), X1.shape[0], _lib.KERNEL_IDS[self.kernel], float(self.sigma), _stream(self._device)))
+        self._check_factorisation()
+
+    def save_state_data(self, name="gpis_state"):
+        # gpis.py:155-160 - frozen layout: R, X1, y1 (bias-subtracted), E11, bias
+        np.savez(f"{STATE_DIR}/{name}.npz", R=self.R.cpu().numpy(), X1=self.X1.cpu().numpy(), y1=self.y1.cpu().numpy(),
+                 E11=self.E11.cpu().numpy(), bias=self.bias if not torch.is_tensor(self.bias) else self.bias.cpu().numpy())
+
+    def load_state_data(self, name="gpis_state", device="cuda"):
+        # gpis.py:162-168
+        path = name if os.path.isfile(str(name)) else f"{STATE_DIR}/{name}.npz"
+        data = np.load(path)
+        dev = torch.device(device)
+        self._adopt(torch.from_numpy(data["R"]).to(dev), torch.from_numpy(data["X1"]).to(dev),
+                    torch.from_numpy(data["y1"]).to(dev), torch.from_numpy(data["E11"]).to(dev),
+                    torch.from_numpy(np.asarray(data["bias"])).double().to(dev))
+
+    # ---- posterior -------------------------------------------------------------------------------------
+    def pred(self, X2):
+        """gpis.py:43-59: X2 [M,3] or [B,F,3] -> (mean, std) shaped like X2 without the last dim."""
+        shape = list(X2.shape[:-1])
+        mean, std = _PredFn.apply(X2.reshape(-1, 3).double(), self)
+        return mean.view(shape), std.view(shape)
+
+    def pred_with_grads(self, X2):
+        """mean, std, d mean/dX2, d std/dX2 in one fused call (no autograd graph)."""
+        X = X2.detach().reshape(-1, 3).double().contiguous()
+        M = X.shape[0]
+        mean = torch.empty(M, dtype=torch.float64, device=X.device)
+        std = torch.empty_like(mean)
+        gm = torch.empty(M, 3, dtype=torch.float64, device=X.device)
+        gs = torch.empty_like(gm)
+        self._query(X, mean, gm, std, gs)
+        return mean, std, gm, gs
+
+    def compute_normal(self, X2, index=None):
+        """gpis.py:63-87: unit gradient of the posterior mean (detached); `index` = training-row subset."""
+        shape = X2.shape
+        X = X2.detach().reshape(-1, 3).double().contiguous()
+        g = torch.empty(X.shape[0], 3, dtype=torch.float64, device=X.device)
+        if index is None:
+            self._query(X, None, g, None, None)
+        else:
+            N = self.X1.shape[0]
+            alpha = torch.empty(N, dtype=torch.float64, device=X.device)
+            _lib.check(_lib.load().cdx_gpis_get(self._ctx, _lib.VEC_ALPHA, _ptr(alpha), _stream(self._device)))
+            idx = torch.as_tensor(index, device=X.device, dtype=torch.long)
+            w = torch.zeros_like(alpha)
+            w[idx] = alpha[idx]
+            _lib.check(_lib.load().cdx_gpis_query_weights(self._ctx, _ptr(w), _ptr(X), X.shape[0], None, _ptr(g),
+                                                          _stream(self._device)))
+            weight_sum = alpha[idx].sum()
+        n = g / (torch.norm(g, dim=1, keepdim=True) + 1e-8)
+        if index is None:
+            return n.view(shape)
+        return n.view(shape), weight_sum
+
+    def compute_multinormals(self, X2, num_normal_samples):
+        # gpis.py:89-111
+        if self.fraction is None:
+            self.fraction = torch.linspace(0.8, 1, num_normal_samples // 2)
+            self.indices = []
+            n = len(self.X1)
+            for i in range(num_normal_samples // 2):
+                self.indices.append(list(range(int(self.fraction[i] * n))))
+            self.indices.append(list(range(n)))
+            for i in range(num_normal_samples // 2):
+                self.indices.append(list(range(int(1 - self.fraction[-i - 1]), n)))
+        normals, weights = [], []
+        for i in range(num_normal_samples):
+            nrm, w = self.compute_normal(X2, self.indices[i])
+            normals.append(nrm)
+            weights.append(w)
+        weights = torch.hstack(weights)
+        return torch.stack(normals, dim=1), weights / weights.sum()
+
+    def get_visualization_data(self, lb, ub, steps=100):
+        """gpis.py:113-125: the grid driver; one fused query over all steps^3 points instead of `steps` slabs."""
+        dev = self.X1.device
+        grid = torch.stack(torch.meshgrid(torch.linspace(lb[0], ub[0], steps), torch.linspace(lb[1], ub[1], steps),
+                                          torch.linspace(lb[2], ub[2], steps), indexing="xy"), dim=3).double().to(dev)
+        X = grid.reshape(-1, 3).contiguous()
+        mean = torch.empty(X.shape[0], dtype=torch.float64, device=dev)
+        std = torch.empty_like(mean)
+        g = torch.empty(X.shape[0], 3, dtype=torch.float64, device=dev)
+        self._query(X, mean, g, std, None)
+        n = g / (torch.norm(g, dim=1, keepdim=True) + 1e-8)
+        return (mean.view(steps, steps, steps).float().cpu().numpy(), std.view(steps, steps, steps).float().cpu().numpy(),
+                n.view(steps, steps, steps, 3).float().cpu().numpy(), np.asarray(lb), np.asarray(ub))

@@ -1,0 +1,130 @@
+/* cdx - C ABI of the B200-native GPIS + pregrasp hot path (drop-in for ComplianceDex's gpis.py /
+ * optimize_pregrasp.py `prob` path).  The reference has NO FFI layer: its callers import plain Python classes
+ * (optimize_pregrasp.py:5 `from gpis import GPIS`, :842-848 `optimizers[...]`).  This header is therefore the
+ * boundary a maintainer binds with ctypes; each entry point cites the reference
+ * function(s) it replaces.
+ *
+ * Conventions
+ *  - every function returns 0 (CDX_OK) or a CDX_ERR_* code; cdx_last_error() gives the message (thread local).
+ *  - pointers named *_dev are DEVICE pointers owned by the caller (float64, contiguous, row-major); pointers
+ *    named *_host are host pointers and the call performs the H2D/D2H copies itself on `stream`.
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream). Calls are asynchronous on that
+ *    stream unless stated; no internal threads; one cdx_ctx per device.
+ *  - no CPU fallback exists: every compute entry point fails with CDX_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef CDX_H_
+#define CDX_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cdx_ctx cdx_ctx;
+
+enum { CDX_OK = 0, CDX_ERR_ARG = 1, CDX_ERR_CUDA = 2, CDX_ERR_NOT_SPD = 3, CDX_ERR_STATE = 4, CDX_ERR_ALLOC = 5 };
+enum { CDX_KERNEL_TPS = 0, CDX_KERNEL_RBF = 1, CDX_KERNEL_JOINT = 2 }; /* gpis.py:9-14 */
+enum { CDX_MAT_E11 = 0, CDX_MAT_CHOL = 1, CDX_MAT_CHOL_INV = 2, CDX_MAT_E11_INV = 3,
+       CDX_VEC_ALPHA = 4, CDX_VEC_Y1 = 5, CDX_MAT_X1 = 6 };
+
+const char* cdx_last_error(void);
+int cdx_version(void);
+
+/* one context per device; owns the factorised GPIS state and the pregrasp work buffers */
+int cdx_create(int device, cdx_ctx** out);
+int cdx_destroy(cdx_ctx* ctx);
+
+/* ------------------------------------------------------------------ GPIS ------------------------------- */
+/* GPIS.fit (gpis.py:33-40): R = max pairwise distance (tps/joint), y1 <- y1 - bias, E11 = k(X1,X1) + diag(noise^2);
+ * then - what the reference defers to every pred/compute_normal call (LU at gpis.py:53, inverse at :77) - the
+ * in-house blocked Cholesky E11 = L L^T, L^-1, E11^-1 and alpha = E11^-1 y1, once.
+ * X1_dev [N,3], y1_dev [N] (labels BEFORE bias subtraction), noise_dev [N] or NULL (then noise_scalar is used). */
+int cdx_gpis_fit(cdx_ctx* ctx, const double* X1_dev, const double* y1_dev, const double* noise_dev,
+                 double noise_scalar, int64_t N, double bias, int kernel, double sigma, void* stream);
+
+/* GPIS.load_state_data (gpis.py:162-168): adopt a stored state (y1 already bias-subtracted, E11 as stored) and
+ * factorise it. */
+int cdx_gpis_set_state(cdx_ctx* ctx, const double* X1_dev, const double* y1_dev, const double* E11_dev, double R,
+                       double bias, int64_t N, int kernel, double sigma, void* stream);
+
+/* state read-back for GPIS.save_state_data (gpis.py:155-160) and for tests. `which` = CDX_MAT_* / CDX_VEC_*;
+ * matrices are written dense [N,N] row-major (no padding). */
+int cdx_gpis_get(cdx_ctx* ctx, int which, double* out_dev, void* stream);
+/* synchronises `stream`; not_spd_col = -1 or the first failing pivot column of the Cholesky */
+int cdx_gpis_info(cdx_ctx* ctx, int64_t* N, double* R, double* bias, double* prior_var, int* not_spd_col,
+                  void* stream);
+
+/* GPIS.pred (gpis.py:43-59) + the gradients the optimizers obtain by autograd through it
+ * (optimize_pregrasp.py:733-736,758,763) + the un-normalised normal of GPIS.compute_normal (gpis.py:63-87):
+ *   mean[M] = k(x,X1) alpha + bias,  grad_mean[M,3],  std[M] = sqrt|k(x,x) - k*^T E11^-1 k*|,  grad_std[M,3].
+ * Any output may be NULL.  std alone uses the triangular factor (N^2 flop/query); grad_std uses E11^-1
+ * (2 N^2 flop/query). */
+int cdx_gpis_query(cdx_ctx* ctx, const double* X_dev, int64_t M, double* mean_dev, double* grad_mean_dev,
+                   double* std_dev, double* grad_std_dev, void* stream);
+/* same through HOST buffers (copies on `stream`, synchronises before returning) - the e2e path of bench.py */
+int cdx_gpis_query_host(cdx_ctx* ctx, const double* X_host, int64_t M, double* mean_host, double* grad_mean_host,
+                        double* std_host, double* grad_std_host, void* stream);
+/* mean / grad_mean with caller-supplied weights alpha_dev[N] (compute_normal's `index` subsets, gpis.py:69-80);
+ * the bias is NOT added (gpis.py:80 differentiates mu without bias) */
+int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha_dev, const double* X_dev, int64_t M, double* mean_dev,
+                           double* grad_mean_dev, void* stream);
+
+/* ------------------------------------------------------------------ hand model + pregrasp -------------- */
+/* Kinematic tree in URDF link order (robot_model.py:115-127, urdf_utils.py:28-83): body i has parent[i] < i
+ * (-1 for the root), dof[i] = column of q driving it or -1 (fixed), axis[i] in {0,1,2} with axis_sign[i] = +-1
+ * (rigid_body.py:149-154), fixed rpy/xyz (float32, as the reference stores them).  tips: 4 link ids + offsets
+ * (robot_model.py:255-263).  All HOST pointers. */
+int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, const int* dof, const int* axis,
+                  const float* axis_sign, const float* rpy, const float* xyz, int n_dofs, const int* tip_body,
+                  const float* tip_offset);
+
+/* ProbabilisticGraspOptimizer.forward_kinematics (optimize_pregrasp.py:657-669): q_dev [B,16] f64,
+ * palm_dev [B,6] f64 (xyz + XYZ Euler) -> tips_dev [B,4,3] f64 (FK evaluated in float32 like the reference). */
+int cdx_hand_fk(cdx_ctx* ctx, const double* q_dev, const double* palm_dev, int64_t B, double* tips_dev, void* stream);
+
+typedef struct cdx_pregrasp_params {
+  int32_t num_copies;            /* len(pregrasp_coefficients), optimize_pregrasp.py:623-625 (<= 4) */
+  float coeffs[4][4];            /* float32 as the reference stores them (:644) */
+  double weights[4];             /* pregrasp_weights as float32->float64 (:645) */
+  float ref_q[16];               /* float32 (:634) */
+  float box_lo[4][3], box_hi[4][3]; /* tip_bounding_box float32 (:643) */
+  double mass, com[3];           /* :629 */
+  int32_t gravity;               /* :629; gravity constant 10.0 at :726 */
+  double uncertainty;            /* :630 */
+  int32_t optimize_target, optimize_palm; /* :621,:631 */
+  double friction_mu;
+  int32_t friction_is_f32;       /* torch.tensor(int|float) -> float32 cos_mu (:111,:707) */
+  uint64_t noise_seed;           /* keyed stream replacing torch.rand_like at :61 (see oracle/noise.py) */
+  int64_t env_offset;            /* global index of candidate 0 (multi-GPU sharding) */
+  double lr[5];                  /* q, compliance, target, palm pos, palm ori (:782-796) */
+  double compliance_min;         /* 80.0 (:833) */
+  int32_t track_after;           /* best-iterate tracking for s > 20 (:823) */
+} cdx_pregrasp_params;
+
+/* ProbabilisticGraspOptimizer.optimize setup (optimize_pregrasp.py:771-804): copies the initial iterate, zeroes
+ * Adam moments and the best-iterate buffers. q0 [B,16], compliance0 [B,4], target0 [B,4,3], palm0 [B,6]. */
+int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int64_t B, const double* q0_dev,
+                      const double* compliance0_dev, const double* target0_dev, const double* palm0_dev, void* stream);
+/* n_iters iterations of closure + best-tracking + Adam + clamps (optimize_pregrasp.py:805-834), no host sync */
+int cdx_pregrasp_run(cdx_ctx* ctx, int n_iters, void* stream);
+/* objective and its gradient at the CURRENT iterate without stepping (closure, :741-769) - for parity tests.
+ * total_loss [B], margin [B,4], grads: q [B,16], compliance [B,4], target [B,4,3], palm [B,6]; any may be NULL */
+int cdx_pregrasp_eval(cdx_ctx* ctx, double* total_loss_dev, double* margin_dev, double* gq_dev, double* gc_dev,
+                      double* gt_dev, double* gp_dev, void* stream);
+/* the reference's 5-tuple (:839) + opt_value (:802); any may be NULL */
+int cdx_pregrasp_results(cdx_ctx* ctx, double* opt_q_dev, double* opt_compliance_dev, double* opt_target_dev,
+                         double* opt_palm_dev, double* opt_margin_dev, double* opt_value_dev, void* stream);
+/* current iterate (for tests) */
+int cdx_pregrasp_state(cdx_ctx* ctx, double* q_dev, double* compliance_dev, double* target_dev, double* palm_dev,
+                       void* stream);
+/* local arg-min over opt_value with lowest-index tie-break: out_dev[0] = value, out_dev[1] = (double) GLOBAL index
+ * (env_offset + local).  The cross-rank step is an all-gather of these 16 bytes. */
+int cdx_pregrasp_argmin(cdx_ctx* ctx, double* out_dev, void* stream);
+
+/* how many cdx kernels this context has launched since creation (bench.py's gpu_launches) */
+int64_t cdx_launch_count(cdx_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CDX_H_ */

@@ -1,0 +1,176 @@
+"""GPU parity: CUDA GPIS path (through the C ABI / drop-in class) vs the oracle and the reference-generated
+golden vectors.  Gates (BASELINE.json): mean, grad_mean <= 1e-5 rel; std^2 within 1e-6 * prior (R^3) abs."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NAMES = ["mug", "mug2", "coffeebottle", "lego", "hammer", "banana", "dummy"]
+
+
+def _gpis(name):
+    from compliancedex_b200 import GPIS, state_path
+    g = GPIS(0.08, 1.0)
+    g.load_state_data(state_path(f"{name}_state"))
+    return g
+
+
+def _check(got_mean, got_std, got_gm, got_gs, ref, prior):
+    gm_scale = np.abs(ref["grad_mean"]).max()
+    assert np.abs(got_mean - ref["mean"]).max() <= 1e-5 * np.abs(ref["mean"]).max()
+    rel_pt = np.abs(got_mean - ref["mean"]) / np.maximum(np.abs(ref["mean"]), 1e-3)
+    assert rel_pt.max() <= 1e-5
+    assert np.abs(got_gm - ref["grad_mean"]).max() <= 1e-5 * gm_scale
+    assert np.abs(got_std ** 2 - ref["std"] ** 2).max() <= 1e-6 * prior
+    if got_gs is not None:
+        assert np.abs(got_gs - ref["grad_std"]).max() <= 1e-5 * np.abs(ref["grad_std"]).max()
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_shipped_states_against_reference_golden(name, golden_dir):
+    ref = np.load(os.path.join(golden_dir, f"gpis_{name}.npz"))
+    g = _gpis(name)
+    X = torch.from_numpy(ref["X"]).cuda()
+    prior = float(g.R) ** 3
+    mean, std, gm, gs = g.pred_with_grads(X)                                  # extended kernel (E11^-1)
+    _check(mean.cpu().numpy(), std.cpu().numpy(), gm.cpu().numpy(), gs.cpu().numpy(), ref, prior)
+    with torch.no_grad():
+        m2, s2 = g.pred(X)                                                    # unit kernel (L^-1)
+    _check(m2.cpu().numpy(), s2.cpu().numpy(), gm.cpu().numpy(), None, ref, prior)
+    n = g.compute_normal(X)                                                   # mean-only kernel (TMA-staged)
+    assert np.abs(n.cpu().numpy() - ref["normal"]).max() <= 1e-5
+    # autograd through pred, as the optimizers use it
+    Xr = X.clone().requires_grad_(True)
+    m3, s3 = g.pred(Xr)
+    (m3.sum() * 2.0 + s3.sum() * 3.0).backward()
+    want = 2.0 * ref["grad_mean"] + 3.0 * ref["grad_std"]
+    assert np.abs(Xr.grad.cpu().numpy() - want).max() <= 1e-5 * np.abs(want).max()
+
+
+def test_batched_shape_rule(golden_dir):
+    ref = np.load(os.path.join(golden_dir, "gpis_batched_lego.npz"))
+    g = _gpis("lego")
+    X = torch.from_numpy(ref["X"]).cuda()
+    m, s = g.pred(X)
+    assert tuple(m.shape) == (5, 4) and tuple(s.shape) == (5, 4) and m.dtype == torch.float64
+    assert np.abs(m.cpu().numpy() - ref["mean"]).max() < 1e-6 and np.abs(s.cpu().numpy() - ref["std"]).max() < 1e-6
+    n = g.compute_normal(X)
+    assert tuple(n.shape) == (5, 4, 3) and np.abs(n.cpu().numpy() - ref["normal"]).max() < 1e-5
+
+
+@pytest.mark.parametrize("kern", ["tps", "rbf", "joint"])
+def test_fit_against_reference_golden(kern, golden_dir):
+    from compliancedex_b200 import GPIS
+    ref = np.load(os.path.join(golden_dir, "gpis_fit_synth211.npz"))
+    g = GPIS(0.08, 1.0, kernel=kern)
+    g.fit(torch.from_numpy(ref["X1"]).cuda(), torch.from_numpy(ref["y1"]).cuda(), torch.from_numpy(ref["noise"]).cuda())
+    E = g.E11.cpu().numpy()
+    assert np.abs(E - ref[f"{kern}_E11"]).max() <= 1e-12 * np.abs(ref[f"{kern}_E11"]).max()
+    if kern != "rbf":
+        assert abs(float(g.R) - float(ref[f"{kern}_R"])) <= 1e-14
+    assert np.abs(g.y1.cpu().numpy() - ref[f"{kern}_y1"]).max() == 0.0
+    prior = {"tps": float(ref["tps_R"]) ** 3, "rbf": 1.0, "joint": 0.3 + 0.7 * float(ref["tps_R"]) ** 3}[kern]
+    with torch.no_grad():
+        m, s = g.pred(torch.from_numpy(ref["Xq"]).cuda())
+    assert np.abs(m.cpu().numpy() - ref[f"{kern}_mean"]).max() <= 1e-5 * np.abs(ref[f"{kern}_mean"]).max()
+    assert np.abs(s.cpu().numpy() ** 2 - ref[f"{kern}_std"] ** 2).max() <= 1e-6 * prior
+    n = g.compute_normal(torch.from_numpy(ref["Xq"]).cuda())
+    assert np.abs(n.cpu().numpy() - ref[f"{kern}_normal"]).max() <= 1e-5
+
+
+def test_factorisation_identities():
+    """L L^T = E11, U L = I, P E11 = I on a shipped state (padding must not leak)."""
+    from compliancedex_b200 import _lib
+    g = _gpis("hammer")
+    N = g.X1.shape[0]
+    lib = _lib.load()
+    mats = {}
+    for nm, which in [("L", _lib.MAT_CHOL), ("U", _lib.MAT_CHOL_INV), ("P", _lib.MAT_E11_INV), ("E", _lib.MAT_E11)]:
+        t = torch.empty(N, N, dtype=torch.float64, device="cuda")
+        _lib.check(lib.cdx_gpis_get(g._ctx, which, ctypes.c_void_p(t.data_ptr()), None))
+        mats[nm] = t
+    torch.cuda.synchronize()
+    E, L, U, P = mats["E"], mats["L"], mats["U"], mats["P"]
+    assert torch.equal(E, g.E11)
+    assert (L @ L.T - E).abs().max() <= 1e-13 * E.abs().max()
+    assert torch.triu(L, 1).abs().max() == 0 and torch.triu(U, 1).abs().max() == 0
+    I = torch.eye(N, dtype=torch.float64, device="cuda")
+    assert (U @ L - I).abs().max() <= 1e-9
+    assert (P @ E - I).abs().max() <= 1e-6
+    assert (P - P.T).abs().max() == 0
+
+
+def test_synthetic_large_state_vs_oracle():
+    """N=1024 synthetic fit (SURVEY 8d generator): CUDA fit+query vs the oracle restatement on 512 points; exercises
+    the 128-wide tile path and the multi-level triangular inverse."""
+    from compliancedex_b200 import GPIS
+    from oracle.gpis_oracle import GPISOracle, synthetic_training_set
+    X1, y1, noise = synthetic_training_set(1024, seed=0)
+    o = GPISOracle(0.08, 1.0).fit(X1, y1, noise)
+    g = GPIS(0.08, 1.0)
+    g.fit(X1.cuda(), y1.cuda(), noise.cuda())
+    X = (torch.rand(512, 3, generator=torch.Generator().manual_seed(4), dtype=torch.float64) * 2 - 1) * 0.1
+    m_ref, s_ref = o.pred_diag(X)
+    gm_ref, gs_ref = o.grads(X)
+    mean, std, gm, gs = g.pred_with_grads(X.cuda())
+    prior = float(o.R) ** 3
+    assert (mean.cpu() - m_ref).abs().max() <= 1e-5 * m_ref.abs().max()
+    assert (gm.cpu() - gm_ref).abs().max() <= 1e-5 * gm_ref.abs().max()
+    assert (std.cpu() ** 2 - s_ref ** 2).abs().max() <= 1e-6 * prior
+    assert (gs.cpu() - gs_ref).abs().max() <= 1e-4 * gs_ref.abs().max()
+    with torch.no_grad():
+        m2, s2 = g.pred(X.cuda())
+    assert (m2.cpu() - m_ref).abs().max() <= 1e-5 * m_ref.abs().max()
+    assert (s2.cpu() ** 2 - s_ref ** 2).abs().max() <= 1e-6 * prior
+
+
+def test_edge_cases():
+    g = _gpis("mug")
+    # empty query
+    m, s = g.pred(torch.zeros(0, 3, dtype=torch.float64, device="cuda"))
+    assert m.numel() == 0 and s.numel() == 0
+    # ragged sizes around the 128-query tile, query exactly on training points, host-buffer entry point
+    from compliancedex_b200 import _lib
+    lib = _lib.load()
+    for M in [1, 127, 128, 129, 300]:
+        X = torch.vstack([g.X1[:min(M, 50)], (torch.rand(max(M - 50, 0), 3, dtype=torch.float64, device="cuda") - 0.5) * 0.2])[:M]
+        mean, std, gm, gs = g.pred_with_grads(X)
+        assert torch.isfinite(mean).all() and torch.isfinite(std).all() and torch.isfinite(gm).all()
+        Xh = X.cpu().contiguous()
+        mh = torch.empty(M, dtype=torch.float64)
+        sh = torch.empty(M, dtype=torch.float64)
+        gh = torch.empty(M, 3, dtype=torch.float64)
+        _lib.check(lib.cdx_gpis_query_host(g._ctx, Xh.data_ptr(), M, mh.data_ptr(), gh.data_ptr(), sh.data_ptr(), None, None))
+        with torch.no_grad():
+            m2, s2 = g.pred(X)
+        assert torch.equal(mh, m2.cpu()) and torch.equal(sh, s2.cpu())
+        assert (mean.cpu() - mh).abs().max() < 1e-9
+    # non-SPD matrix raises like torch.linalg would
+    from compliancedex_b200 import GPIS
+    bad = GPIS(0.08, 1.0)
+    with pytest.raises(torch.linalg.LinAlgError):
+        bad._adopt(g.R, g.X1, g.y1, -g.E11, g.bias)
+
+
+def test_full_size_properties():
+    """Size-independent properties at the bench size (N=4096 synthetic, 2^18 queries): chunking invariance and
+    std^2 <= prior, std -> noise level on training points."""
+    from compliancedex_b200 import GPIS
+    from oracle.gpis_oracle import synthetic_training_set
+    X1, y1, noise = synthetic_training_set(4096, seed=0)
+    g = GPIS(0.08, 1.0)
+    g.fit(X1.cuda(), y1.cuda(), noise.cuda())
+    X = (torch.rand(1 << 18, 3, generator=torch.Generator().manual_seed(1), dtype=torch.float64) * 2 - 1) * 0.1
+    X = X.cuda()
+    with torch.no_grad():
+        m, s = g.pred(X)
+        m1, s1 = g.pred(X[1000:5000])
+    assert torch.equal(m[1000:5000], m1) and torch.equal(s[1000:5000], s1)
+    assert torch.isfinite(m).all() and (s ** 2 <= float(g.R) ** 3 * (1 + 1e-9)).all()
+    n = g.compute_normal(X[:4096])
+    assert (n.norm(dim=1) - 1).abs().max() < 1e-6
