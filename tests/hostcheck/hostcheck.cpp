@@ -26,10 +26,12 @@ void hc_svd3(const double* A, double* U, double* S, double* V) { cdx_svd3(A, U, 
 void hc_closure(const cdx_pg_setup* P, const cdx_hand_dev* hand, const double* q, const double* k, const double* T,
                 const double* palm, const double* dist, const double* sd, const double* gmu, const double* gsd,
                 const double* mean9, const double* gmean9, uint64_t seed, int it, int64_t b, double* total,
-                double* tmargin, double* gq, double* gk, double* gT, double* gpalm) {
+                double* tmargin, double* gq, double* gk, double* gT, double* gpalm, const double* tl_override) {
   double tl[4][3];
   float J[4][3][CDX_MAX_CHAIN_DOF];
   hc_fk(hand, q, &tl[0][0], &J[0][0][0]);
+  if (tl_override)   // isolate the objective's derivation from float32 FK rounding
+    for (int e = 0; e < 12; e++) (&tl[0][0])[e] = tl_override[e];
   cdx_pg_gpis G = {dist, sd, gmu, gsd, mean9, gmean9};
   auto nf = [=](int p, int e) { return cdx_kabsch_noise(seed, it, p, b, e); };
   cdx_pg_closure(*P, *hand, q, k, reinterpret_cast<const double (*)[3]>(T), palm, tl, J, G, nf, *total, tmargin, gq,
