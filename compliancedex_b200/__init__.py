@@ -23,7 +23,6 @@ def hand_path(hand):
     return os.path.join(DATA_DIR, "hands", f"{hand}.json")
 
 
-try:
-    from .pregrasp import ProbabilisticGraspOptimizer, optimizers, load_hand, EE_OFFSETS, WRIST_OFFSET, FINGERTIP_LB, FINGERTIP_UB
-except ImportError:  # pragma: no cover - only while the module is being built
-    pass
+from .hand import load_hand
+from .pregrasp import (ProbabilisticGraspOptimizer, optimizers, EE_OFFSETS, WRIST_OFFSET, FINGERTIP_LB,
+                       FINGERTIP_UB)

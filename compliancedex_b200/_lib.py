@@ -14,21 +14,24 @@ class PregraspParams(ctypes.Structure):
     _fields_ = [
         ("num_copies", ctypes.c_int32),
         ("coeffs", (ctypes.c_float * 4) * 4),
-        ("weights", c_double * 4),
+        ("weights", ctypes.c_float * 4),
         ("ref_q", ctypes.c_float * 16),
         ("box_lo", (ctypes.c_float * 3) * 4),
         ("box_hi", (ctypes.c_float * 3) * 4),
-        ("mass", c_double),
-        ("com", c_double * 3),
+        ("com", ctypes.c_float * 3),
+        ("dummy_k", ctypes.c_float),
+        ("dummy_M", ctypes.c_float),
         ("gravity", ctypes.c_int32),
         ("uncertainty", c_double),
         ("optimize_target", ctypes.c_int32),
         ("optimize_palm", ctypes.c_int32),
-        ("friction_mu", c_double),
-        ("friction_is_f32", ctypes.c_int32),
+        ("cos_mu", ctypes.c_float),
         ("noise_seed", c_u64),
         ("env_offset", c_i64),
         ("lr", c_double * 5),
+        ("beta1", c_double),
+        ("beta2", c_double),
+        ("eps", c_double),
         ("compliance_min", c_double),
         ("track_after", ctypes.c_int32),
     ]

@@ -1,0 +1,217 @@
+"""Drop-in `ProbabilisticGraspOptimizer` (reference: optimize_pregrasp.py:614-839) backed by libcdx.so.
+
+Same constructor keywords, `.forward_kinematics(...)`, `.optimize(...)` signature and 5-tuple return as the reference
+class.  The whole optimisation loop (float32 FK, GPIS queries, Kabsch equilibrium, cost terms, analytic gradient,
+Adam, clamps, best-iterate tracking) runs in sm_100a kernels behind the C ABI of include/cdx.h with no host sync per
+iteration.  Differences a caller can observe, all deliberate:
+  * the per-iteration cost print (:738) and the final `print("Margin:")` (:838) only happen with verbose=True and
+    never force a sync inside the loop;
+  * the `1e-6 * torch.rand_like(H)` perturbation (:61) comes from a keyed stream (seed, iteration, copy, GLOBAL
+    candidate index) so results do not depend on batch size or on how candidates are sharded over GPUs;
+  * `opt_value` (best loss per candidate, :802) is kept as `self.opt_value`, and `argmin()` returns its arg-min.
+There is no CPU path.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from .hand import load_hand, tree_for
+
+# optimize_pregrasp.py:13-30
+EE_OFFSETS = [[0.0, -0.04, 0.015], [0.0, -0.04, 0.015], [0.0, -0.04, 0.015], [0.0, -0.05, -0.015]]
+WRIST_OFFSET = np.array([[-0.06, 0.0, 0.05, 0.0, 0.0, 0.0],
+                         [-0.04, 0.03, 0.05, 0.0, 0.0, -np.pi / 4],
+                         [-0.01, 0.0, 0.05, 0.0, 0.0, np.pi / 4],
+                         [0.1, 0.06, 0.03, -np.pi / 2, np.pi / 2, 0.0],
+                         [-0.0, -0.06, 0.05, 0.0, 0.0, np.pi / 2],
+                         [0.02, -0.04, 0.05, 0.0, 0.0, 3 * np.pi / 4]])
+z_margin = 0.2
+FINGERTIP_LB = [-0.2, -0.2, 0.015] * 4
+FINGERTIP_UB = [0.2, 0.2, z_margin] * 4
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _np_ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class ProbabilisticGraspOptimizer:
+    def __init__(self, robot_urdf, ee_link_names, ee_link_offsets=EE_OFFSETS, palm_offset=WRIST_OFFSET, num_iters=1000,
+                 optimize_target=False, ref_q=None, tip_bounding_box=[FINGERTIP_LB, FINGERTIP_UB],
+                 pregrasp_coefficients=[[0.8, 0.8, 0.8, 0.8], [0.8, 0.8, 0.8, 0.8], [0.8, 0.8, 0.8, 0.8]],
+                 pregrasp_weights=[0.1, 0.8, 0.1], anchor_link_names=None, anchor_link_offsets=None, collision_pairs=None,
+                 collision_pair_threshold=0.02, mass=0.1, com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0,
+                 optimize_palm=False, device="cuda", noise_seed=0, env_offset=0):
+        """robot_urdf: URDF path (as the reference), or 'leap' / 'allegro' / a hand JSON of data/hands."""
+        self.device = torch.device(device)
+        self.tree = tree_for(robot_urdf, ee_link_names, ee_link_offsets)
+        self.ref_q = torch.tensor(ref_q)                                         # float32 (:634)
+        self.num_iters = num_iters
+        self.ee_link_names = ee_link_names
+        self.ee_link_offsets = ee_link_offsets
+        self.palm_offset = torch.from_numpy(np.asarray(palm_offset)).double()   # [B,6] (:640)
+        self.optimize_target = optimize_target
+        self.optimize_palm = optimize_palm
+        self.tip_bounding_box = [torch.tensor(tip_bounding_box[0]).view(-1, 3), torch.tensor(tip_bounding_box[1]).view(-1, 3)]
+        self.pregrasp_coefficients = torch.tensor(pregrasp_coefficients)        # float32 (:644)
+        self.pregrasp_weights = torch.tensor(pregrasp_weights).double()         # float32 values widened (:645)
+        self.anchor_link_names = anchor_link_names
+        self.anchor_link_offsets = anchor_link_offsets
+        self.collision_pairs = collision_pairs
+        self.collision_pair_threshold = collision_pair_threshold
+        self.mass, self.com, self.gravity, self.uncertainty = mass, com, gravity, uncertainty
+        self.noise_seed, self.env_offset = int(noise_seed), int(env_offset)
+        self.opt_value = None
+        self._ctx = None
+        self._hand_loaded_for = None
+
+    # ---- plumbing --------------------------------------------------------------------------------------
+    def _dev_index(self):
+        if self.device.type != "cuda":
+            raise RuntimeError("compliancedex_b200.ProbabilisticGraspOptimizer runs on CUDA only (no CPU fallback)")
+        return self.device.index if self.device.index is not None else torch.cuda.current_device()
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self._dev_index()).cuda_stream)
+
+    def _bind(self, ctx):
+        """use `ctx` (the GPIS object's context, which owns the fitted state) and load the hand into it once"""
+        self._ctx = ctx
+        if self._hand_loaded_for != ctx.value:
+            t = self.tree
+            _lib.check(_lib.load().cdx_hand_load(ctx, t.n_bodies, _np_ptr(t.parent), _np_ptr(t.dof), _np_ptr(t.axis),
+                                                 _np_ptr(t.sign), _np_ptr(t.rot), _np_ptr(t.xyz), t.n_dofs,
+                                                 _np_ptr(t.tip_body), _np_ptr(t.tip_offset)))
+            self._hand_loaded_for = ctx.value
+
+    def _own_ctx(self):
+        if self._ctx is None:
+            self._bind(_lib.new_context(self._dev_index()))
+        return self._ctx
+
+    def _params(self, friction_mu):
+        p = _lib.PregraspParams()
+        coeffs = self.pregrasp_coefficients.numpy()
+        P = coeffs.shape[0]
+        if P > 4 or coeffs.shape[1] != 4:
+            raise ValueError("pregrasp_coefficients must be [P<=4, 4]")
+        p.num_copies = P
+        w32 = self.pregrasp_weights.float().numpy()
+        for a in range(P):
+            for f in range(4):
+                p.coeffs[a][f] = float(coeffs[a, f])
+            p.weights[a] = float(w32[a])
+        for i in range(self.tree.n_dofs):
+            p.ref_q[i] = float(self.ref_q[i])
+        lo, hi = self.tip_bounding_box[0].numpy(), self.tip_bounding_box[1].numpy()
+        for f in range(4):
+            for r in range(3):
+                p.box_lo[f][r] = float(lo[f, r])
+                p.box_hi[f][r] = float(hi[f, r])
+        com32 = torch.zeros(3)                                                   # dummy_tip is float32 (:90-92)
+        com32[:] = torch.tensor(self.com).double()
+        for r in range(3):
+            p.com[r] = float(com32[r])
+        M = 2.0
+        p.dummy_k = float((10.0 * self.mass / M * torch.ones(1))[0])             # gravity=10.0 (:726), float32 (:94)
+        p.dummy_M = M
+        p.gravity = 1 if self.gravity else 0
+        p.uncertainty = float(self.uncertainty)
+        p.optimize_target = int(bool(self.optimize_target))
+        p.optimize_palm = int(bool(self.optimize_palm))
+        p.cos_mu = float(torch.sqrt(1 / (1 + torch.tensor(friction_mu) ** 2)))   # exactly :111 / :707 (float32)
+        p.noise_seed = self.noise_seed
+        p.env_offset = self.env_offset
+        for i, lr in enumerate([1e-3, 0.2, 2e-3, 1e-4, 1e-4]):                   # :782-796
+            p.lr[i] = lr
+        p.beta1, p.beta2, p.eps = 0.9, 0.999, 1e-8
+        p.compliance_min = 80.0                                                  # :833
+        p.track_after = 20                                                       # :823
+        return p
+
+    # ---- reference API ---------------------------------------------------------------------------------
+    def forward_kinematics(self, joint_angles, palm_poses=None):
+        """optimize_pregrasp.py:657-669: [B,n_dofs] (+ [B,6] palm poses) -> fingertip positions [B,4,3] float64."""
+        if palm_poses is None:
+            palm_poses = self.palm_offset
+        ctx = self._own_ctx()
+        dev = self.device
+        q = joint_angles.detach().double().to(dev).contiguous()
+        palm = palm_poses.detach().double().to(dev).contiguous()
+        B = q.shape[0]
+        tips = torch.empty(B, 4, 3, dtype=torch.float64, device=dev)
+        _lib.check(_lib.load().cdx_hand_fk(ctx, _ptr(q), _ptr(palm), B, _ptr(tips), self._stream()))
+        return tips
+
+    def _init(self, init_joint_angles, target_pose, compliance, friction_mu, gpis):
+        if getattr(gpis, "_ctx", None) is None:
+            raise RuntimeError("gpis must be a fitted compliancedex_b200.GPIS (fit() or load_state_data() first)")
+        self.device = torch.device("cuda", gpis._device)
+        self._bind(gpis._ctx)
+        dev = self.device
+        q0 = init_joint_angles.detach().double().to(dev).contiguous()
+        k0 = compliance.detach().double().to(dev).contiguous()
+        T0 = target_pose.detach().double().to(dev).contiguous()
+        palm0 = self.palm_offset.to(dev).contiguous()
+        B = q0.shape[0]
+        if palm0.shape[0] != B or k0.shape != (B, 4) or T0.shape != (B, 4, 3) or q0.shape[1] != self.tree.n_dofs:
+            raise ValueError("shapes: joint_angles [B,n_dofs], target_pose [B,4,3], compliance [B,4], palm_offset [B,6]")
+        p = self._params(friction_mu)
+        _lib.check(_lib.load().cdx_pregrasp_init(self._ctx, ctypes.byref(p), B, _ptr(q0), _ptr(k0), _ptr(T0), _ptr(palm0),
+                                                 self._stream()))
+        self._B = B
+        return B
+
+    def evaluate(self):
+        """closure() at the current iterate without stepping: total_loss [B], margin [B,4] and the gradients
+        autograd leaves in q / compliance / target / palm (.grad after total_loss.sum().backward(), :767-768)."""
+        B, dev, nd = self._B, self.device, self.tree.n_dofs
+        out = [torch.empty(s, dtype=torch.float64, device=dev) for s in ((B,), (B, 4), (B, nd), (B, 4), (B, 4, 3), (B, 6))]
+        _lib.check(_lib.load().cdx_pregrasp_eval(self._ctx, *[_ptr(t) for t in out], self._stream()))
+        return out
+
+    def step(self, n_iters):
+        _lib.check(_lib.load().cdx_pregrasp_run(self._ctx, int(n_iters), self._stream()))
+
+    def current(self):
+        B, dev, nd = self._B, self.device, self.tree.n_dofs
+        out = [torch.empty(s, dtype=torch.float64, device=dev) for s in ((B, nd), (B, 4), (B, 4, 3), (B, 6))]
+        _lib.check(_lib.load().cdx_pregrasp_state(self._ctx, *[_ptr(t) for t in out], self._stream()))
+        return out
+
+    def results(self):
+        B, dev, nd = self._B, self.device, self.tree.n_dofs
+        out = [torch.empty(s, dtype=torch.float64, device=dev) for s in ((B, nd), (B, 4), (B, 4, 3), (B, 6), (B, 4), (B,))]
+        _lib.check(_lib.load().cdx_pregrasp_results(self._ctx, *[_ptr(t) for t in out], self._stream()))
+        return out
+
+    def optimize(self, init_joint_angles, target_pose, compliance, friction_mu, gpis, verbose=True):
+        """optimize_pregrasp.py:771-839 -> (opt_joint_angle [B,n_dofs], opt_compliance [B,4], opt_target_pose [B,4,3],
+        opt_palm_poses [B,6], opt_margin [B,4])."""
+        self._init(init_joint_angles, target_pose, compliance, friction_mu, gpis)
+        self.step(self.num_iters)
+        oq, ok, oT, opalm, omargin, ovalue = self.results()
+        self.opt_value = ovalue
+        if verbose:
+            print("Margin:", omargin)
+        return oq, ok, oT, opalm, omargin
+
+    def argmin(self):
+        """(best opt_value, GLOBAL candidate index = env_offset + local index), lowest index on ties; the cross-rank
+        reduction of these pairs is compliancedex_b200.distributed.global_argmin."""
+        out = torch.empty(2, dtype=torch.float64, device=self.device)
+        _lib.check(_lib.load().cdx_pregrasp_argmin(self._ctx, _ptr(out), self._stream()))
+        v, i = out.tolist()
+        return v, int(i)
+
+    def compute_collision_loss(self, joint_angles, palm_poses=None):
+        # optimize_pregrasp.py:671-701 is dead code on this path (its call at :765 is commented out)
+        raise NotImplementedError("compute_collision_loss is not on the prob path (call commented out at optimize_pregrasp.py:765)")
+
+
+optimizers = {"prob": ProbabilisticGraspOptimizer}   # optimize_pregrasp.py:842-848; other modes are out of scope

@@ -72,31 +72,34 @@ int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha_dev, const double* 
 /* ------------------------------------------------------------------ hand model + pregrasp -------------- */
 /* Kinematic tree in URDF link order (robot_model.py:115-127, urdf_utils.py:28-83): body i has parent[i] < i
  * (-1 for the root), dof[i] = column of q driving it or -1 (fixed), axis[i] in {0,1,2} with axis_sign[i] = +-1
- * (rigid_body.py:149-154), fixed rpy/xyz (float32, as the reference stores them).  tips: 4 link ids + offsets
- * (robot_model.py:255-263).  All HOST pointers. */
+ * (rigid_body.py:149-154), fixed_rot[i] = (Rz(yaw) Ry(pitch)) Rx(roll) of the joint origin as the float32 3x3 the
+ * reference builds (rigid_body.py:142), xyz[i] float32.  tips: 4 link ids + offsets (robot_model.py:255-263).
+ * All HOST pointers. */
 int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, const int* dof, const int* axis,
-                  const float* axis_sign, const float* rpy, const float* xyz, int n_dofs, const int* tip_body,
+                  const float* axis_sign, const float* fixed_rot, const float* xyz, int n_dofs, const int* tip_body,
                   const float* tip_offset);
 
-/* ProbabilisticGraspOptimizer.forward_kinematics (optimize_pregrasp.py:657-669): q_dev [B,16] f64,
+/* ProbabilisticGraspOptimizer.forward_kinematics (optimize_pregrasp.py:657-669): q_dev [B,n_dofs] f64,
  * palm_dev [B,6] f64 (xyz + XYZ Euler) -> tips_dev [B,4,3] f64 (FK evaluated in float32 like the reference). */
 int cdx_hand_fk(cdx_ctx* ctx, const double* q_dev, const double* palm_dev, int64_t B, double* tips_dev, void* stream);
 
 typedef struct cdx_pregrasp_params {
   int32_t num_copies;            /* len(pregrasp_coefficients), optimize_pregrasp.py:623-625 (<= 4) */
   float coeffs[4][4];            /* float32 as the reference stores them (:644) */
-  double weights[4];             /* pregrasp_weights as float32->float64 (:645) */
+  float weights[4];              /* pregrasp_weights: float32 values, widened by .double() (:645) */
   float ref_q[16];               /* float32 (:634) */
   float box_lo[4][3], box_hi[4][3]; /* tip_bounding_box float32 (:643) */
-  double mass, com[3];           /* :629 */
-  int32_t gravity;               /* :629; gravity constant 10.0 at :726 */
+  float com[3];                  /* COM as it lands in the float32 dummy_tip (:90-92) */
+  float dummy_k;                 /* float32(gravity_const * mass / M), gravity_const = 10.0 (:94,:726) */
+  float dummy_M;                 /* M = 2.0 (:73) */
+  int32_t gravity;               /* 0: no dummy gravity finger (:98-99) */
   double uncertainty;            /* :630 */
   int32_t optimize_target, optimize_palm; /* :621,:631 */
-  double friction_mu;
-  int32_t friction_is_f32;       /* torch.tensor(int|float) -> float32 cos_mu (:111,:707) */
-  uint64_t noise_seed;           /* keyed stream replacing torch.rand_like at :61 (see oracle/noise.py) */
+  float cos_mu;                  /* torch.sqrt(1/(1+torch.tensor(friction_mu)**2)): float32 (:111,:707) */
+  uint64_t noise_seed;           /* keyed stream replacing torch.rand_like at :61 (cdx_noise.cuh) */
   int64_t env_offset;            /* global index of candidate 0 (multi-GPU sharding) */
   double lr[5];                  /* q, compliance, target, palm pos, palm ori (:782-796) */
+  double beta1, beta2, eps;      /* torch.optim.Adam defaults 0.9, 0.999, 1e-8 (:796) */
   double compliance_min;         /* 80.0 (:833) */
   int32_t track_after;           /* best-iterate tracking for s > 20 (:823) */
 } cdx_pregrasp_params;

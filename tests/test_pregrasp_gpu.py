@@ -1,0 +1,143 @@
+"""GPU parity: fused pregrasp path (C ABI / drop-in ProbabilisticGraspOptimizer) vs the reference-generated golden
+vectors (tests/golden/pregrasp_*.npz, made by oracle/make_golden.py from the reference's own classes) and vs the
+oracle at other sizes.  Gates (BASELINE.json): objective <= 1e-4 rel per candidate, identical arg-min index."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CASES = [("leap_mug", "leap", "mug"), ("allegro_hammer", "allegro", "hammer"),
+         ("allegro_coffeebottle", "allegro", "coffeebottle")]
+
+
+def _setup(tag, hand, state, golden_dir, num_iters=None, B=None):
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path, FINGERTIP_LB, FINGERTIP_UB
+    g = np.load(os.path.join(golden_dir, f"pregrasp_{tag}.npz"))
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path(f"{state}_state"))
+    doc = load_hand(hand)
+    sl = slice(0, B)
+    opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                      palm_offset=g["palm0"][sl], num_iters=int(g["iters"]) if num_iters is None else num_iters,
+                                      optimize_target=True, ref_q=doc["ref_q"], tip_bounding_box=[FINGERTIP_LB, FINGERTIP_UB],
+                                      mass=float(g["mass"]), com=g["com"].tolist(), gravity=True, uncertainty=20.0,
+                                      optimize_palm=True, noise_seed=int(g["noise_seed"]))
+    q0, T0, k0 = (torch.from_numpy(g[k][sl]).cuda() for k in ("q0", "target0", "compliance0"))
+    return g, gp, opt, q0, T0, k0, g["friction_mu"].item()
+
+
+@pytest.mark.parametrize("tag,hand,state", CASES)
+def test_forward_kinematics(tag, hand, state, golden_dir):
+    g, gp, opt, q0, T0, k0, mu = _setup(tag, hand, state, golden_dir)
+    tips = opt.forward_kinematics(q0, torch.from_numpy(g["palm0"]).cuda())
+    assert tips.dtype == torch.float64 and tuple(tips.shape) == (q0.shape[0], 4, 3)
+    assert np.abs(tips.cpu().numpy() - g["tips0"]).max() < 5e-7          # float32 FK, different op order
+
+
+@pytest.mark.parametrize("tag,hand,state", CASES)
+def test_first_three_closures_match_reference(tag, hand, state, golden_dir):
+    """total_loss and every leaf gradient of iterations 0..2 against the reference's autograd."""
+    g, gp, opt, q0, T0, k0, mu = _setup(tag, hand, state, golden_dir)
+    opt._init(q0, T0, k0, mu, gp)
+    for it in range(3):
+        loss, margin, gq, gk, gT, gp6 = [t.cpu().numpy() for t in opt.evaluate()]
+        ref = g["losses"][it]
+        assert np.array_equal(np.isnan(loss), np.isnan(ref))
+        ok = ~np.isnan(ref)
+        assert (np.abs(loss[ok] - ref[ok]) <= 1e-4 * np.abs(ref[ok])).all(), (it, loss, ref)
+        for got, nm, tol in [(gq, "q", 2e-4), (gk, "compliance", 2e-5), (gT, "target", 2e-5), (gp6[:, :3], "palm_pos", 2e-5),
+                             (gp6[:, 3:], "palm_ori", 2e-5)]:
+            want = g[f"grad{it}_{nm}"]
+            assert np.array_equal(np.isnan(got), np.isnan(want)), (it, nm)
+            assert np.nanmax(np.abs(got - want)) <= tol * np.nanmax(np.abs(want)), (it, nm)
+        opt.step(1)
+
+
+@pytest.mark.parametrize("tag,hand,state", CASES)
+def test_full_trajectory_matches_reference(tag, hand, state, golden_dir):
+    g, gp, opt, q0, T0, k0, mu = _setup(tag, hand, state, golden_dir)
+    iters = int(g["iters"])
+    opt._init(q0, T0, k0, mu, gp)
+    losses = []
+    for it in range(iters):
+        losses.append(opt.evaluate()[0].cpu().numpy())
+        opt.step(1)
+    losses = np.stack(losses)
+    ref = g["losses"]
+    assert np.array_equal(np.isnan(losses), np.isnan(ref))
+    rel = np.nan_to_num(np.abs(losses - ref) / np.maximum(np.abs(ref), 1.0))
+    assert rel.max() <= 1e-4, rel.max(axis=1)
+    # the drop-in call: same 5-tuple as optimize_pregrasp.py:839
+    res = opt.optimize(q0, T0, k0, mu, gp, verbose=False)
+    for a, nm, tol in zip(res, ["opt_q", "opt_compliance", "opt_target", "opt_palm", "opt_margin"], [1e-4, 1e-3, 1e-4, 1e-4, 1e-4]):
+        want = g[nm]
+        assert tuple(a.shape) == want.shape and a.dtype == torch.float64
+        assert np.array_equal(np.isnan(a.cpu().numpy()), np.isnan(want))
+        assert np.nanmax(np.abs(a.cpu().numpy() - want)) <= tol * max(1.0, np.nanmax(np.abs(want))), nm
+    # arg-min over opt_value (BASELINE.json: identical arg-min candidate index)
+    best_ref = np.where(np.isnan(ref[21:]), np.inf, ref[21:]).min(axis=0)
+    v, idx = opt.argmin()
+    assert idx == int(np.argmin(best_ref)) and abs(v - best_ref.min()) <= 1e-4 * abs(best_ref.min())
+
+
+def test_sharding_invariance(golden_dir):
+    """candidates [4:8] run alone with env_offset=4 reproduce rows 4:8 of the full batch bit for bit."""
+    g, gp, opt, q0, T0, k0, mu = _setup(*CASES[0], golden_dir, num_iters=25)
+    full = [t.clone() for t in opt.optimize(q0, T0, k0, mu, gp, verbose=False)]
+    full_v = opt.opt_value.clone()
+    from compliancedex_b200 import ProbabilisticGraspOptimizer, load_hand
+    doc = load_hand("leap")
+    part = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                       palm_offset=g["palm0"][4:8], num_iters=25, optimize_target=True, ref_q=doc["ref_q"],
+                                       mass=float(g["mass"]), com=g["com"].tolist(), optimize_palm=True,
+                                       noise_seed=int(g["noise_seed"]), env_offset=4)
+    res = part.optimize(q0[4:8], T0[4:8], k0[4:8], mu, gp, verbose=False)
+    for a, b in zip(res, full):
+        assert torch.equal(a, b[4:8])
+    assert torch.equal(part.opt_value, full_v[4:8])
+    v, idx = part.argmin()
+    assert 4 <= idx < 8
+
+
+def test_distinct_pregrasp_coefficients_against_oracle(golden_dir):
+    """coefficient rows that differ (U = 3 GPIS query blocks) + optimize_palm/target off, vs the oracle."""
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path, hand_path
+    from oracle.gpis_oracle import GPISOracle
+    from oracle.pregrasp_oracle import PregraspOracle
+    g = np.load(os.path.join(golden_dir, "pregrasp_leap_mug.npz"))
+    coeffs = [[0.7, 0.75, 0.8, 0.85], [0.8, 0.8, 0.8, 0.8], [0.9, 0.85, 0.8, 0.75]]
+    doc = load_hand("leap")
+    for opt_palm, opt_target in [(True, True), (False, False)]:
+        gp = GPIS(0.08, 1.0)
+        gp.load_state_data(state_path("mug_state"))
+        opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                          palm_offset=g["palm0"], num_iters=6, optimize_target=opt_target, ref_q=doc["ref_q"],
+                                          pregrasp_coefficients=coeffs, mass=0.1, optimize_palm=opt_palm, noise_seed=77)
+        q0, T0, k0 = (torch.from_numpy(g[k]) for k in ("q0", "target0", "compliance0"))
+        T0 = T0 + 0.01 * torch.randn(T0.shape, generator=torch.Generator().manual_seed(1), dtype=torch.float64)
+        o = PregraspOracle(hand_path("leap"), g["palm0"], 6, optimize_target=opt_target, optimize_palm=opt_palm,
+                           pregrasp_coefficients=coeffs, mass=0.1, noise_seed=77)
+        go = GPISOracle(0.08, 1.0).load_npz(state_path("mug_state"))
+        ref_losses = []
+        o.optimize(q0, T0, k0, 1, go, record=lambda s, t, gr: ref_losses.append(t.numpy()))
+        opt._init(q0.cuda(), T0.cuda(), k0.cuda(), 1, gp)
+        for it in range(6):
+            loss = opt.evaluate()[0].cpu().numpy()
+            ref = ref_losses[it]
+            assert np.array_equal(np.isnan(loss), np.isnan(ref))
+            ok = ~np.isnan(ref)
+            assert (np.abs(loss[ok] - ref[ok]) <= 1e-4 * np.maximum(np.abs(ref[ok]), 1.0)).all(), (it, loss, ref)
+            opt.step(1)
+
+
+def test_errors():
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand
+    doc = load_hand("leap")
+    opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                      palm_offset=np.zeros((2, 6)), num_iters=1, ref_q=doc["ref_q"])
+    with pytest.raises(RuntimeError):
+        opt.optimize(torch.zeros(2, 16), torch.zeros(2, 4, 3), torch.ones(2, 4), 1, GPIS(0.08, 1.0))   # unfitted GPIS
