@@ -102,7 +102,7 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
     const float* F = ch.fixed_rot[i];
     if (ch.dof[i] >= 0) {
       const float ang = ch.sign[i] * q32[ch.dof[i]];
-      const float c = cosf(ang), s = sinf(ang);
+      const float c = (float)cos((double)ang), s = (float)sin((double)ang);  // correctly rounded float32 values
       // fixed @ R_axis(ang): the two columns orthogonal to the axis mix, the axis column is kept
       const int a = ch.axis[i], u = (a + 1) % 3, v = (a + 2) % 3;
       for (int r = 0; r < 3; r++) {

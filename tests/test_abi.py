@@ -54,5 +54,5 @@ def test_params_struct_layout_matches_header():
             continue
         _, rest = decl.split(None, 1)
         for part in rest.split(","):
-            fields.append(re.match(r"\s*([a-z_0-9]+)", part).group(1))
+            fields.append(re.match(r"\s*([A-Za-z_0-9]+)", part).group(1))
     assert fields == [f[0] for f in _lib.PregraspParams._fields_]
