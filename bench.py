@@ -122,21 +122,11 @@ def barrier(world):
 
 # ------------------------------------------------------------------------------------------ GPIS C3
 def gpis_c3_inputs(ntrain, m_total, rank, world):
-    from oracle.gpis_oracle import synthetic_training_set   # input GENERATOR only (seeded synthetic data), no oracle compute
+    from compliancedex_b200.distributed import shard_range
+    from compliancedex_b200.synthetic import synthetic_queries, synthetic_training_set
     X1, y1, noise = synthetic_training_set(ntrain, seed=0)
-    per = (m_total + world - 1) // world
-    lo, hi = rank * per, min(m_total, (rank + 1) * per)
-    g = torch.Generator().manual_seed(1234)
-    # queries: uniform in [-b,b]^3, generated in fixed 2^20 blocks so a rank's slice is independent of world size
-    blk = 1 << 20
-    parts = []
-    for b0 in range(0, m_total, blk):
-        n = min(blk, m_total - b0)
-        x = (torch.rand(n, 3, generator=g, dtype=torch.float64) * 2 - 1) * 0.1
-        s, e = max(lo, b0), min(hi, b0 + n)
-        if s < e:
-            parts.append(x[s - b0:e - b0])
-    return X1, y1, noise, torch.cat(parts), per
+    lo, hi = shard_range(m_total, rank, world)
+    return X1, y1, noise, synthetic_queries(m_total, lo, hi), hi - lo
 
 
 def run_gpis_c3(args, rank, world, local):
@@ -252,7 +242,7 @@ def main():
     workload = args.workload
     if workload == "auto":
         try:
-            from compliancedex_b200.pregrasp import run_bench_c2  # noqa: F401
+            from bench_pregrasp import run_bench_c2  # noqa: F401
             workload = "pregrasp_c2"
         except ImportError:
             workload = "gpis_c3"
@@ -278,7 +268,7 @@ def main():
                                      "sample": "2048 queries per step: one pred (LU) + one compute_normal (inverse)"},
                     "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         else:
-            from compliancedex_b200.pregrasp import run_reference_c2
+            from bench_pregrasp import run_reference_c2
             line = run_reference_c2(args, threads, world)
         print(json.dumps(line), flush=True)
         return
@@ -293,8 +283,15 @@ def main():
                                     "sample": "2048 of the queries: one pred (LU of the 4096^2 matrix + MxM covariance) + "
                                               "one compute_normal (explicit inverse), %.1f s" % dt}
     else:
-        from compliancedex_b200.pregrasp import run_bench_c2
+        from bench_pregrasp import run_bench_c2
         line = run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks)
+        if rank == 0 and not args.no_cpu_baseline:
+            from bench_pregrasp import cpu_pregrasp
+            cpu_pregrasp(16, 2, threads)                          # warm-up (torch thread pool, LAPACK)
+            v, dt = cpu_pregrasp(64, 10, threads)
+            line["cpu_baseline"] = {"value": v, "unit": "candidate-iters/s", "cores": threads, "kind": "port",
+                                    "sample": "64 candidates x 10 iterations of the same workload through the oracle port of "
+                                              "the reference (torch CPU, per-call LU/inverse GPIS as gpis.py:53,77), %.1f s" % dt}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -1,0 +1,166 @@
+"""bench.py's pregrasp workload (BASELINE.json configs[1]): ProbabilisticGraspOptimizer, Leap hand on the mug GPIS,
+1,024 candidates x 200 iterations per GPU.  One "step" = one whole optimisation (init + 200 iterations + arg-min).
+Weak scaling: every rank optimises its own 1,024 candidates (global candidate index = rank * 1024 + local), the only
+cross-rank traffic is the final 16-byte all-gather for the arg-min."""
+import ctypes
+import json
+import os
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+METRIC = "pregrasp candidate-iters/sec"
+
+
+def _workload_name(B, iters, world):
+    return ("pregrasp_c2: ProbabilisticGraspOptimizer (optimize_target, optimize_palm), Leap hand on the mug GPIS state "
+            "(N=196), %d candidates x %d iterations per GPU, %d GPU(s)" % (B, iters, world))
+
+
+def _make(rank, B, iters, device):
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path("mug_state"), device=device)
+    doc = load_hand("leap")
+    d = np.load(state_path("mug_state"))
+    center = surface_center(d["X1"], d["y1"])
+    q0, T0, k0, palm = synthetic_candidates(doc, B, center, seed=100 + rank)
+    opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                      palm_offset=palm, num_iters=iters, optimize_target=True, ref_q=doc["ref_q"],
+                                      mass=0.1, com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True,
+                                      device=device, noise_seed=2024, env_offset=rank * B)
+    return gp, opt, q0, T0, k0, palm, int(d["X1"].shape[0])
+
+
+def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks):
+    from compliancedex_b200 import _lib
+    from compliancedex_b200.distributed import global_argmin
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    B, iters = args.candidates, args.iters
+    gp, opt, q0, T0, k0, palm, N = _make(rank, B, iters, dev)
+    lib = _lib.load()
+    q0d, T0d, k0d = q0.to(dev), T0.to(dev), k0.to(dev)
+
+    def step():
+        opt._init(q0d, T0d, k0d, 1, gp)
+        opt.step(iters)
+        return global_argmin(opt, world)
+
+    for _ in range(args.warmup):
+        best = step()
+    sampler = ClockSampler(local)
+    l0 = lib.cdx_launch_count(gp._ctx)
+    barrier(world)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        best = step()
+    e1.record()
+    barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = lib.cdx_launch_count(gp._ctx) - l0
+
+    # e2e: the public call with HOST tensors (pinned): H2D of the candidates, D2H of the 5-tuple + arg-min
+    hq, hT, hk = q0.pin_memory(), T0.pin_memory(), k0.pin_memory()
+    outs = None
+
+    def step_e2e():
+        res = opt.optimize(hq, hT, hk, 1, gp, verbose=False)
+        b = global_argmin(opt, world)
+        return [t.cpu() for t in res], b
+
+    step_e2e()
+    barrier(world)
+    e0.record()
+    for _ in range(args.steps):
+        outs, best = step_e2e()
+    e1.record()
+    barrier(world)
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world)
+
+    # one more step with per-kernel CUDA events (cdx_pregrasp_profile) for the roofline of the dominant kernel
+    _lib.check(lib.cdx_pregrasp_profile(gp._ctx, 1))
+    step()
+    kms = (ctypes.c_double * 4)()
+    nit = ctypes.c_int()
+    _lib.check(lib.cdx_pregrasp_profile_read(gp._ctx, kms, ctypes.byref(nit), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    _lib.check(lib.cdx_pregrasp_profile(gp._ctx, 0))
+    if rank != 0:
+        return None
+    kernel_ms = {k: kms[i] / max(1, nit.value) for i, k in enumerate(["pg_points", "gpis_var_ext", "gpis_mean", "pg_objective"])}
+    ms_step = ms / args.steps
+    total_units = B * world * iters
+    pipes = fp64_pipe_peaks()
+    peaks, src = measured_peaks()
+    U = 1                                                          # identical coefficient rows share one query block
+    ext_queries = B * U * 4
+    flop_ext = 2 * N * N + 34 * N                                  # extended query {mean, grad, std, grad std}
+    achieved = flop_ext * ext_queries / (kernel_ms["gpis_var_ext"] * 1e-3) / 1e12
+    peak = pipes.get("dmma_m8n8k4_tflops")
+    share = {k: v / sum(kernel_ms.values()) for k, v in kernel_ms.items()}
+    return {
+        "metric": METRIC, "value": total_units / (ms_step * 1e-3), "unit": "candidate-iters/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": _workload_name(B, iters, world), "ms_per_iteration": ms_step / iters,
+                   "l2_policy": "latency-bound loop: the 0.6 MB state (L, E11^-1) and the per-candidate buffers are re-used "
+                                "every iteration by design (resident working set), no flush applies",
+                   "argmin": {"value": best[0], "global_index": best[1]}},
+        "e2e": {"value": total_units / (ms_e2e / args.steps * 1e-3), "unit": "candidate-iters/s",
+                "h2d_bytes_per_step": int(B * (16 + 12 + 4 + 6) * 8), "d2h_bytes_per_step": int(B * (16 + 4 + 12 + 6 + 4) * 8 + 16)},
+        "gpu_launches": int(launches), "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,64,ext> (FP64 DMMA) inside the pregrasp iteration",
+                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if peak else None,
+                     "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json has no "
+                                    "FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0)),
+                     "flop_per_query": flop_ext, "queries_per_launch": ext_queries, "traffic": None,
+                     "kernel_ms_per_iteration": kernel_ms, "kernel_share": share,
+                     "note": "per-kernel times from one extra step with CUDA events around each launch (cdx_pregrasp_profile)",
+                     "fp64_pipes": pipes},
+    }
+
+
+# ------------------------------------------------------------------------------------------ CPU side (oracle port)
+def cpu_pregrasp(B, iters, threads, seed=100):
+    """The reference's algorithm (oracle/pregrasp_oracle.py, a torch restatement of optimize_pregrasp.py:614-839 with the
+    reference's own per-call LU / inverse GPIS, kind "port": /root/reference cannot travel to the GPU box) on the host
+    cores: B candidates x iters iterations of the same workload.  -> candidate-iters/s, seconds"""
+    from compliancedex_b200 import hand_path, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    from oracle.gpis_oracle import GPISOracle
+    from oracle.pregrasp_oracle import PregraspOracle
+    torch.set_num_threads(threads)
+    go = GPISOracle(0.08, 1.0).load_npz(state_path("mug_state"))
+    doc = load_hand("leap")
+    d = np.load(state_path("mug_state"))
+    q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=seed)
+    o = PregraspOracle(hand_path("leap"), palm, iters, mass=0.1, noise_seed=2024)
+    t0 = time.perf_counter()
+    o.optimize(q0, T0, k0, 1, go)
+    dt = time.perf_counter() - t0
+    return B * iters / dt, dt
+
+
+def run_reference_c2(args, threads, world):
+    Bs, its = 64, 10
+    vals = []
+    for i in range(args.warmup + args.steps):
+        v, dt = cpu_pregrasp(Bs, its, threads)
+        if i >= args.warmup:
+            vals.append((v, dt))
+    v = float(np.mean([a for a, _ in vals]))
+    ms = float(np.mean([b for _, b in vals])) * 1e3
+    sample = "each step = %d candidates x %d iterations of the same workload (oracle port of the reference, torch CPU)" % (Bs, its)
+    return {"impl": "reference", "metric": METRIC, "value": v, "unit": "candidate-iters/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": _workload_name(args.candidates, args.iters, world), "sample": sample},
+            "cpu_baseline": {"value": v, "unit": "candidate-iters/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "candidate-iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}

@@ -59,6 +59,8 @@ SIGNATURES = {
     "cdx_pregrasp_results": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_argmin": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "cdx_pregrasp_profile": (c_int, [c_void_p, c_int]),
+    "cdx_pregrasp_profile_read": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_int), c_void_p]),
     "cdx_launch_count": (c_i64, [c_void_p]),
 }
 

@@ -34,6 +34,8 @@ struct cdx_pg_state {
   double* adam_tab = nullptr;  // [tab_cap][2]: 1 - beta1^t, sqrt(1 - beta2^t) for t = index + 1
   int tab_cap = 0;
   cdx_hand_dev* hand_dev = nullptr;
+  bool prof = false;
+  std::vector<cudaEvent_t> prof_ev;   // 5 events per profiled iteration
 };
 
 namespace {
@@ -87,6 +89,10 @@ pg_points_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg
 }
 
 __global__ void pg_tick_kernel(int* it) { *it += 1; }
+__global__ void pg_fill_kernel(double* p, int64_t n, double v) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
 
 // NaN-propagating clamps (torch.clamp keeps NaN; fmax/fmin would not)
 __device__ __forceinline__ double clamp_lo(double x, double lo) { return x < lo ? lo : x; }
@@ -324,11 +330,8 @@ extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int
   CDX_CUDA(cudaMemsetAsync(s->m1, 0, sizeof(double) * B * NPAR, st));
   CDX_CUDA(cudaMemsetAsync(s->m2, 0, sizeof(double) * B * NPAR, st));
   CDX_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), st));
-  {
-    std::vector<double> inf((size_t)B, INFINITY);
-    CDX_CUDA(cudaMemcpyAsync(s->ovalue, inf.data(), sizeof(double) * B, cudaMemcpyHostToDevice, st));
-    CDX_CUDA(cudaStreamSynchronize(st));
-  }
+  pg_fill_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(s->ovalue, B, INFINITY);
+  CDX_CHECK_LAUNCH(ctx);
   s->it_host = 0;
   return CDX_OK;
 }
@@ -338,18 +341,31 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
                         cudaStream_t st) {
   const int64_t B = s->B;
   const int U = s->U;
+  const bool prof = s->prof && do_step;
+  auto mark = [&]() {
+    if (!prof) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    s->prof_ev.push_back(e);
+  };
+  mark();
   pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(s->hand_dev, B, U, s->setup, s->q, s->T, s->palm, s->tl,
                                                                   s->J, s->Xext, s->Xmean, nullptr);
   CDX_CHECK_LAUNCH(ctx);
+  mark();
   int rc = cdx_gpis_query(ctx, s->Xext, B * U * 4, s->dist, s->gmu, s->sd, s->gsd, (void*)st);
   if (rc) return rc;
+  mark();
   rc = cdx_gpis_query(ctx, s->Xmean, B * 9, s->mean9, s->gmean9, nullptr, nullptr, (void*)st);
   if (rc) return rc;
+  mark();
   pg_objective_kernel<<<(unsigned)((B + 63) / 64), 64, 0, st>>>(
       s->hand_dev, B, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd, s->mean9,
       s->gmean9, loss, margin, grad, do_step, s->it_dev, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,
       s->omargin, s->ovalue);
   CDX_CHECK_LAUNCH(ctx);
+  mark();
   return CDX_OK;
 }
 
@@ -450,5 +466,30 @@ extern "C" int cdx_pregrasp_argmin(cdx_ctx* ctx, double* out, void* stream) {
   cdx_pg_state* s = ctx->pg;
   pg_argmin_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(s->ovalue, s->B, s->prm.env_offset, out);
   CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}
+
+extern "C" int cdx_pregrasp_profile(cdx_ctx* ctx, int enable) {
+  if (!ctx) { cdx_set_error("cdx_pregrasp_profile: NULL context"); return CDX_ERR_ARG; }
+  pg_get(ctx)->prof = enable != 0;
+  return CDX_OK;
+}
+
+extern "C" int cdx_pregrasp_profile_read(cdx_ctx* ctx, double* ms_out4, int* n_iters, void* stream) {
+  if (!ctx || !ctx->pg || !ms_out4 || !n_iters) { cdx_set_error("cdx_pregrasp_profile_read: bad argument"); return CDX_ERR_ARG; }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  CDX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  cdx_pg_state* s = ctx->pg;
+  for (int k = 0; k < 4; k++) ms_out4[k] = 0.0;
+  const size_t n = s->prof_ev.size() / 5;
+  for (size_t i = 0; i < n; i++)
+    for (int k = 0; k < 4; k++) {
+      float ms = 0.f;
+      CDX_CUDA(cudaEventElapsedTime(&ms, s->prof_ev[i * 5 + k], s->prof_ev[i * 5 + k + 1]));
+      ms_out4[k] += (double)ms;
+    }
+  for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);
+  s->prof_ev.clear();
+  *n_iters = (int)n;
   return CDX_OK;
 }

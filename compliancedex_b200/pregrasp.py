@@ -205,9 +205,13 @@ class ProbabilisticGraspOptimizer:
         """(best opt_value, GLOBAL candidate index = env_offset + local index), lowest index on ties; the cross-rank
         reduction of these pairs is compliancedex_b200.distributed.global_argmin."""
         out = torch.empty(2, dtype=torch.float64, device=self.device)
-        _lib.check(_lib.load().cdx_pregrasp_argmin(self._ctx, _ptr(out), self._stream()))
+        self.argmin_into(out)
         v, i = out.tolist()
         return v, int(i)
+
+    def argmin_into(self, out):
+        """device-side arg-min into out[2] (float64, on this optimizer's device): no host sync"""
+        _lib.check(_lib.load().cdx_pregrasp_argmin(self._ctx, _ptr(out), self._stream()))
 
     def compute_collision_loss(self, joint_angles, palm_poses=None):
         # optimize_pregrasp.py:671-701 is dead code on this path (its call at :765 is commented out)

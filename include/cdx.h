@@ -124,6 +124,13 @@ int cdx_pregrasp_state(cdx_ctx* ctx, double* q_dev, double* compliance_dev, doub
  * (env_offset + local).  The cross-rank step is an all-gather of these 16 bytes. */
 int cdx_pregrasp_argmin(cdx_ctx* ctx, double* out_dev, void* stream);
 
+/* optional per-kernel timing (bench.py's roofline): after cdx_pregrasp_profile(ctx, 1) every cdx_pregrasp_run records
+ * CUDA events around the four kernels of each iteration; cdx_pregrasp_profile_read synchronises `stream` and returns the
+ * summed milliseconds {points, gpis extended query, gpis mean query, objective+Adam} and the iterations covered, then
+ * clears the record. */
+int cdx_pregrasp_profile(cdx_ctx* ctx, int enable);
+int cdx_pregrasp_profile_read(cdx_ctx* ctx, double* ms_out4, int* n_iters, void* stream);
+
 /* how many cdx kernels this context has launched since creation (bench.py's gpu_launches) */
 int64_t cdx_launch_count(cdx_ctx* ctx);
 
