@@ -36,18 +36,31 @@ struct cdx_hand_dev {
 };
 
 // ------------------------------------------------------------------------------------------------ helpers
+// float32 product / sum that the compiler may NOT contract into an FMA: the reference's FK runs as separate torch
+// float32 multiplies and adds (CPU ATen), so the kernels round after every operation as well.
+#ifdef __CUDA_ARCH__
+#define CDX_FM(a, b) __fmul_rn((a), (b))
+#define CDX_FA(a, b) __fadd_rn((a), (b))
+#define CDX_FS(a, b) __fsub_rn((a), (b))
+#else   // host build (tests/hostcheck) is compiled with -ffp-contract=off
+#define CDX_FM(a, b) ((a) * (b))
+#define CDX_FA(a, b) ((a) + (b))
+#define CDX_FS(a, b) ((a) - (b))
+#endif
 CDX_HD void cdx_cross3(const double* a, const double* b, double* o) {
   o[0] = a[1] * b[2] - a[2] * b[1];
   o[1] = a[2] * b[0] - a[0] * b[2];
   o[2] = a[0] * b[1] - a[1] * b[0];
 }
 CDX_HD void cdx_cross3f(const float* a, const float* b, float* o) {
-  o[0] = a[1] * b[2] - a[2] * b[1];
-  o[1] = a[2] * b[0] - a[0] * b[2];
-  o[2] = a[0] * b[1] - a[1] * b[0];
+  o[0] = CDX_FS(CDX_FM(a[1], b[2]), CDX_FM(a[2], b[1]));
+  o[1] = CDX_FS(CDX_FM(a[2], b[0]), CDX_FM(a[0], b[2]));
+  o[2] = CDX_FS(CDX_FM(a[0], b[1]), CDX_FM(a[1], b[0]));
 }
 CDX_HD double cdx_dot3(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
-CDX_HD float cdx_dot3f(const float* a, const float* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+CDX_HD float cdx_dot3f(const float* a, const float* b) {
+  return CDX_FA(CDX_FA(CDX_FM(a[0], b[0]), CDX_FM(a[1], b[1])), CDX_FM(a[2], b[2]));
+}
 // o = M v, o = M^T v  (row-major 3x3)
 CDX_HD void cdx_mv(const double* M, const double* v, double* o) {
   o[0] = M[0] * v[0] + M[1] * v[1] + M[2] * v[2];
@@ -65,7 +78,8 @@ CDX_HD void cdx_mm(const double* A, const double* B, double* C) {
 }
 CDX_HD void cdx_mmf(const float* A, const float* B, float* C) {
   for (int r = 0; r < 3; r++)
-    for (int c = 0; c < 3; c++) C[r * 3 + c] = A[r * 3] * B[c] + A[r * 3 + 1] * B[3 + c] + A[r * 3 + 2] * B[6 + c];
+    for (int c = 0; c < 3; c++)
+      C[r * 3 + c] = CDX_FA(CDX_FA(CDX_FM(A[r * 3], B[c]), CDX_FM(A[r * 3 + 1], B[3 + c])), CDX_FM(A[r * 3 + 2], B[6 + c]));
 }
 
 // ------------------------------------------------------------------------------------------------ FK
@@ -101,13 +115,13 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
     float jr[9];
     const float* F = ch.fixed_rot[i];
     if (ch.dof[i] >= 0) {
-      const float ang = ch.sign[i] * q32[ch.dof[i]];
-      const float c = (float)cos((double)ang), s = (float)sin((double)ang);  // correctly rounded float32 values
+      const float ang = CDX_FM(ch.sign[i], q32[ch.dof[i]]);
+      const float c = cosf(ang), s = sinf(ang);   // torch.cos/sin on a CUDA float32 tensor are these libdevice functions
       // fixed @ R_axis(ang): the two columns orthogonal to the axis mix, the axis column is kept
       const int a = ch.axis[i], u = (a + 1) % 3, v = (a + 2) % 3;
       for (int r = 0; r < 3; r++) {
-        jr[r * 3 + u] = F[r * 3 + u] * c + F[r * 3 + v] * s;
-        jr[r * 3 + v] = F[r * 3 + v] * c - F[r * 3 + u] * s;
+        jr[r * 3 + u] = CDX_FA(CDX_FM(F[r * 3 + u], c), CDX_FM(F[r * 3 + v], s));
+        jr[r * 3 + v] = CDX_FS(CDX_FM(F[r * 3 + v], c), CDX_FM(F[r * 3 + u], s));
         jr[r * 3 + a] = F[r * 3 + a];
       }
     } else {
@@ -116,7 +130,8 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
     // CoordinateTransform.multiply_transform (spatial_vector_algebra.py:98-103)
     float Rn[9], pn[3];
     cdx_mmf(R, jr, Rn);
-    for (int r = 0; r < 3; r++) pn[r] = R[r * 3] * ch.xyz[i][0] + R[r * 3 + 1] * ch.xyz[i][1] + R[r * 3 + 2] * ch.xyz[i][2] + p[r];
+    for (int r = 0; r < 3; r++)
+      pn[r] = CDX_FA(CDX_FA(CDX_FA(CDX_FM(R[r * 3], ch.xyz[i][0]), CDX_FM(R[r * 3 + 1], ch.xyz[i][1])), CDX_FM(R[r * 3 + 2], ch.xyz[i][2])), p[r]);
     for (int e = 0; e < 9; e++) R[e] = Rn[e];
     for (int r = 0; r < 3; r++) p[r] = pn[r];
     if (ch.dof[i] >= 0 && nd < CDX_MAX_CHAIN_DOF) {
@@ -136,12 +151,15 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
   float qr[4];
   const float tn = cdx_quat_raw(R, branch, 1.f, qr);
   const float s = (float)(0.5 / sqrt((double)tn));  // python-float normaliser (spatial_vector_algebra.py:135)
-  const float qv[3] = {qr[0] * s, qr[1] * s, qr[2] * s}, qw = qr[3] * s;
+  const float qv[3] = {CDX_FM(qr[0], s), CDX_FM(qr[1], s), CDX_FM(qr[2], s)}, qw = CDX_FM(qr[3], s);
   const float* o = ch.offset;
   float cvo[3];
   cdx_cross3f(qv, o, cvo);
   const float qvo = cdx_dot3f(qv, o);
-  for (int r = 0; r < 3; r++) tip[r] = p[r] + (o[r] * (2.f * qw * qw - 1.f) + cvo[r] * qw * 2.f + qv[r] * qvo * 2.f);
+  // a = v (2 qw^2 - 1);  b = cross(qv, v) qw 2;  c = qv (qv . v) 2;  a + b + c   (se3_so3_util.py:245-250)
+  const float aw = CDX_FS(CDX_FM(2.f, CDX_FM(qw, qw)), 1.f);
+  for (int r = 0; r < 3; r++)
+    tip[r] = CDX_FA(p[r], CDX_FA(CDX_FA(CDX_FM(o[r], aw), CDX_FM(CDX_FM(cvo[r], qw), 2.f)), CDX_FM(CDX_FM(qv[r], qvo), 2.f)));
   for (int c = 0; c < nd; c++) {
     float d[3] = {p[0] - org[c][0], p[1] - org[c][1], p[2] - org[c][2]}, dp[3];
     cdx_cross3f(om[c], d, dp);

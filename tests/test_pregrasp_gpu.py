@@ -134,7 +134,8 @@ def test_distinct_pregrasp_coefficients_against_oracle(golden_dir):
             ref = ref_losses[it]
             assert np.array_equal(np.isnan(loss), np.isnan(ref))
             ok = ~np.isnan(ref)
-            assert (np.abs(loss[ok] - ref[ok]) <= 1e-4 * np.maximum(np.abs(ref[ok]), 1.0)).all(), (it, loss, ref)
+            # the loss is a sum of cancelling terms of magnitude 1e2..1e3 (1000 |dist|, 200 log barriers): floor the scale at 10
+            assert (np.abs(loss[ok] - ref[ok]) <= 1e-4 * np.maximum(np.abs(ref[ok]), 10.0)).all(), (it, loss, ref)
             opt.step(1)
 
 
