@@ -94,7 +94,7 @@ def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks
     _lib.check(lib.cdx_pregrasp_profile(gp._ctx, 0))
     if rank != 0:
         return None
-    kernel_ms = {k: kms[i] / max(1, nit.value) for i, k in enumerate(["pg_points", "gpis_var_ext", "gpis_mean", "pg_objective"])}
+    kernel_ms = {k: kms[i] / max(1, nit.value) for i, k in enumerate(["wait_for_mean_query", "gpis_var_ext", "gpis_mean_overlapped", "pg_step"])}
     ms_step = ms / args.steps
     total_units = B * world * iters
     pipes = fp64_pipe_peaks()
@@ -104,7 +104,8 @@ def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks
     flop_ext = 2 * N * N + 34 * N                                  # extended query {mean, grad, std, grad std}
     achieved = flop_ext * ext_queries / (kernel_ms["gpis_var_ext"] * 1e-3) / 1e12
     peak = pipes.get("dmma_m8n8k4_tflops")
-    share = {k: v / sum(kernel_ms.values()) for k, v in kernel_ms.items()}
+    crit = kernel_ms["gpis_var_ext"] + kernel_ms["wait_for_mean_query"] + kernel_ms["pg_step"]   # main-stream critical path
+    share = {k: kernel_ms[k] / crit for k in ("gpis_var_ext", "wait_for_mean_query", "pg_step")}
     return {
         "metric": METRIC, "value": total_units / (ms_step * 1e-3), "unit": "candidate-iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -116,13 +117,13 @@ def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks
         "e2e": {"value": total_units / (ms_e2e / args.steps * 1e-3), "unit": "candidate-iters/s",
                 "h2d_bytes_per_step": int(B * (16 + 12 + 4 + 6) * 8), "d2h_bytes_per_step": int(B * (16 + 4 + 12 + 6 + 4) * 8 + 16)},
         "gpu_launches": int(launches), "clocks": clocks,
-        "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,64,ext> (FP64 DMMA) inside the pregrasp iteration",
+        "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,64,ext,32> (FP64 DMMA) inside the pregrasp iteration",
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if peak else None,
                      "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json has no "
                                     "FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0)),
                      "flop_per_query": flop_ext, "queries_per_launch": ext_queries, "traffic": None,
                      "kernel_ms_per_iteration": kernel_ms, "kernel_share": share,
-                     "note": "per-kernel times from one extra step with CUDA events around each launch (cdx_pregrasp_profile)",
+                     "note": "per-kernel times from one extra step with CUDA events around each launch (cdx_pregrasp_profile); the mean-only query runs on a forked stream, overlapped with the extended query; kernel_share is over the main-stream critical path",
                      "fp64_pipes": pipes},
     }
 

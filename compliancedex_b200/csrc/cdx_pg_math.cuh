@@ -211,7 +211,7 @@ CDX_HD void cdx_svd3(const double* A, double* U, double* S, double* V) {
     for (int pr = 0; pr < 3; pr++) {
       const int p = (pr == 2) ? 1 : 0, q = (pr == 0) ? 1 : 2;
       const double al = cdx_dot3(g[p], g[p]), be = cdx_dot3(g[q], g[q]), ga = cdx_dot3(g[p], g[q]);
-      if (ga == 0.0 || fabs(ga) <= 1e-17 * sqrt(al * be)) continue;
+      if (ga * ga <= 1e-30 * (al * be)) continue;   // columns orthogonal to 1e-15 relative: converged pair
       rotated = true;
       const double zeta = (be - al) / (2.0 * ga);
       const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));

@@ -1,11 +1,13 @@
 // Batched probabilistic pregrasp optimisation (ProbabilisticGraspOptimizer, optimize_pregrasp.py:614-839) without
-// autograd and without host synchronisation.  One optimiser iteration is four launches on the caller's stream:
-//   pg_points_kernel     float32 FK + reference-compatible Jacobian per (candidate, finger); palm transform; emits the
-//                        GPIS query points (pregrasp blend :747-750, targets, tips, palm position)
+// autograd and without host synchronisation.  One optimiser iteration is three launches:
 //   gpis_var_kernel<EXT> mean, grad mean, std, grad std at the blended contact points (cdx_query.cu, FP64 DMMA)
-//   gpis_mean_kernel     mean, grad mean at targets / tips / palm (cdx_query.cu, TMA-staged training set)
-//   pg_objective_kernel  per candidate: Kabsch (3x3 Jacobi SVD) equilibrium, all cost terms, ANALYTIC reverse pass
-//                        (cdx_pg_math.cuh), best-iterate tracking (:822-829), Adam (:831) and the clamps (:833-834)
+//   gpis_mean_kernel     mean, grad mean at targets / tips / palm (cdx_query.cu, TMA-staged training set), on a forked
+//                        stream so that it overlaps the extended query
+//   pg_step_kernel       4 lanes per candidate: Kabsch (3x3 Jacobi SVD) equilibrium per pregrasp copy, all cost terms,
+//                        ANALYTIC reverse pass (cdx_pg_math.cuh), best-iterate tracking (:822-829), Adam (:831), the
+//                        clamps (:833-834), then float32 FK + reference-compatible Jacobian of the NEW iterate and its
+//                        GPIS query points (pregrasp blend :747-750, targets, tips, palm position)
+// pg_points_kernel does the FK / query points once for the initial iterate.
 #include <math.h>
 #include <vector>
 #include "cdx_internal.cuh"
@@ -29,8 +31,10 @@ struct cdx_pg_state {
   double *dist = nullptr, *sd = nullptr, *gmu = nullptr, *gsd = nullptr;   // [B*U*4], [.. ,3]
   double *mean9 = nullptr, *gmean9 = nullptr;                               // [B*9], [B*9,3]
   double *loss = nullptr, *margin = nullptr, *grad = nullptr;               // [B], [B,4], [B,38]
-  int* it_dev = nullptr;     // absolute iteration index (keys the noise stream, Adam bias correction, s > 20)
-  int it_host = 0;
+  int it_host = 0;           // absolute iteration index (keys the noise stream, Adam bias correction, s > 20)
+  bool points_valid = false; // tl / J / Xext / Xmean describe the current iterate
+  cudaStream_t side = nullptr;              // forked stream for the mean-only GPIS query
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   double* adam_tab = nullptr;  // [tab_cap][2]: 1 - beta1^t, sqrt(1 - beta2^t) for t = index + 1
   int tab_cap = 0;
   cdx_hand_dev* hand_dev = nullptr;
@@ -44,25 +48,23 @@ constexpr int NPAR = 38;  // q16 | k4 | T12 | palm6
 
 struct pg_lr { double v[5]; };
 
-__global__ void __launch_bounds__(128)
-pg_points_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_setup S, const double* __restrict__ q,
-                 const double* __restrict__ T, const double* __restrict__ palm, double* __restrict__ tl,
-                 float* __restrict__ J, double* __restrict__ Xext, double* __restrict__ Xmean,
-                 double* __restrict__ tips_out) {
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= B * 4) return;
-  const int64_t b = gid >> 2;
-  const int f = (int)(gid & 3);
+// FK of finger f for candidate b at joint angles q (float64, n_dofs entries), palm pose palm6, target Tf; writes the
+// per-iteration scratch (tl, J) and the GPIS query points of this finger (pregrasp blend :747-750, target, tip, palm).
+__device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ hand, const cdx_pg_setup& S, int U, int64_t b,
+                                               int f, const double* q, const double* Tf, const double* palm6,
+                                               double* __restrict__ tl, float* __restrict__ J, double* __restrict__ Xext,
+                                               double* __restrict__ Xmean, double* __restrict__ tips_out) {
   float q32[16];
 #pragma unroll
-  for (int i = 0; i < 16; i++) q32[i] = i < S.n_dofs ? (float)q[b * S.n_dofs + i] : 0.f;   // q.float(), :665
+  for (int i = 0; i < 16; i++) q32[i] = i < S.n_dofs ? (float)q[i] : 0.f;                    // q.float(), :665
   float tip[3], Jf[3][CDX_MAX_CHAIN_DOF];
   cdx_fk_finger(hand->finger[f], q32, tip, Jf);
-  const double tlf[3] = {(double)tip[0], (double)tip[1], (double)tip[2]};                   // .double(), :666
+  const double tlf[3] = {(double)tip[0], (double)tip[1], (double)tip[2]};                    // .double(), :666
   double Rw[9], tw[3];
-  cdx_euler_xyz(palm + b * 6 + 3, Rw, nullptr, nullptr, nullptr);
+  cdx_euler_xyz(palm6 + 3, Rw, nullptr, nullptr, nullptr);
   cdx_mv(Rw, tlf, tw);
-  for (int r = 0; r < 3; r++) tw[r] += palm[b * 6 + r];
+  for (int r = 0; r < 3; r++) tw[r] += palm6[r];
+  const int64_t gid = b * 4 + f;
   if (tips_out) {
     for (int r = 0; r < 3; r++) tips_out[gid * 3 + r] = tw[r];
     return;
@@ -71,24 +73,34 @@ pg_points_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg
     tl[gid * 3 + r] = tlf[r];
     for (int c = 0; c < CDX_MAX_CHAIN_DOF; c++) J[(gid * 3 + r) * CDX_MAX_CHAIN_DOF + c] = Jf[r][c];
   }
-  const double* Tf = T + gid * 3;
   int seen = 0;
   for (int p = 0; p < S.P; p++) {
     const int u = S.uniq[p];
     if (u < seen) continue;   // this coefficient row already has its query block
     seen = u + 1;
     double* x = Xext + ((b * U + u) * 4 + f) * 3;
-    for (int r = 0; r < 3; r++) x[r] = Tf[r] + S.coeff[p][f] * (tw[r] - Tf[r]);             // :750
+    for (int r = 0; r < 3; r++) x[r] = Tf[r] + S.coeff[p][f] * (tw[r] - Tf[r]);              // :750
   }
   double* xm = Xmean + b * 27;
   for (int r = 0; r < 3; r++) {
     xm[f * 3 + r] = Tf[r];
     xm[(4 + f) * 3 + r] = tw[r];
-    if (f == 0) xm[24 + r] = palm[b * 6 + r];
+    if (f == 0) xm[24 + r] = palm6[r];
   }
 }
 
-__global__ void pg_tick_kernel(int* it) { *it += 1; }
+__global__ void __launch_bounds__(128)
+pg_points_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_setup S, const double* __restrict__ q,
+                 const double* __restrict__ T, const double* __restrict__ palm, double* __restrict__ tl,
+                 float* __restrict__ J, double* __restrict__ Xext, double* __restrict__ Xmean,
+                 double* __restrict__ tips_out) {
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= B * 4) return;
+  const int64_t b = gid >> 2;
+  pg_emit_points(hand, S, U, b, (int)(gid & 3), q + b * S.n_dofs, T ? T + gid * 3 : nullptr, palm + b * 6, tl, J, Xext,
+                 Xmean, tips_out);
+}
+
 __global__ void pg_fill_kernel(double* p, int64_t n, double v) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -98,76 +110,205 @@ __global__ void pg_fill_kernel(double* p, int64_t n, double v) {
 __device__ __forceinline__ double clamp_lo(double x, double lo) { return x < lo ? lo : x; }
 __device__ __forceinline__ double clamp_hi(double x, double hi) { return x > hi ? hi : x; }
 
-__global__ void __launch_bounds__(64)
-pg_objective_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_setup S, cdx_pregrasp_params prm,
-                    double* __restrict__ q, double* __restrict__ k, double* __restrict__ T, double* __restrict__ palm,
-                    const double* __restrict__ tl, const float* __restrict__ J, const double* __restrict__ dist,
-                    const double* __restrict__ sd, const double* __restrict__ gmu, const double* __restrict__ gsd,
-                    const double* __restrict__ mean9, const double* __restrict__ gmean9, double* __restrict__ loss,
-                    double* __restrict__ margin, double* __restrict__ grad, int do_step, const int* __restrict__ it_dev,
-                    const double* __restrict__ adam_tab, double* __restrict__ m1, double* __restrict__ m2,
-                    double* __restrict__ oq, double* __restrict__ ok, double* __restrict__ oT,
-                    double* __restrict__ opalm, double* __restrict__ omargin, double* __restrict__ ovalue) {
-  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  const int it = *it_dev;
+constexpr int CPB = 16;     // candidates per CTA: 4 lanes each
+constexpr int NRED = 33;    // total | margin 4 | gk 4 | gtips 12 | gT 12
+
+// One closure (+ optional optimiser step) per candidate, spread over a group of 4 lanes:
+//   lane p < P evaluates pregrasp copy p (cdx_pg_row: Kabsch equilibrium, costs, analytic reverse pass) - the copies are
+//   independent given the GPIS outputs - and the weighted sum over copies (:755) is a 2-step shuffle reduction;
+//   lane f then owns finger f: chain rule through the palm transform and the float32 FK Jacobian, its share of the
+//   38 parameters in best-iterate tracking (:822-829), Adam (:831) and the clamps (:833-834), and - when stepping - the FK
+//   and query points of the NEW iterate, so the next iteration needs no separate points launch.
+__global__ void __launch_bounds__(CPB * 4)
+pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_setup S, cdx_pregrasp_params prm,
+               double* __restrict__ q, double* __restrict__ k, double* __restrict__ T, double* __restrict__ palm,
+               double* __restrict__ tl, float* __restrict__ J, const double* __restrict__ dist,
+               const double* __restrict__ sd, const double* __restrict__ gmu, const double* __restrict__ gsd,
+               const double* __restrict__ mean9, const double* __restrict__ gmean9, double* __restrict__ loss,
+               double* __restrict__ margin, double* __restrict__ grad, int do_step, int it,
+               const double* __restrict__ adam_tab, double* __restrict__ m1, double* __restrict__ m2,
+               double* __restrict__ oq, double* __restrict__ ok, double* __restrict__ oT, double* __restrict__ opalm,
+               double* __restrict__ omargin, double* __restrict__ ovalue, double* __restrict__ Xext,
+               double* __restrict__ Xmean) {
+  __shared__ double sp[CPB][NPAR];      // the candidate's parameters: q16 | k4 | T12 | palm6
+  __shared__ double sr[CPB][NRED];      // reduced per-copy results
+  __shared__ double sg[CPB][NPAR];      // gradient
+  const int l = threadIdx.x & 3, cl = threadIdx.x >> 2;
+  const int64_t b = (int64_t)blockIdx.x * CPB + cl;
+  if (b >= B) return;                   // whole 4-lane groups leave together
+  const unsigned gmask = 0xFu << ((threadIdx.x & 31) & ~3);
   const int nd = S.n_dofs;
-  double par[NPAR], g[NPAR];
-  for (int i = 0; i < 16; i++) par[i] = i < nd ? q[b * nd + i] : 0.0;
-  for (int i = 0; i < 4; i++) par[16 + i] = k[b * 4 + i];
-  for (int i = 0; i < 12; i++) par[20 + i] = T[b * 12 + i];
-  for (int i = 0; i < 6; i++) par[32 + i] = palm[b * 6 + i];
-  cdx_pg_gpis G = {dist + b * U * 4, sd + b * U * 4, gmu + b * U * 12, gsd + b * U * 12, mean9 + b * 9, gmean9 + b * 27};
-  const uint64_t seed = prm.noise_seed;
-  const int64_t gb = prm.env_offset + b;
-  auto nf = [=](int p, int e) { return cdx_kabsch_noise(seed, it, p, gb, e); };
-  double total, tm[4];
-  for (int i = 0; i < 16; i++) g[i] = 0.0;
-  cdx_pg_closure(S, *hand, par, par + 16, reinterpret_cast<const double (*)[3]>(par + 20), par + 32,
-                 reinterpret_cast<const double (*)[3]>(tl + b * 12),
-                 reinterpret_cast<const float (*)[3][CDX_MAX_CHAIN_DOF]>(J + b * 12 * CDX_MAX_CHAIN_DOF), G, nf, total, tm,
-                 g, g + 16, reinterpret_cast<double (*)[3]>(g + 20), g + 32);
-  if (loss) loss[b] = total;
-  if (margin) for (int i = 0; i < 4; i++) margin[b * 4 + i] = tm[i];
-  if (grad) for (int i = 0; i < NPAR; i++) grad[b * NPAR + i] = g[i];
-  if (!do_step) return;
-  // best-iterate tracking (:822-829): BEFORE the optimiser step, only for s > track_after; NaN never updates
-  if (it > prm.track_after && total < ovalue[b]) {
-    ovalue[b] = total;
-    for (int i = 0; i < 4; i++) omargin[b * 4 + i] = tm[i];
-    for (int i = 0; i < nd; i++) oq[b * nd + i] = par[i];
-    for (int i = 0; i < 4; i++) ok[b * 4 + i] = par[16 + i];
-    for (int i = 0; i < 12; i++) oT[b * 12 + i] = par[20 + i];
-    for (int i = 0; i < 6; i++) opalm[b * 6 + i] = par[32 + i];
+  double* par = sp[cl];
+  for (int i = l; i < NPAR; i += 4)
+    par[i] = i < 16 ? (i < nd ? q[b * nd + i] : 0.0) : (i < 20 ? k[b * 4 + i - 16] : (i < 32 ? T[b * 12 + i - 20] : palm[b * 6 + i - 32]));
+  for (int i = l; i < 16; i += 4) sg[cl][i] = 0.0;
+  __syncwarp(gmask);
+  const double (*Tp)[3] = reinterpret_cast<const double (*)[3]>(par + 20);
+  const double (*tlp)[3] = reinterpret_cast<const double (*)[3]>(tl + b * 12);
+  double Rw[9], dR0[9], dR1[9], dR2[9], tips[4][3];
+  cdx_euler_xyz(par + 35, Rw, dR0, dR1, dR2);
+#pragma unroll
+  for (int f = 0; f < 4; f++) {
+    cdx_mv(Rw, tlp[f], tips[f]);
+    for (int r = 0; r < 3; r++) tips[f][r] += par[32 + r];
   }
-  // torch.optim.Adam (:796,:831): exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2 v + (1-b2) g^2;
-  // p -= (lr / (1-b1^t)) * m / (sqrt(v)/sqrt(1-b2^t) + eps)
+  double refn = 0.0;
+  for (int i = l; i < nd; i += 4) refn += (par[i] - S.ref_q[i]) * (par[i] - S.ref_q[i]);
+  refn += __shfl_xor_sync(gmask, refn, 1);
+  refn += __shfl_xor_sync(gmask, refn, 2);
+  refn = sqrt(refn);
+  const double* m9 = mean9 + b * 9;
+  const double* g9 = gmean9 + b * 27;
+  // ---- copy p = l
+  double red[NRED];
+#pragma unroll
+  for (int i = 0; i < NRED; i++) red[i] = 0.0;
+  double wsum = 0.0;
+  for (int p = 0; p < S.P; p++) wsum += S.weight[p];
+  if (l < S.P) {
+    const int p = l, u = S.uniq[p];
+    double a[4][3], noise[9], lossp, mg[4], ga[4][3], gTr[4][3], gkr[4];
+#pragma unroll
+    for (int f = 0; f < 4; f++)
+      for (int r = 0; r < 3; r++) a[f][r] = Tp[f][r] + S.coeff[p][f] * (tips[f][r] - Tp[f][r]);
+    const int64_t gb = prm.env_offset + b;
+#pragma unroll
+    for (int e = 0; e < 9; e++) noise[e] = cdx_kabsch_noise(prm.noise_seed, it, p, gb, e);
+    const int64_t e0 = (b * U + u) * 4;
+    cdx_pg_row(a, Tp, par + 16, dist + e0, sd + e0, reinterpret_cast<const double (*)[3]>(gmu + e0 * 3),
+               reinterpret_cast<const double (*)[3]>(gsd + e0 * 3), m9, reinterpret_cast<const double (*)[3]>(g9), noise, S.C,
+               lossp, mg, ga, gTr, gkr);
+    const double wp = S.weight[p];
+    red[0] = wp * (lossp + 10.0 * refn);
+#pragma unroll
+    for (int f = 0; f < 4; f++) {
+      red[1 + f] = wp * mg[f];
+      red[5 + f] = wp * gkr[f];
+      const double c = S.coeff[p][f];
+      for (int r = 0; r < 3; r++) {
+        red[9 + f * 3 + r] = wp * c * ga[f][r];
+        red[21 + f * 3 + r] = wp * ((1.0 - c) * ga[f][r] + gTr[f][r]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NRED; i++) {
+    double v = red[i];
+    v += __shfl_xor_sync(gmask, v, 1);
+    v += __shfl_xor_sync(gmask, v, 2);
+    red[i] = v;
+  }
+  if (l == 0)
+    for (int i = 0; i < NRED; i++) sr[cl][i] = red[i];
+  __syncwarp(gmask);
+  // ---- :757-763 and the chain rule of finger f = l
+  double total = red[0];
+  for (int f = 0; f < 4; f++) total -= 5.0 * m9[4 + f];
+  double gpalm_pm[3] = {0.0, 0.0, 0.0};
+  if (S.optimize_palm) {
+    const double pm = m9[8];
+    total += 1.0 / pm;
+    for (int r = 0; r < 3; r++) gpalm_pm[r] = -g9[24 + r] / (pm * pm);
+  }
+  const int f = l;
+  double gt[3], gl[3], acc[12];
+  for (int r = 0; r < 3; r++) gt[r] = sr[cl][9 + f * 3 + r] - 5.0 * g9[(4 + f) * 3 + r];
+  cdx_mtv(Rw, gt, gl);
+  for (int r = 0; r < 3; r++) {
+    acc[r] = gt[r];
+    for (int c = 0; c < 3; c++) acc[3 + r * 3 + c] = gt[r] * tlp[f][c];
+  }
+#pragma unroll
+  for (int i = 0; i < 12; i++) {
+    acc[i] += __shfl_xor_sync(gmask, acc[i], 1);
+    acc[i] += __shfl_xor_sync(gmask, acc[i], 2);
+  }
+  // back through .double() (:666) into the float32 FK graph; fingers take turns so shared joints would accumulate
+  const float g32[3] = {(float)gl[0], (float)gl[1], (float)gl[2]};
+  const cdx_chain& ch = hand->finger[f];
+  const float* Jf = J + (b * 4 + f) * 3 * CDX_MAX_CHAIN_DOF;
+  for (int turn = 0; turn < 4; turn++) {
+    if (turn == f)
+      for (int c = 0; c < ch.ndof; c++) {
+        const float gj = Jf[c] * g32[0] + Jf[CDX_MAX_CHAIN_DOF + c] * g32[1] + Jf[2 * CDX_MAX_CHAIN_DOF + c] * g32[2];
+        sg[cl][ch.dofs[c]] += (double)gj;
+      }
+    __syncwarp(gmask);
+  }
+  double* g = sg[cl];
+  for (int i = l; i < nd; i += 4) g[i] += refn > 0.0 ? wsum * 10.0 * (par[i] - S.ref_q[i]) / refn : 0.0;
+  g[16 + f] = sr[cl][5 + f];
+  for (int r = 0; r < 3; r++) g[20 + f * 3 + r] = sr[cl][21 + f * 3 + r];
+  for (int i = l; i < 6; i += 4) {
+    double v;
+    if (i < 3) v = acc[i] + gpalm_pm[i];
+    else {
+      const double* dR = i == 3 ? dR0 : (i == 4 ? dR1 : dR2);
+      v = 0.0;
+      for (int e = 0; e < 9; e++) v += acc[3 + e] * dR[e];
+    }
+    g[32 + i] = v;
+  }
+  __syncwarp(gmask);
+  if (l == 0) {
+    if (loss) loss[b] = total;
+    if (margin) for (int i = 0; i < 4; i++) margin[b * 4 + i] = sr[cl][1 + i];
+  }
+  if (grad) for (int i = l; i < NPAR; i += 4) grad[b * NPAR + i] = g[i];
+  if (!do_step) return;
+  // ---- best-iterate tracking (:822-829): BEFORE the optimiser step, only for s > track_after; NaN never updates
+  const bool better = it > prm.track_after && total < ovalue[b];
+  __syncwarp(gmask);                                    // every lane has read ovalue[b] before lane 0 overwrites it
+  if (better) {
+    if (l == 0) {
+      ovalue[b] = total;
+      for (int i = 0; i < 4; i++) omargin[b * 4 + i] = sr[cl][1 + i];
+    }
+    for (int i = l; i < NPAR; i += 4) {
+      const double v = par[i];
+      if (i < 16) { if (i < nd) oq[b * nd + i] = v; }
+      else if (i < 20) ok[b * 4 + i - 16] = v;
+      else if (i < 32) oT[b * 12 + i - 20] = v;
+      else opalm[b * 6 + i - 32] = v;
+    }
+  }
+  // ---- torch.optim.Adam (:796,:831): exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2 v + (1-b2) g^2;
+  //      p -= (lr / (1-b1^t)) * m / (sqrt(v)/sqrt(1-b2^t) + eps);  then the clamps (:833-834)
   const double bc1 = adam_tab[2 * it], bc2s = adam_tab[2 * it + 1];
   const double omb1 = 1.0 - prm.beta1, omb2 = 1.0 - prm.beta2;
-  for (int i = 0; i < NPAR; i++) {
+  for (int i = l; i < NPAR; i += 4) {
     int grp;
-    if (i < 16) { if (i >= nd) continue; grp = 0; }
+    bool upd = true;
+    if (i < 16) { upd = i < nd; grp = 0; }
     else if (i < 20) grp = 1;
-    else if (i < 32) { if (!prm.optimize_target) continue; grp = 2; }
-    else { if (!prm.optimize_palm) continue; grp = i < 35 ? 3 : 4; }
-    const double gi = g[i];
-    double m = m1[b * NPAR + i], v = m2[b * NPAR + i];
-    m = m + omb1 * (gi - m);
-    v = v * prm.beta2 + omb2 * gi * gi;
-    m1[b * NPAR + i] = m;
-    m2[b * NPAR + i] = v;
-    const double step = prm.lr[grp] / bc1;
-    const double denom = sqrt(v) / bc2s + prm.eps;
-    par[i] = par[i] - step * (m / denom);
+    else if (i < 32) { upd = prm.optimize_target != 0; grp = 2; }
+    else { upd = prm.optimize_palm != 0; grp = i < 35 ? 3 : 4; }
+    double pv = par[i];
+    if (upd) {
+      const double gi = g[i];
+      double m = m1[b * NPAR + i], v = m2[b * NPAR + i];
+      m = m + omb1 * (gi - m);
+      v = v * prm.beta2 + omb2 * gi * gi;
+      m1[b * NPAR + i] = m;
+      m2[b * NPAR + i] = v;
+      const double step = prm.lr[grp] / bc1;
+      const double denom = sqrt(v) / bc2s + prm.eps;
+      pv = pv - step * (m / denom);
+    }
+    if (i >= 16 && i < 20) pv = clamp_lo(pv, prm.compliance_min);
+    if (i >= 20 && i < 32) {
+      const int e = i - 20;
+      pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[e / 3][e % 3]), (double)prm.box_hi[e / 3][e % 3]);
+    }
+    par[i] = pv;
+    if (i < 16) { if (i < nd) q[b * nd + i] = pv; }
+    else if (i < 20) k[b * 4 + i - 16] = pv;
+    else if (i < 32) T[b * 12 + i - 20] = pv;
+    else palm[b * 6 + i - 32] = pv;
   }
-  for (int i = 0; i < 4; i++) par[16 + i] = clamp_lo(par[16 + i], prm.compliance_min);           // :833
-  for (int f = 0; f < 4; f++)
-    for (int r = 0; r < 3; r++)                                                                 // :834 (always applied)
-      par[20 + f * 3 + r] = clamp_hi(clamp_lo(par[20 + f * 3 + r], (double)prm.box_lo[f][r]), (double)prm.box_hi[f][r]);
-  for (int i = 0; i < nd; i++) q[b * nd + i] = par[i];
-  for (int i = 0; i < 4; i++) k[b * 4 + i] = par[16 + i];
-  for (int i = 0; i < 12; i++) T[b * 12 + i] = par[20 + i];
-  for (int i = 0; i < 6; i++) palm[b * 6 + i] = par[32 + i];
+  __syncwarp(gmask);
+  // ---- FK + GPIS query points of the NEW iterate (what pg_points_kernel does for the first iteration)
+  pg_emit_points(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
 }
 
 // arg-min with lowest-index tie-break over opt_value (NaN / inf never win unless everything is)
@@ -215,7 +356,8 @@ static void pg_free_buffers(cdx_pg_state* s) {
 void cdx_pregrasp_free(cdx_ctx* ctx) {
   if (!ctx || !ctx->pg) return;
   pg_free_buffers(ctx->pg);
-  cudaFree(ctx->pg->it_dev);
+  if (ctx->pg->side) { cudaStreamDestroy(ctx->pg->side); cudaEventDestroy(ctx->pg->ev_fork); cudaEventDestroy(ctx->pg->ev_join); }
+  for (cudaEvent_t e : ctx->pg->prof_ev) cudaEventDestroy(e);
   cudaFree(ctx->pg->adam_tab);
   cudaFree(ctx->pg->hand_dev);
   delete ctx->pg;
@@ -315,7 +457,11 @@ extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int
     s->cap = B;
     s->U = U;
   }
-  if (!s->it_dev) PG_ALLOC(s->it_dev, 1);
+  if (!s->side) {
+    CDX_CUDA(cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking));
+    CDX_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
+    CDX_CUDA(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+  }
   s->B = B;
   CDX_CUDA(cudaMemcpyAsync(s->q, q0, sizeof(double) * B * nd, cudaMemcpyDeviceToDevice, st));
   CDX_CUDA(cudaMemcpyAsync(s->k, k0, sizeof(double) * B * 4, cudaMemcpyDeviceToDevice, st));
@@ -329,43 +475,52 @@ extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int
   CDX_CUDA(cudaMemsetAsync(s->omargin, 0, sizeof(double) * B * 4, st));
   CDX_CUDA(cudaMemsetAsync(s->m1, 0, sizeof(double) * B * NPAR, st));
   CDX_CUDA(cudaMemsetAsync(s->m2, 0, sizeof(double) * B * NPAR, st));
-  CDX_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), st));
   pg_fill_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(s->ovalue, B, INFINITY);
   CDX_CHECK_LAUNCH(ctx);
   s->it_host = 0;
+  s->points_valid = false;
   return CDX_OK;
 }
 
-// one closure evaluation: points -> GPIS queries -> objective (+ optional optimiser step)
+// one closure evaluation: (points of the initial iterate) -> GPIS queries (extended on `st`, mean-only overlapped on the
+// side stream) -> step kernel (objective + gradient, optionally Adam + points of the new iterate)
 static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss, double* margin, double* grad,
                         cudaStream_t st) {
   const int64_t B = s->B;
   const int U = s->U;
   const bool prof = s->prof && do_step;
-  auto mark = [&]() {
+  auto mark = [&](cudaStream_t on) {
     if (!prof) return;
     cudaEvent_t e;
     cudaEventCreate(&e);
-    cudaEventRecord(e, st);
+    cudaEventRecord(e, on);
     s->prof_ev.push_back(e);
   };
-  mark();
-  pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(s->hand_dev, B, U, s->setup, s->q, s->T, s->palm, s->tl,
-                                                                  s->J, s->Xext, s->Xmean, nullptr);
-  CDX_CHECK_LAUNCH(ctx);
-  mark();
+  if (!s->points_valid) {
+    pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(s->hand_dev, B, U, s->setup, s->q, s->T, s->palm, s->tl,
+                                                                    s->J, s->Xext, s->Xmean, nullptr);
+    CDX_CHECK_LAUNCH(ctx);
+    s->points_valid = true;
+  }
+  CDX_CUDA(cudaEventRecord(s->ev_fork, st));
+  CDX_CUDA(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
+  mark(st);
   int rc = cdx_gpis_query(ctx, s->Xext, B * U * 4, s->dist, s->gmu, s->sd, s->gsd, (void*)st);
   if (rc) return rc;
-  mark();
-  rc = cdx_gpis_query(ctx, s->Xmean, B * 9, s->mean9, s->gmean9, nullptr, nullptr, (void*)st);
+  mark(st);
+  mark(s->side);
+  rc = cdx_gpis_query(ctx, s->Xmean, B * 9, s->mean9, s->gmean9, nullptr, nullptr, (void*)s->side);
   if (rc) return rc;
-  mark();
-  pg_objective_kernel<<<(unsigned)((B + 63) / 64), 64, 0, st>>>(
+  mark(s->side);
+  CDX_CUDA(cudaEventRecord(s->ev_join, s->side));
+  CDX_CUDA(cudaStreamWaitEvent(st, s->ev_join, 0));
+  mark(st);
+  pg_step_kernel<<<(unsigned)((B + CPB - 1) / CPB), CPB * 4, 0, st>>>(
       s->hand_dev, B, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd, s->mean9,
-      s->gmean9, loss, margin, grad, do_step, s->it_dev, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,
-      s->omargin, s->ovalue);
+      s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,
+      s->omargin, s->ovalue, s->Xext, s->Xmean);
   CDX_CHECK_LAUNCH(ctx);
-  mark();
+  mark(st);
   return CDX_OK;
 }
 
@@ -405,10 +560,8 @@ extern "C" int cdx_pregrasp_run(cdx_ctx* ctx, int n_iters, void* stream) {
   for (int i = 0; i < n_iters; i++) {
     rc = pg_iteration(ctx, s, 1, s->loss, s->margin, nullptr, st);
     if (rc) return rc;
-    pg_tick_kernel<<<1, 1, 0, st>>>(s->it_dev);
-    CDX_CHECK_LAUNCH(ctx);
+    s->it_host++;
   }
-  s->it_host += n_iters;
   return CDX_OK;
 }
 
@@ -481,11 +634,13 @@ extern "C" int cdx_pregrasp_profile_read(cdx_ctx* ctx, double* ms_out4, int* n_i
   CDX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   cdx_pg_state* s = ctx->pg;
   for (int k = 0; k < 4; k++) ms_out4[k] = 0.0;
-  const size_t n = s->prof_ev.size() / 5;
+  // per iteration: [0] before ext, [1] after ext (main) | [2] before mean, [3] after mean (side) | [4] before step, [5] after
+  const size_t n = s->prof_ev.size() / 6;
+  const int pairs[4][2] = {{1, 4}, {0, 1}, {2, 3}, {4, 5}};   // wait for the mean query after ext | ext | mean | step
   for (size_t i = 0; i < n; i++)
     for (int k = 0; k < 4; k++) {
       float ms = 0.f;
-      CDX_CUDA(cudaEventElapsedTime(&ms, s->prof_ev[i * 5 + k], s->prof_ev[i * 5 + k + 1]));
+      CDX_CUDA(cudaEventElapsedTime(&ms, s->prof_ev[i * 6 + pairs[k][0]], s->prof_ev[i * 6 + pairs[k][1]]));
       ms_out4[k] += (double)ms;
     }
   for (cudaEvent_t e : s->prof_ev) cudaEventDestroy(e);

@@ -11,13 +11,14 @@
 
 namespace {
 
-constexpr int TQ = 128;   // queries per CTA
+// queries per CTA (TQ) is a template parameter: 128 for throughput (one 512-thread CTA per SM), 32 when the batch is too
+// small to fill the chip with 128-query tiles (the pregrasp loop: a few thousand queries per launch)
 constexpr int TK = 16;    // training points per k-chunk
 constexpr int LDS = 20;   // shared-memory row stride (doubles): conflict-free for lane -> (row = T/4, k = T%4)
 constexpr int NA = 3, NB = 4;  // ring depths: generated k* tiles / cp.async tiles of U or P
 
-template <int KERNEL, int TN, bool EXT>
-__global__ void __launch_bounds__(512, 1)
+template <int KERNEL, int TN, bool EXT, int TQ>
+__global__ void __launch_bounds__(TQ * 4, TQ == 128 ? 1 : (TN == 64 ? 3 : 2))
 gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restrict__ Xa, const double* __restrict__ Bmat,
                 int N, int Np, cdx_kparams kp, double bias, double prior, double* __restrict__ mean,
                 double* __restrict__ gmean, double* __restrict__ stdv, double* __restrict__ gstd) {
@@ -33,7 +34,8 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
   const int wm = warp >> 2, wn = warp & 3;
   const int64_t q0 = (int64_t)blockIdx.x * TQ;
 
-  for (int e = t; e < TQ * 3; e += 512) {
+  constexpr int NTHR = TQ * 4;
+  for (int e = t; e < TQ * 3; e += NTHR) {
     int64_t q = q0 + e / 3;
     sxq[e] = q < M ? Xq[q * 3 + e % 3] : 0.0;
   }
@@ -53,7 +55,7 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
 
   auto issueB = [&](int n0, int c, int buf) {
     double* dst = Bs + buf * TN * LDS;
-    for (int p = t; p < TN * 8; p += 512) {
+    for (int p = t; p < TN * 8; p += NTHR) {
       int row = p >> 3, seg = p & 7;
       double* d = dst + row * LDS + seg * 2;
       if (n0 + row < Np) cdx_cp_async16(d, Bmat + (int64_t)(n0 + row) * Np + c * TK + seg * 2);
@@ -307,18 +309,18 @@ int launch_mean(cdx_ctx* ctx, const double* Xa, const double* X, int64_t M, doub
   return CDX_OK;
 }
 
-template <int KERNEL, int TN, bool EXT>
+template <int KERNEL, int TN, bool EXT, int TQ>
 int launch_var(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
                cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
   size_t smem = sizeof(double) * (size_t)(NA * TQ * LDS + NB * TN * LDS + TQ * 3 + 4 * TQ * 4);
   static bool attr_set = false;
   if (!attr_set) {
-    CDX_CUDA(cudaFuncSetAttribute(gpis_var_kernel<KERNEL, TN, EXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CDX_CUDA(cudaFuncSetAttribute(gpis_var_kernel<KERNEL, TN, EXT, TQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   int64_t grid = (M + TQ - 1) / TQ;
-  gpis_var_kernel<KERNEL, TN, EXT><<<(unsigned)grid, 512, smem, st>>>(X, M, g.Xa, EXT ? g.P : g.U, (int)g.N, (int)g.Np,
+  gpis_var_kernel<KERNEL, TN, EXT, TQ><<<(unsigned)grid, TQ * 4, smem, st>>>(X, M, g.Xa, EXT ? g.P : g.U, (int)g.N, (int)g.Np,
                                                                       cdx_make_kparams(g), g.bias, g.prior, mean, gmean,
                                                                       stdv, gstd);
   CDX_CHECK_LAUNCH(ctx);
@@ -330,10 +332,22 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
                    cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
   const bool big = (g.Np % 128 == 0) && g.Np >= 512;
-  if (gstd) return big ? launch_var<KERNEL, 128, true>(ctx, X, M, mean, gmean, stdv, gstd, st)
-                       : launch_var<KERNEL, 64, true>(ctx, X, M, mean, gmean, stdv, gstd, st);
-  if (stdv) return big ? launch_var<KERNEL, 128, false>(ctx, X, M, mean, gmean, stdv, nullptr, st)
-                       : launch_var<KERNEL, 64, false>(ctx, X, M, mean, gmean, stdv, nullptr, st);
+  // fewer 128-query tiles than SMs: spread the batch over the chip with 32-query CTAs (3 resident per SM)
+  const bool small_batch = (M + 127) / 128 < (int64_t)ctx->sms;
+  // the column tile TN depends on the state only, never on the batch size: a query's result is then bit-identical
+  // whichever TQ variant (or shard) evaluates it
+  if (gstd) {
+    if (small_batch) return big ? launch_var<KERNEL, 128, true, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
+                                : launch_var<KERNEL, 64, true, 32>(ctx, X, M, mean, gmean, stdv, gstd, st);
+    return big ? launch_var<KERNEL, 128, true, 128>(ctx, X, M, mean, gmean, stdv, gstd, st)
+               : launch_var<KERNEL, 64, true, 128>(ctx, X, M, mean, gmean, stdv, gstd, st);
+  }
+  if (stdv) {
+    if (small_batch) return big ? launch_var<KERNEL, 128, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st)
+                                : launch_var<KERNEL, 64, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st);
+    return big ? launch_var<KERNEL, 128, false, 128>(ctx, X, M, mean, gmean, stdv, nullptr, st)
+               : launch_var<KERNEL, 64, false, 128>(ctx, X, M, mean, gmean, stdv, nullptr, st);
+  }
   return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
 }
 
