@@ -97,6 +97,8 @@ def dist_setup(args):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"          # NCCL prints its version banner to STDOUT; keep stdout = one JSON line
         backend = "nccl" if args.impl == "cdx" else "gloo"
         if args.impl == "cdx":
             torch.cuda.set_device(local)
