@@ -7,7 +7,10 @@
 //                          |v|^2 reduced in the epilogue; nothing of size N per query ever reaches HBM.   N^2 + 26 N flop
 //  * gpis_var_kernel<EXT=1> extended query (+ grad_std): w = E11^-1 k* with the full inverse, epilogue forms
 //                          var = k(x,x) - k*.w and grad var = -2 sum_i w_i c_i (x - x_i).                 2 N^2 + 34 N flop
+#include <cooperative_groups.h>
 #include "cdx_internal.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -18,16 +21,20 @@ constexpr int LDS = 20;   // shared-memory row stride (doubles): conflict-free f
 constexpr int NA = 3, NB = 4;  // ring depths: generated k* tiles / cp.async tiles of U or P
 
 template <int KERNEL, int TN, bool EXT, int TQ>
-__global__ void __launch_bounds__(TQ * 4, TQ == 128 ? 1 : (TN == 64 ? 3 : 2))
+__global__ void __launch_bounds__(TQ * 4, TQ == 128 ? 1 : (TN == 64 ? 4 : 2))
 gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restrict__ Xa, const double* __restrict__ Bmat,
                 int N, int Np, cdx_kparams kp, double bias, double prior, double* __restrict__ mean,
-                double* __restrict__ gmean, double* __restrict__ stdv, double* __restrict__ gstd) {
+                double* __restrict__ gmean, double* __restrict__ stdv, double* __restrict__ gstd, int csplit) {
   constexpr int WN = TN / 4, NBW = WN / 8;
+  // 32-query CTAs use a 3-deep ring for the matrix tiles (4 CTAs of 52 KB per SM: the 4 x 128 CTAs of the pregrasp batch are
+  // all resident at once); the tile for chunk c+2 is then requested AFTER the barrier of chunk c, when its slot is free
+  constexpr int NBq = TQ == 32 ? 3 : NB;
   extern __shared__ __align__(16) double smem[];
   double* As = smem;                          // [NA][TQ*LDS]
-  double* Bs = As + NA * TQ * LDS;            // [NB][TN*LDS]
-  double* sxq = Bs + NB * TN * LDS;           // [TQ][3]
+  double* Bs = As + NA * TQ * LDS;            // [NBq][TN*LDS]
+  double* sxq = Bs + NBq * TN * LDS;          // [TQ][3]
   double* red = sxq + TQ * 3;                 // [4][TQ][4]
+  double* tot = red + 4 * TQ * 4;             // [TQ][4] running sum of the per-n-tile partials (fixed order)
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int fr = lane >> 2, fk = lane & 3;
@@ -45,10 +52,6 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
   const double xq = sxq[qg * 3], yq = sxq[qg * 3 + 1], zq = sxq[qg * 3 + 2];
   double m_acc = 0.0, gx = 0.0, gy = 0.0, gz = 0.0;
 
-  double ss[4];          // !EXT: sum v^2 per owned row
-  double ev[4][4];       // EXT: (k.w, w c dx, w c dy, w c dz) per owned row
-#pragma unroll
-  for (int i = 0; i < 4; i++) { ss[i] = 0.0; ev[i][0] = ev[i][1] = ev[i][2] = ev[i][3] = 0.0; }
 
   const int NT = (Np + TN - 1) / TN;
   const double2* Xa2 = reinterpret_cast<const double2*>(Xa);
@@ -82,9 +85,20 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
     }
   };
 
-  for (int nt = NT - 1; nt >= 0; nt--) {
+  // n-tiles are visited in DESCENDING order; with csplit > 1 (a thread-block cluster of csplit == NT CTAs along y) CTA
+  // rank r owns the single tile NT-1-r and rank 0 adds the partials in rank order over distributed shared memory, which is
+  // the same association as the sequential loop: a query's result does not depend on the variant that computed it.
+  const int crank = csplit > 1 ? (int)cg::this_cluster().block_rank() : 0;
+  bool first_tile = true;
+  for (int nt = NT - 1 - crank; nt >= 0; nt -= csplit) {
     const int n0 = nt * TN;
-    const int kmax = EXT ? Np : min(Np, n0 + TN);
+    double ss[4];          // !EXT: sum v^2 per owned row (this tile)
+    double ev[4][4];       // EXT: (k.w, w c dx, w c dy, w c dz) per owned row (this tile)
+#pragma unroll
+    for (int i = 0; i < 4; i++) { ss[i] = 0.0; ev[i][0] = ev[i][1] = ev[i][2] = ev[i][3] = 0.0; }
+    // training rows >= N are padding (k* = 0, identity rows of the factor): whole chunks of them contribute exact zeros
+    const int kpad = (N + TK - 1) / TK * TK;
+    const int kmax = EXT ? kpad : min(kpad, n0 + TN);
     const int nch = kmax / TK;
     const bool meanpass = (nt == NT - 1);
     double acc[4][NBW][2];
@@ -99,13 +113,19 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
     cdx_cp_async_commit();
     genA(0, 0, meanpass);
     for (int c = 0; c < nch; c++) {
-      if (c + 2 < nch) issueB(n0, c + 2, (c + 2) % NB);
-      cdx_cp_async_commit();
+      if (NBq == NB) {
+        if (c + 2 < nch) issueB(n0, c + 2, (c + 2) % NBq);
+        cdx_cp_async_commit();
+      }
       if (c + 1 < nch) genA(c + 1, (c + 1) % NA, meanpass);
-      cdx_cp_async_wait<2>();
+      if (NBq == NB) cdx_cp_async_wait<2>(); else cdx_cp_async_wait<1>();
       __syncthreads();
+      if (NBq != NB) {
+        if (c + 2 < nch) issueB(n0, c + 2, (c + 2) % NBq);
+        cdx_cp_async_commit();
+      }
       const double* a_s = As + (c % NA) * TQ * LDS + (wm * 32 + fr) * LDS + fk;
-      const double* b_s = Bs + (c % NB) * TN * LDS + (wn * WN + fr) * LDS + fk;
+      const double* b_s = Bs + (c % NBq) * TN * LDS + (wn * WN + fr) * LDS + fk;
 #pragma unroll
       for (int ks = 0; ks < TK; ks += 4) {
         double a[4], b[NBW];
@@ -148,42 +168,57 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
           }
       }
     }
-    __syncthreads();  // all warps done with the rings before the next n-tile refills them
-  }
-
-  // mean / grad_mean: reduce over the 4 lanes that share a query row
-  m_acc += __shfl_xor_sync(0xffffffffu, m_acc, 1); m_acc += __shfl_xor_sync(0xffffffffu, m_acc, 2);
-  gx += __shfl_xor_sync(0xffffffffu, gx, 1); gx += __shfl_xor_sync(0xffffffffu, gx, 2);
-  gy += __shfl_xor_sync(0xffffffffu, gy, 1); gy += __shfl_xor_sync(0xffffffffu, gy, 2);
-  gz += __shfl_xor_sync(0xffffffffu, gz, 1); gz += __shfl_xor_sync(0xffffffffu, gz, 2);
-  if (fk == 0 && q0 + qg < M) {
-    if (mean) mean[q0 + qg] = m_acc + bias;
-    if (gmean) { gmean[(q0 + qg) * 3] = gx; gmean[(q0 + qg) * 3 + 1] = gy; gmean[(q0 + qg) * 3 + 2] = gz; }
-  }
-  // variance terms: quad reduce, then across the 4 column-warps through shared memory (fixed order: deterministic)
+    // this tile's partial: quad reduce, then across the 4 column-warps through shared memory in a fixed order
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const int r = wm * 32 + i * 8 + fr;
-    if (!EXT) {
-      double s = ss[i];
-      s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
-      if (fk == 0) red[(wn * TQ + r) * 4] = s;
-    } else {
-#pragma unroll
-      for (int e = 0; e < 4; e++) {
-        double s = ev[i][e];
+    for (int i = 0; i < 4; i++) {
+      const int r = wm * 32 + i * 8 + fr;
+      if (!EXT) {
+        double s = ss[i];
         s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
-        if (fk == 0) red[(wn * TQ + r) * 4 + e] = s;
+        if (fk == 0) red[(wn * TQ + r) * 4] = s;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          double s = ev[i][e];
+          s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
+          if (fk == 0) red[(wn * TQ + r) * 4 + e] = s;
+        }
       }
     }
+    __syncthreads();  // partials visible; all warps done with the rings before the next n-tile refills them
+    if (t < TQ) {
+#pragma unroll
+      for (int e = 0; e < (EXT ? 4 : 1); e++) {
+        const double pv = (red[(0 * TQ + t) * 4 + e] + red[(1 * TQ + t) * 4 + e]) + (red[(2 * TQ + t) * 4 + e] + red[(3 * TQ + t) * 4 + e]);
+        tot[t * 4 + e] = first_tile ? pv : tot[t * 4 + e] + pv;
+      }
+    }
+    first_tile = false;
+    __syncthreads();  // red is rewritten by the next tile
   }
-  __syncthreads();
-  if (t < TQ && q0 + t < M) {
+
+  // mean / grad_mean (accumulated by the CTA that owns the last n-tile): reduce over the 4 lanes that share a query row
+  if (crank == 0) {
+    m_acc += __shfl_xor_sync(0xffffffffu, m_acc, 1); m_acc += __shfl_xor_sync(0xffffffffu, m_acc, 2);
+    gx += __shfl_xor_sync(0xffffffffu, gx, 1); gx += __shfl_xor_sync(0xffffffffu, gx, 2);
+    gy += __shfl_xor_sync(0xffffffffu, gy, 1); gy += __shfl_xor_sync(0xffffffffu, gy, 2);
+    gz += __shfl_xor_sync(0xffffffffu, gz, 1); gz += __shfl_xor_sync(0xffffffffu, gz, 2);
+    if (fk == 0 && q0 + qg < M) {
+      if (mean) mean[q0 + qg] = m_acc + bias;
+      if (gmean) { gmean[(q0 + qg) * 3] = gx; gmean[(q0 + qg) * 3 + 1] = gy; gmean[(q0 + qg) * 3 + 2] = gz; }
+    }
+  }
+  if (csplit > 1) cg::this_cluster().sync();   // every rank's `tot` is complete and visible cluster-wide
+  if (crank == 0 && t < TQ && q0 + t < M) {
     const int64_t q = q0 + t;
     double v[4];
 #pragma unroll
-    for (int e = 0; e < (EXT ? 4 : 1); e++)
-      v[e] = (red[(0 * TQ + t) * 4 + e] + red[(1 * TQ + t) * 4 + e]) + (red[(2 * TQ + t) * 4 + e] + red[(3 * TQ + t) * 4 + e]);
+    for (int e = 0; e < (EXT ? 4 : 1); e++) v[e] = tot[t * 4 + e];
+    for (int r = 1; r < csplit; r++) {           // rank r holds tile NT-1-r: descending-tile order, as the sequential loop
+      const double* rt = cg::this_cluster().map_shared_rank(tot, r);
+#pragma unroll
+      for (int e = 0; e < (EXT ? 4 : 1); e++) v[e] += rt[t * 4 + e];
+    }
     double var = prior - v[0];
     double sd = sqrt(fabs(var));  // gpis.py:59
     if (stdv) stdv[q] = sd;
@@ -193,6 +228,7 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
       gstd[q * 3] = f * v[1]; gstd[q * 3 + 1] = f * v[2]; gstd[q * 3 + 2] = f * v[3];
     }
   }
+  if (csplit > 1) cg::this_cluster().sync();   // remote shared memory stays alive until rank 0 has read it
 }
 
 // ------------------------------------------------------------------------------------------ mean only
@@ -313,16 +349,32 @@ template <int KERNEL, int TN, bool EXT, int TQ>
 int launch_var(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
                cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
-  size_t smem = sizeof(double) * (size_t)(NA * TQ * LDS + NB * TN * LDS + TQ * 3 + 4 * TQ * 4);
+  size_t smem = sizeof(double) * (size_t)(NA * TQ * LDS + (TQ == 32 ? 3 : NB) * TN * LDS + TQ * 3 + 4 * TQ * 4 + TQ * 4);
   static bool attr_set = false;
   if (!attr_set) {
     CDX_CUDA(cudaFuncSetAttribute(gpis_var_kernel<KERNEL, TN, EXT, TQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  int64_t grid = (M + TQ - 1) / TQ;
-  gpis_var_kernel<KERNEL, TN, EXT, TQ><<<(unsigned)grid, TQ * 4, smem, st>>>(X, M, g.Xa, EXT ? g.P : g.U, (int)g.N, (int)g.Np,
-                                                                      cdx_make_kparams(g), g.bias, g.prior, mean, gmean,
-                                                                      stdv, gstd);
+  const int64_t grid = (M + TQ - 1) / TQ;
+  const int NT = (int)((g.Np + TN - 1) / TN);
+  // small batch and few column tiles: one CTA per (query tile, column tile), the column tiles of a query tile forming a
+  // thread-block cluster that reduces over distributed shared memory
+  const int csplit = (TQ == 32 && NT >= 2 && NT <= 8 && grid * NT <= 8 * (int64_t)ctx->sms) ? NT : 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, (unsigned)csplit, 1);
+  cfg.blockDim = dim3(TQ * 4, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = (unsigned)csplit;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = csplit > 1 ? 1 : 0;
+  const double* Bm = EXT ? g.P : g.U;
+  CDX_CUDA(cudaLaunchKernelEx(&cfg, gpis_var_kernel<KERNEL, TN, EXT, TQ>, X, M, (const double*)g.Xa, Bm, (int)g.N, (int)g.Np,
+                              cdx_make_kparams(g), g.bias, g.prior, mean, gmean, stdv, gstd, csplit));
   CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
 }
