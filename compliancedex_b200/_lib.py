@@ -49,6 +49,7 @@ SIGNATURES = {
     "cdx_gpis_info": (c_int, [c_void_p, ctypes.POINTER(c_i64), ctypes.POINTER(c_double), ctypes.POINTER(c_double),
                               ctypes.POINTER(c_double), ctypes.POINTER(c_int), c_void_p]),
     "cdx_gpis_query": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cdx_gpis_set_var_mode": (c_int, [c_void_p, c_int]),
     "cdx_gpis_query_host": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_gpis_query_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p]),
     "cdx_hand_load": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),

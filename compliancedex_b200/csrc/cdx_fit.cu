@@ -191,6 +191,7 @@ int gpis_reserve(cdx_ctx* ctx, int64_t N) {
   g.N = N;
   g.Np = Np;
   g.ready = false;
+  g.i8_S = 0;   // the sliced copy of U belongs to the previous state
   return CDX_OK;
 }
 
@@ -299,6 +300,7 @@ extern "C" int cdx_destroy(cdx_ctx* ctx) {
   cudaFree(g.Xa); cudaFree(g.y1); cudaFree(g.E11); cudaFree(g.L); cudaFree(g.U); cudaFree(g.P);
   cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.dR2); cudaFree(g.flag);
   cudaFree(ctx->hx); cudaFree(ctx->hout);
+  cdx_i8_free(ctx);
   cdx_pregrasp_free(ctx);
   delete ctx;
   return CDX_OK;

@@ -395,6 +395,16 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
                : launch_var<KERNEL, 64, true, 128>(ctx, X, M, mean, gmean, stdv, gstd, st);
   }
   if (stdv) {
+    // large TPS states and batches: std on the INT8 tensor cores (tcgen05, cdx_query_i8.cu), mean / grad_mean by the
+    // TMA-staged mean kernel.  auto = 5 slices (|d var| < 1e-8 prior measured; the gate is 1e-6 prior).
+    const int vm = g.var_mode;
+    const bool i8 = vm != -1 && cdx_i8_eligible(ctx) && (vm >= 4 || (g.Np >= 1024 && M >= 16384));
+    if (i8) {
+      int rc = cdx_i8_std(ctx, vm >= 4 ? vm : 5, X, M, stdv, st);
+      if (rc) return rc;
+      if (mean || gmean) return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
+      return CDX_OK;
+    }
     if (small_batch) return big ? launch_var<KERNEL, 128, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st)
                                 : launch_var<KERNEL, 64, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st);
     return big ? launch_var<KERNEL, 128, false, 128>(ctx, X, M, mean, gmean, stdv, nullptr, st)

@@ -91,6 +91,7 @@ class GPIS:
         if self._ctx is None or self._device != idx:
             self._ctx = _lib.new_context(idx)
             self._device = idx
+            _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, getattr(self, "_var_mode", 0)))
         return self._ctx
 
     def _check_factorisation(self):
@@ -107,6 +108,13 @@ class GPIS:
         X = X.contiguous()
         _lib.check(_lib.load().cdx_gpis_query(self._ctx, _ptr(X), X.shape[0], _ptr(mean), _ptr(gmean), _ptr(std),
                                               _ptr(gstd), _stream(self._device)))
+
+    def set_var_mode(self, mode):
+        """-1: std always by FP64 tensor MMA; 0: auto (tcgen05 INT8 slices for large TPS states and batches);
+        4..6: INT8 path with that many byte slices whenever eligible (include/cdx.h cdx_gpis_set_var_mode)."""
+        self._var_mode = int(mode)
+        if self._ctx is not None:
+            _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, self._var_mode))
 
     # ---- fit / state -----------------------------------------------------------------------------------
     def fit(self, X1, y1, noise=0.0):
