@@ -25,18 +25,25 @@ namespace {
 
 constexpr int I8_TQ = 128;   // queries per CTA  (UMMA M)
 constexpr int I8_TN = 64;    // training rows per tile (UMMA N)
-constexpr int I8_BK = 64;    // training points per stage (2 UMMA K-steps of 32 bytes)
 constexpr int I8_GEN_WARPS = 16, I8_WARP_MMA = 16, I8_WARP_LOAD = 17, I8_WARP_EPI = 18;
 constexpr int I8_THREADS = 22 * 32;
 constexpr double I8_MAGIC = 6755399441055744.0;  // 1.5 * 2^52: adding it leaves rint(x) in the low mantissa bits
 
 template <int S> struct i8cfg {
-  static constexpr int A_SLICE = I8_TQ * I8_BK;        // 8 KB
-  static constexpr int B_SLICE = I8_TN * I8_BK;        // 4 KB
-  static constexpr int A_BYTES = S * A_SLICE, B_BYTES = S * B_SLICE, SLOT = A_BYTES + B_BYTES;
-  static constexpr int NS = (220 * 1024) / SLOT > 4 ? 4 : (220 * 1024) / SLOT;   // S=4: 4, S=5: 3, S=6: 3
-  static constexpr int TMEM_COLS = S * I8_TN <= 256 ? 256 : 512;
-  static constexpr size_t SMEM = (size_t)NS * SLOT + 256;
+  static constexpr int BK = S >= 6 ? 32 : 64;          // training points per stage (TMEM budget: S*64 + 2*S*BK/4 <= 512 columns)
+  static constexpr int KG = BK / 16;                   // 16-byte k groups per stage
+  static constexpr int GSPLIT = 4 / KG;                // generator warps are split over this many consecutive stages
+  static constexpr int ACOLS = S * BK / 4;             // TMEM columns of one A stage (4 int8 per 32-bit column)
+  static constexpr int NSA = 2;                        // A stages in TMEM
+  static constexpr int ACC_COLS = S * I8_TN, A_BASE = ACC_COLS;
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int B_SLICE = I8_TN * BK;           // bytes of one slice of one U tile
+  static constexpr int B_BYTES = S * B_SLICE;
+  static constexpr int P_BYTES = BK * 32;              // the stage's training points (-2x,-2y,-2z,|x|^2)
+  static constexpr int SLOT = B_BYTES + P_BYTES;
+  static constexpr int NSB = 6;                        // smem stages of (U slices, points)
+  static constexpr size_t SMEM = (size_t)NSB * SLOT + 256;
+  static_assert(ACC_COLS + NSA * ACOLS <= 512, "TMEM budget");
 };
 
 // ------------------------------------------------------------------------------------------- PTX helpers
@@ -56,6 +63,16 @@ __device__ __forceinline__ void mb_wait(uint64_t* bar, unsigned parity) {
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
       "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(s32(bar)), "r"(parity) : "memory");
 }
+// for waits that are long by design (epilogue / loader): poll with back-off so the spin does not take issue slots
+__device__ __forceinline__ void mb_wait_relaxed(uint64_t* bar, unsigned parity) {
+  unsigned done = 0;
+  for (;;) {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                 : "=r"(done) : "r"(s32(bar)), "r"(parity) : "memory");
+    if (done) break;
+    __nanosleep(128);
+  }
+}
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(s32(dst)),
                "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
@@ -74,6 +91,18 @@ __device__ __forceinline__ void tc_mma_i8(unsigned tmem_d, uint64_t da, uint64_t
       "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u)
       : "memory");
 }
+// same with the A operand in tensor memory (lane = row, 4 int8 per 32-bit column)
+__device__ __forceinline__ void tc_mma_i8_ts(unsigned tmem_d, unsigned tmem_a, uint64_t db, unsigned idesc, unsigned accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u)
+      : "memory");
+}
+__device__ __forceinline__ void tc_st4(unsigned taddr, unsigned a, unsigned b, unsigned c, unsigned d) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
 // K-major, no swizzle: 8x16-byte core matrices; LBO = byte stride between the two 16-byte K columns of one MMA,
 // SBO = byte stride between 8-row groups (cute/arch/mma_sm100_desc.hpp SmemDescriptor; version 1 = sm_100)
 __device__ __forceinline__ uint64_t tc_desc(unsigned saddr, unsigned lbo, unsigned sbo) {
@@ -116,10 +145,11 @@ __global__ void __launch_bounds__(256) i8_slice_kernel(const double* __restrict_
                                                        int8_t* __restrict__ Bsl) {
   const int k = blockIdx.x * 256 + threadIdx.x, n = blockIdx.y;
   if (k >= Np) return;
-  const int NC = Np / I8_BK;
+  constexpr int BK = i8cfg<S>::BK;
+  const int NC = Np / BK;
   long long V = 0;
   if (n < N && k <= n) V = llrint(ldexp(U[(int64_t)n * Np + k], 8 * S - eb[n]));
-  const int nt = n / I8_TN, nl = n % I8_TN, c = k / I8_BK, kk = k % I8_BK;
+  const int nt = n / I8_TN, nl = n % I8_TN, c = k / BK, kk = k % BK;
   int8_t* base = Bsl + ((size_t)(nt * NC + c) * S) * i8cfg<S>::B_SLICE + (kk / 16) * (I8_TN * 16) + nl * 16 + (kk % 16);
 #pragma unroll
   for (int j = S - 1; j >= 0; j--) {
@@ -177,22 +207,25 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
                    const double* __restrict__ sb, const double* __restrict__ bb, int Np, double R, double R3, double prior,
                    double* __restrict__ stdv) {
   using C = i8cfg<S>;
-  constexpr int NS = C::NS;
+  constexpr int NSA = C::NSA, NSB = C::NSB, BK = C::BK, KG = C::KG;
   extern __shared__ __align__(128) unsigned char smem[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)NS * C::SLOT);
-  uint64_t* a_full = bars;            // [NS] 16 generator warps arrive
-  uint64_t* b_full = bars + NS;       // [NS] bulk copy (tx bytes)
-  uint64_t* s_empty = bars + 2 * NS;  // [NS] tcgen05.commit
-  uint64_t* acc_full = bars + 3 * NS;
-  uint64_t* acc_empty = bars + 3 * NS + 1;
-  unsigned* tmem_slot = reinterpret_cast<unsigned*>(bars + 3 * NS + 2);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)NSB * C::SLOT);
+  uint64_t* a_full = bars;                  // [NSA] generator warps arrive (k* slices are in tensor memory)
+  uint64_t* a_empty = bars + NSA;           // [NSA] tcgen05.commit
+  uint64_t* b_full = bars + 2 * NSA;        // [NSB] bulk copies (tx bytes)
+  uint64_t* b_empty = b_full + NSB;         // [NSB] tcgen05.commit
+  uint64_t* acc_full = b_empty + NSB;
+  uint64_t* acc_empty = acc_full + 1;
+  unsigned* tmem_slot = reinterpret_cast<unsigned*>(acc_empty + 1);
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   const int64_t q0 = (int64_t)blockIdx.x * I8_TQ;
-  const int NT = Np / I8_TN, NC = Np / I8_BK;
+  const int NT = Np / I8_TN, NC = Np / BK;
+  constexpr int CPT = I8_TN / BK;           // k chunks per n tile (triangular bound: chunks c < (nt + 1) CPT)
 
   if (t == 0) {
-    for (int i = 0; i < NS; i++) { mb_init(a_full + i, I8_GEN_WARPS); mb_init(b_full + i, 1); mb_init(s_empty + i, 1); }
+    for (int i = 0; i < NSA; i++) { mb_init(a_full + i, 4 * KG); mb_init(a_empty + i, 1); }
+    for (int i = 0; i < NSB; i++) { mb_init(b_full + i, 1); mb_init(b_empty + i, 1); }
     mb_init(acc_full, 1);
     mb_init(acc_empty, 4);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
@@ -207,34 +240,37 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
   const unsigned tmem = *tmem_slot;
 
   if (warp < I8_GEN_WARPS) {
-    // ===================================================== generators: row = t % 128, 16 training points per stage
-    const int row = t & 127, kg = t >> 7;
+    // ===================================================== generators: row = t % 128, 16 training points per owned stage
+    const int row = t & 127, kq = t >> 7, kg = kq % KG, sub = kq / KG;
     const int64_t q = q0 + row;
     const bool ok = q < M;
     const double xq = ok ? Xq[q * 3] : 0.0, yq = ok ? Xq[q * 3 + 1] : 0.0, zq = ok ? Xq[q * 3 + 2] : 0.0;
     const double qq = fma(xq, xq, fma(yq, yq, zq * zq)) + 1e-16;   // keeps the expanded squared distance positive
     const double sc = i8_query_scale<S>(xq, yq, zq, bb, R, R3);
     const double c2 = 2.0 * sc, c3 = -3.0 * R * sc, c0m = R3 * sc + I8_MAGIC;
-    const double2* P2 = reinterpret_cast<const double2*>(pts);
+    const unsigned trow = tmem + ((unsigned)((warp & 3) * 32) << 16) + C::A_BASE + kg * 4;
     int g = 0;
     for (int nt = 0; nt < NT; nt++) {
-      for (int c = 0; c <= nt; c++, g++) {
-        const int slot = g % NS;
-        const unsigned ph = (unsigned)(g / NS) & 1u;
-        if (lane == 0) mb_wait(s_empty + slot, ph ^ 1u);
+      const int nch = (nt + 1) * CPT;
+      for (int c = 0; c < nch; c++, g++) {
+        if (C::GSPLIT > 1 && (g % C::GSPLIT) != sub) continue;
+        const int sa = g % NSA, sbk = g % NSB;
+        if (lane == 0) mb_wait(a_empty + sa, ((unsigned)(g / NSA) & 1u) ^ 1u);
         __syncwarp();
-        unsigned char* As = smem + (size_t)slot * C::SLOT + kg * (I8_TQ * 16) + row * 16;
+        tc_fence_after();
+        mb_wait(b_full + sbk, (unsigned)(g / NSB) & 1u);     // the stage's training points arrive with the U slices
+        const double2* P2 = reinterpret_cast<const double2*>(smem + (size_t)sbk * C::SLOT + C::B_BYTES) + kg * 32;
         unsigned ow[S][4];
 #pragma unroll
         for (int gq = 0; gq < 4; gq++) {
           unsigned L[4], H[4];
 #pragma unroll
           for (int p = 0; p < 4; p++) {
-            const int j = c * I8_BK + kg * 16 + gq * 4 + p;
-            const double2 a = __ldg(P2 + 2 * j), b = __ldg(P2 + 2 * j + 1);
+            const int j = gq * 4 + p;
+            const double2 a = P2[2 * j], b = P2[2 * j + 1];
             const double s = fma(xq, a.x, fma(yq, a.y, fma(zq, b.x, b.y + qq)));
             const unsigned shi = (unsigned)__double2hiint(s), slo = (unsigned)__double2loint(s);
-            const unsigned fb = ((shi - 0x38000000u) << 3) | (slo >> 29);       // float(s) by bit moves (no F2F)
+            const unsigned fb = __funnelshift_l(slo, shi - 0x38000000u, 3);     // float(s) by bit moves (no F2F)
             const unsigned yb = __float_as_uint(rsqrtf(__uint_as_float(fb)));
             const double yd = __hiloint2double((int)((yb >> 3) + 0x38000000u), (int)(yb << 29));
             const double hy = __hiloint2double((int)((yb >> 3) + 0x37F00000u), (int)(yb << 29));   // y / 2
@@ -257,26 +293,28 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
           for (int i = 0; i < S; i++) ow[i][gq] = by[S - 1 - i];
         }
 #pragma unroll
-        for (int i = 0; i < S; i++)
-          *reinterpret_cast<uint4*>(As + i * C::A_SLICE) = make_uint4(ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
-        fence_async_smem();
+        for (int i = 0; i < S; i++) tc_st4(trow + sa * C::ACOLS + i * (BK / 4), ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
+        tc_wait_st();
+        tc_fence_before();
         __syncwarp();
-        if (lane == 0) mb_arrive(a_full + slot);
+        if (lane == 0) mb_arrive(a_full + sa);
       }
     }
   } else if (warp == I8_WARP_LOAD) {
-    // ===================================================== U slices: one bulk copy per stage
+    // ===================================================== U slices + points: two bulk copies per stage
     if (lane == 0) {
       int g = 0;
-      for (int nt = 0; nt < NT; nt++)
-        for (int c = 0; c <= nt; c++, g++) {
-          const int slot = g % NS;
-          const unsigned ph = (unsigned)(g / NS) & 1u;
-          mb_wait(s_empty + slot, ph ^ 1u);
-          mb_expect_tx(b_full + slot, (unsigned)C::B_BYTES);
-          bulk_g2s(smem + (size_t)slot * C::SLOT + C::A_BYTES, Bsl + (size_t)(nt * NC + c) * C::B_BYTES, (unsigned)C::B_BYTES,
-                   b_full + slot);
+      for (int nt = 0; nt < NT; nt++) {
+        const int nch = (nt + 1) * CPT;
+        for (int c = 0; c < nch; c++, g++) {
+          const int sbk = g % NSB;
+          mb_wait_relaxed(b_empty + sbk, ((unsigned)(g / NSB) & 1u) ^ 1u);
+          mb_expect_tx(b_full + sbk, (unsigned)(C::B_BYTES + C::P_BYTES));
+          unsigned char* dst = smem + (size_t)sbk * C::SLOT;
+          bulk_g2s(dst, Bsl + (size_t)(nt * NC + c) * C::B_BYTES, (unsigned)C::B_BYTES, b_full + sbk);
+          bulk_g2s(dst + C::B_BYTES, pts + (size_t)c * BK * 4, (unsigned)C::P_BYTES, b_full + sbk);
         }
+      }
     }
   } else if (warp == I8_WARP_MMA) {
     // ===================================================== MMA issue (one lane)
@@ -287,24 +325,25 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
       for (int nt = 0; nt < NT; nt++) {
         mb_wait(acc_empty, ((unsigned)nt & 1u) ^ 1u);
         tc_fence_after();
-        for (int c = 0; c <= nt; c++, g++) {
-          const int slot = g % NS;
-          const unsigned ph = (unsigned)(g / NS) & 1u;
-          mb_wait(a_full + slot, ph);
-          mb_wait(b_full + slot, ph);
+        const int nch = (nt + 1) * CPT;
+        for (int c = 0; c < nch; c++, g++) {
+          const int sa = g % NSA, sbk = g % NSB;
+          mb_wait(b_full + sbk, (unsigned)(g / NSB) & 1u);
+          mb_wait(a_full + sa, (unsigned)(g / NSA) & 1u);
           tc_fence_after();
-          const unsigned abase = s32(smem + (size_t)slot * C::SLOT), bbase = abase + C::A_BYTES;
+          const unsigned bbase = s32(smem + (size_t)sbk * C::SLOT);
+          const unsigned abase = tmem + C::A_BASE + sa * C::ACOLS;
 #pragma unroll
-          for (int ks = 0; ks < 2; ks++)
+          for (int ks = 0; ks < BK / 32; ks++)
 #pragma unroll
             for (int d = 0; d < S; d++)
 #pragma unroll
               for (int i = 0; i <= d; i++) {
-                const uint64_t da = tc_desc(abase + i * C::A_SLICE + ks * (2 * I8_TQ * 16), I8_TQ * 16, 128);
                 const uint64_t db = tc_desc(bbase + (d - i) * C::B_SLICE + ks * (2 * I8_TN * 16), I8_TN * 16, 128);
-                tc_mma_i8(tmem + d * I8_TN, da, db, idesc, (c > 0 || ks > 0 || i > 0) ? 1u : 0u);
+                tc_mma_i8_ts(tmem + d * I8_TN, abase + i * (BK / 4) + ks * 8, db, idesc, (c > 0 || ks > 0 || i > 0) ? 1u : 0u);
               }
-          tc_commit(s_empty + slot);
+          tc_commit(a_empty + sa);
+          tc_commit(b_empty + sbk);
         }
         tc_commit(acc_full);
       }
@@ -318,7 +357,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
     const double sc = i8_query_scale<S>(xq, yq, zq, bb, R, R3);
     double ss = 0.0;
     for (int nt = 0; nt < NT; nt++) {
-      mb_wait(acc_full, (unsigned)nt & 1u);
+      mb_wait_relaxed(acc_full, (unsigned)nt & 1u);
       tc_fence_after();
       const unsigned trow = tmem + ((unsigned)(lq * 32) << 16);
 #pragma unroll 1
@@ -357,7 +396,7 @@ int i8_prepare(cdx_ctx* ctx, cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
   if (g.i8_S == S) return CDX_OK;
   const int Np = (int)g.Np, N = (int)g.N;
-  const size_t need = (size_t)(Np / I8_TN) * (Np / I8_BK) * i8cfg<S>::B_BYTES;
+  const size_t need = (size_t)(Np / I8_TN) * (Np / i8cfg<S>::BK) * i8cfg<S>::B_BYTES;
   if (need > g.i8_cap) {
     cudaFree(g.i8_B);
     g.i8_B = nullptr;
