@@ -34,6 +34,8 @@ def parse():
     ap.add_argument("--candidates", type=int, default=1024)
     ap.add_argument("--iters", type=int, default=200)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--var-mode", type=int, default=0,
+                    help="gpis_c3: 0 auto (tcgen05 INT8 slices), -1 FP64 tensor MMA, 4..6 INT8 with that many slices")
     return ap.parse_args()
 
 
@@ -139,6 +141,7 @@ def run_gpis_c3(args, rank, world, local):
     X1, y1, noise, Xh, per = gpis_c3_inputs(args.ntrain, args.queries, rank, world)
     M = Xh.shape[0]
     g = GPIS(0.08, 1.0)
+    g.set_var_mode(args.var_mode)
     t0 = time.perf_counter()
     g.fit(X1.to(dev), y1.to(dev), noise.to(dev))
     torch.cuda.synchronize()
@@ -189,36 +192,69 @@ def run_gpis_c3(args, rank, world, local):
     barrier(world)
     ms_e2e = max_over_ranks(e0.elapsed_time(e1), world)
 
+    # dominant kernel alone (std only -> one launch), CUDA events on the launching stream
+    def step_std():
+        _lib.check(lib.cdx_gpis_query(g._ctx, Xd.data_ptr(), M, None, None, std.data_ptr(), None, st))
+
+    step_std()
+    e0.record()
+    for _ in range(args.steps):
+        step_std()
+    e1.record()
+    torch.cuda.synchronize()
+    kernel_ms = e0.elapsed_time(e1) / args.steps
+
     if rank != 0:
         return None
     N = args.ntrain
+    Np = (N + 63) // 64 * 64
     total_q = args.queries
     ms_step = ms / args.steps
     flop_per_query = N * N + 26 * N                                # SURVEY 8(d) unit query
     pipes = fp64_pipe_peaks()
     peaks, src = measured_peaks()
-    kernel_ms = ms_step                                            # one launch per step: the step IS the kernel
-    achieved = flop_per_query * M / (kernel_ms * 1e-3) / 1e12      # this rank's launch
-    peak = pipes.get("dmma_m8n8k4_tflops")
+    fp64_equiv = flop_per_query * M / (kernel_ms * 1e-3) / 1e12    # algorithmic FP64 flop of this rank's launch / its time
+    dmma_peak = pipes.get("dmma_m8n8k4_tflops")
+    i8 = args.var_mode != -1 and 1024 <= Np <= 8192
+    if i8:
+        S = args.var_mode if args.var_mode >= 4 else 5
+        NT = Np // 64
+        # executed INT8 multiply-adds: S(S+1)/2 slice pairs x 64x64 blocks of the lower triangle (diagonal blocks whole)
+        ops_per_query = 2 * (S * (S + 1) // 2) * 64 * 64 * (NT * (NT + 1) // 2)
+        achieved = ops_per_query * M / (kernel_ms * 1e-3) / 1e12
+        peak = 2.0 * peaks.get("bf16_tflops", 0)
+        roof = {"bound": "tensor", "kernel": "gpis_std_i8_kernel<%d> (tcgen05 kind::i8, INT32 accumulators in TMEM)" % S,
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+                "peak_source": "INT8 dense tensor peak taken as 2 x the %s bf16 figure of MEASURED_PEAKS.json (%.0f TF/s); "
+                               "achieved counts executed INT8 multiply-adds x 2 (TOP/s)" % (src, peaks.get("bf16_tflops", 0)),
+                "int8_ops_per_query": ops_per_query, "slices": S,
+                "algorithmic_fp64_tflops": fp64_equiv, "fp64_dmma_peak_tflops": dmma_peak,
+                "algorithmic_vs_fp64_dmma_peak": fp64_equiv / dmma_peak if dmma_peak else None,
+                "note": "the FP64 contraction L^-1 k* (N^2 flop/query) is evaluated as error-free INT8 slice products; the "
+                        "kernel is bound by the FP64 generation of the k* slices (16 warps, DFMA + MUFU.RSQ + PRMT), not by "
+                        "the tensor pipe; mean / grad_mean come from the separate TMA-staged mean kernel"}
+    else:
+        roof = {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,128,unit> (FP64 DMMA)", "achieved": fp64_equiv,
+                "peak": dmma_peak, "unit": "TFLOP/s", "frac": (fp64_equiv / dmma_peak) if dmma_peak else None,
+                "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json "
+                               "has no FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0))}
+    roof.update({"flop_per_query": flop_per_query, "queries_per_launch": M, "kernel_ms": kernel_ms,
+                 "kernel_share_of_step": kernel_ms / ms_step, "traffic": None, "fp64_pipes": pipes})
     out = {
         "metric": "GPIS mean+var+grad queries/sec", "value": total_q / (ms_step * 1e-3), "unit": "queries/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "gpis_c3: synthetic TPS GPIS N=%d, %d unit queries {mean,grad_mean,std} per step, "
                                "sharded by contiguous ranges" % (N, total_q),
-                   "l2_policy": "inputs+outputs (%.0f MB) and E11^-1 factor (%.0f MB) exceed L2; no flush needed"
-                                % (M * 64 / 1e6, N * N * 8 / 1e6),
+                   "var_mode": args.var_mode,
+                   "l2_policy": "inputs+outputs (%.0f MB) and the L^-1 operand (%.0f MB) exceed L2; no flush needed"
+                                % (M * 64 / 1e6, (5 * Np * Np if i8 else 8 * N * N) / 1e6),
                    "fit_seconds": fit_s},
         "e2e": {"value": total_q / (ms_e2e / args.steps * 1e-3), "unit": "queries/s",
                 "h2d_bytes_per_step": int(M * 24), "d2h_bytes_per_step": int(M * 40)},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,128,unit> (FP64 DMMA)", "achieved": achieved,
-                     "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if peak else None,
-                     "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json "
-                                    "has no FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0)),
-                     "flop_per_query": flop_per_query, "queries_per_launch": M, "traffic": None,
-                     "fp64_pipes": pipes},
+        "roofline": roof,
     }
     return out
 

@@ -10,15 +10,19 @@
 // the two operands to 8S-2 bits and of the slice pairs to i+j < S, 2^-8S-class relative to |row|.|column| - measured on
 // B200 against the FP64 DMMA path (tests/test_gpis_i8_gpu.py): S = 5 gives |d var| < 1e-8 prior, the gate is 1e-6 prior.
 //
-// Roles per CTA (128 queries x all training rows, one CTA per SM):
+// Roles per CTA (128 queries x all training rows, one CTA per SM; TMEM: S x 64 accumulator columns + 2 stages of k*):
 //   warps 0-15  generate k* for (query row, 16 training points) in FP64 (9 DFMA-class ops + 1 MUFU.RSQ per pair: expanded
 //               squared distance, float rsqrt seed built by integer bit moves instead of F2F conversions, one Newton step,
-//               cubic, fixed-point conversion by the 1.5*2^52 trick), split the value into bytes with PRMT and store the S
-//               slices in the canonical K-major no-swizzle UMMA layout;
-//   warp 17     streams the pre-tiled U slices with one cp.async.bulk (1-D TMA) per stage;
-//   warp 16     one lane issues S(S+1)/2 x 2 tcgen05.mma (M=128, N=64, K=32) per 64-point stage, slots recycled by
-//               tcgen05.commit -> mbarrier;
-//   warps 18-21 drain the S diagonal accumulators from TMEM (tcgen05.ld), recombine them in FP64 and accumulate |v|^2.
+//               cubic, fixed-point conversion by the 1.5*2^52 trick), split the value into bytes with PRMT and write the S
+//               slices straight into tensor memory (tcgen05.st; lane = query row, 4 int8 per column) - the A operand never
+//               touches shared memory;
+//   warp 17     streams the pre-tiled U slices and the stage's training points with two cp.async.bulk (1-D TMA) per stage;
+//   warp 16     stays converged, one elected lane issues S(S+1)/2 tcgen05.mma (A from TMEM, B from smem, M=128, N=64,
+//               K=32) per 32 training points; stages are recycled by tcgen05.commit -> mbarrier;
+//   warps 18-21 drain the S diagonal accumulators from TMEM (tcgen05.ld), recombine them (integer Horner + FP64) and
+//               accumulate |v|^2.
+// Measured on B200 (N=4096): the kernel is bound by the FP64 generation of k* (about 3.6k cycles per 128x64 stage against
+// 1.0k cycles of MMA), because k* is regenerated for each of the N/64 row tiles; see DESIGN.md for the numbers.
 #include "cdx_internal.cuh"
 
 namespace {
@@ -51,37 +55,37 @@ __device__ __forceinline__ unsigned s32(const void* p) { return (unsigned)__cvta
 __device__ __forceinline__ void mb_init(uint64_t* bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(s32(bar)), "r"(count));
 }
-__device__ __forceinline__ void mb_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(s32(bar)) : "memory");
+__device__ __forceinline__ void mb_arrive(unsigned bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void mb_expect_tx(uint64_t* bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(s32(bar)), "r"(bytes) : "memory");
+__device__ __forceinline__ void mb_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mb_wait(uint64_t* bar, unsigned parity) {
+__device__ __forceinline__ void mb_wait(unsigned bar, unsigned parity) {
   asm volatile(
       "{\n.reg .pred p;\nWAIT_%=:\n"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(s32(bar)), "r"(parity) : "memory");
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(bar), "r"(parity) : "memory");
 }
 // for waits that are long by design (epilogue / loader): poll with back-off so the spin does not take issue slots
-__device__ __forceinline__ void mb_wait_relaxed(uint64_t* bar, unsigned parity) {
+__device__ __forceinline__ void mb_wait_relaxed(unsigned bar, unsigned parity, unsigned ns = 128) {
   unsigned done = 0;
   for (;;) {
     asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
-                 : "=r"(done) : "r"(s32(bar)), "r"(parity) : "memory");
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     if (done) break;
-    __nanosleep(128);
+    __nanosleep(ns);
   }
 }
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(s32(dst)),
-               "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(s32(bar)) : "memory");
+__device__ __forceinline__ void tc_commit(unsigned bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
 }
 // D[tmem] (+)= A[smem desc] * B[smem desc]^T, INT8 kind, INT32 accumulate
 __device__ __forceinline__ void tc_mma_i8(unsigned tmem_d, uint64_t da, uint64_t db, unsigned idesc, unsigned accumulate) {
@@ -101,6 +105,16 @@ __device__ __forceinline__ void tc_mma_i8_ts(unsigned tmem_d, unsigned tmem_a, u
 }
 __device__ __forceinline__ void tc_st4(unsigned taddr, unsigned a, unsigned b, unsigned c, unsigned d) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ float rsqrt_ftz(float x) {   // one MUFU.RSQ, no denormal fix-up (inputs are in [1e-16, 1e2])
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;\n" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ bool elect_one() {   // one lane of the (converged) warp
+  unsigned pred;
+  asm volatile("{\n.reg .b32 rx;\n.reg .pred px;\nelect.sync rx|px, 0xffffffff;\nselp.u32 %0, 1, 0, px;\n}\n" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
 // K-major, no swizzle: 8x16-byte core matrices; LBO = byte stride between the two 16-byte K columns of one MMA,
@@ -210,13 +224,15 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
   constexpr int NSA = C::NSA, NSB = C::NSB, BK = C::BK, KG = C::KG;
   extern __shared__ __align__(128) unsigned char smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)NSB * C::SLOT);
-  uint64_t* a_full = bars;                  // [NSA] generator warps arrive (k* slices are in tensor memory)
-  uint64_t* a_empty = bars + NSA;           // [NSA] tcgen05.commit
-  uint64_t* b_full = bars + 2 * NSA;        // [NSB] bulk copies (tx bytes)
-  uint64_t* b_empty = b_full + NSB;         // [NSB] tcgen05.commit
-  uint64_t* acc_full = b_empty + NSB;
-  uint64_t* acc_empty = acc_full + 1;
-  unsigned* tmem_slot = reinterpret_cast<unsigned*>(acc_empty + 1);
+  // mbarriers, addressed by their 32-bit shared-window offsets (8 bytes each)
+  const unsigned smem0 = s32(smem), bar0 = s32(bars);
+  const unsigned a_full = bar0;                         // [NSA] generator warps arrive (k* slices are in tensor memory)
+  const unsigned a_empty = bar0 + 8 * NSA;              // [NSA] tcgen05.commit
+  const unsigned b_full = bar0 + 8 * 2 * NSA;           // [NSB] bulk copies (tx bytes)
+  const unsigned b_empty = b_full + 8 * NSB;            // [NSB] tcgen05.commit
+  const unsigned acc_full = b_empty + 8 * NSB;
+  const unsigned acc_empty = acc_full + 8;
+  unsigned* tmem_slot = reinterpret_cast<unsigned*>(bars + 2 * NSA + 2 * NSB + 2);
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   const int64_t q0 = (int64_t)blockIdx.x * I8_TQ;
@@ -224,10 +240,10 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
   constexpr int CPT = I8_TN / BK;           // k chunks per n tile (triangular bound: chunks c < (nt + 1) CPT)
 
   if (t == 0) {
-    for (int i = 0; i < NSA; i++) { mb_init(a_full + i, 4 * KG); mb_init(a_empty + i, 1); }
-    for (int i = 0; i < NSB; i++) { mb_init(b_full + i, 1); mb_init(b_empty + i, 1); }
-    mb_init(acc_full, 1);
-    mb_init(acc_empty, 4);
+    for (int i = 0; i < NSA; i++) { mb_init(bars + i, 4 * KG); mb_init(bars + NSA + i, 1); }
+    for (int i = 0; i < 2 * NSB; i++) mb_init(bars + 2 * NSA + i, 1);
+    mb_init(bars + 2 * NSA + 2 * NSB, 1);
+    mb_init(bars + 2 * NSA + 2 * NSB + 1, 4);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   if (warp == I8_WARP_MMA) {
@@ -255,10 +271,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
       for (int c = 0; c < nch; c++, g++) {
         if (C::GSPLIT > 1 && (g % C::GSPLIT) != sub) continue;
         const int sa = g % NSA, sbk = g % NSB;
-        if (lane == 0) mb_wait(a_empty + sa, ((unsigned)(g / NSA) & 1u) ^ 1u);
-        __syncwarp();
-        tc_fence_after();
-        mb_wait(b_full + sbk, (unsigned)(g / NSB) & 1u);     // the stage's training points arrive with the U slices
+        mb_wait(b_full + 8 * sbk, (unsigned)(g / NSB) & 1u);     // the stage's training points arrive with the U slices
         const double2* P2 = reinterpret_cast<const double2*>(smem + (size_t)sbk * C::SLOT + C::B_BYTES) + kg * 32;
         unsigned ow[S][4];
 #pragma unroll
@@ -271,7 +284,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
             const double s = fma(xq, a.x, fma(yq, a.y, fma(zq, b.x, b.y + qq)));
             const unsigned shi = (unsigned)__double2hiint(s), slo = (unsigned)__double2loint(s);
             const unsigned fb = __funnelshift_l(slo, shi - 0x38000000u, 3);     // float(s) by bit moves (no F2F)
-            const unsigned yb = __float_as_uint(rsqrtf(__uint_as_float(fb)));
+            const unsigned yb = __float_as_uint(rsqrt_ftz(__uint_as_float(fb)));
             const double yd = __hiloint2double((int)((yb >> 3) + 0x38000000u), (int)(yb << 29));
             const double hy = __hiloint2double((int)((yb >> 3) + 0x37F00000u), (int)(yb << 29));   // y / 2
             double d = s * yd;
@@ -292,12 +305,16 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
 #pragma unroll
           for (int i = 0; i < S; i++) ow[i][gq] = by[S - 1 - i];
         }
+        // the TMEM stage is free once the MMAs of stage g - NSA have completed (the values above did not need it)
+        if (lane == 0) mb_wait(a_empty + 8 * sa, ((unsigned)(g / NSA) & 1u) ^ 1u);
+        __syncwarp();
+        tc_fence_after();
 #pragma unroll
         for (int i = 0; i < S; i++) tc_st4(trow + sa * C::ACOLS + i * (BK / 4), ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
         tc_wait_st();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mb_arrive(a_full + sa);
+        if (lane == 0) mb_arrive(a_full + 8 * sa);
       }
     }
   } else if (warp == I8_WARP_LOAD) {
@@ -308,44 +325,45 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
         const int nch = (nt + 1) * CPT;
         for (int c = 0; c < nch; c++, g++) {
           const int sbk = g % NSB;
-          mb_wait_relaxed(b_empty + sbk, ((unsigned)(g / NSB) & 1u) ^ 1u);
-          mb_expect_tx(b_full + sbk, (unsigned)(C::B_BYTES + C::P_BYTES));
-          unsigned char* dst = smem + (size_t)sbk * C::SLOT;
-          bulk_g2s(dst, Bsl + (size_t)(nt * NC + c) * C::B_BYTES, (unsigned)C::B_BYTES, b_full + sbk);
-          bulk_g2s(dst + C::B_BYTES, pts + (size_t)c * BK * 4, (unsigned)C::P_BYTES, b_full + sbk);
+          mb_wait_relaxed(b_empty + 8 * sbk, ((unsigned)(g / NSB) & 1u) ^ 1u);
+          mb_expect_tx(b_full + 8 * sbk, (unsigned)(C::B_BYTES + C::P_BYTES));
+          const unsigned dst = smem0 + sbk * C::SLOT;
+          bulk_g2s(dst, Bsl + (size_t)(nt * NC + c) * C::B_BYTES, (unsigned)C::B_BYTES, b_full + 8 * sbk);
+          bulk_g2s(dst + C::B_BYTES, pts + (size_t)c * BK * 4, (unsigned)C::P_BYTES, b_full + 8 * sbk);
         }
       }
     }
   } else if (warp == I8_WARP_MMA) {
-    // ===================================================== MMA issue (one lane)
-    if (lane == 0) {
-      // INT32 accumulate (c_format 2 @4), A unsigned 8-bit (0 @7), B signed 8-bit (1 @10), K-major both, N>>3 @17, M>>4 @24
-      constexpr unsigned idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((unsigned)(I8_TN >> 3) << 17) | ((unsigned)(I8_TQ >> 4) << 24);
-      int g = 0;
-      for (int nt = 0; nt < NT; nt++) {
-        mb_wait(acc_empty, ((unsigned)nt & 1u) ^ 1u);
+    // ===================================================== MMA issue: the warp stays converged, one elected lane issues
+    // INT32 accumulate (c_format 2 @4), A unsigned 8-bit (0 @7), B signed 8-bit (1 @10), K-major both, N>>3 @17, M>>4 @24
+    constexpr unsigned idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((unsigned)(I8_TN >> 3) << 17) | ((unsigned)(I8_TQ >> 4) << 24);
+    int g = 0;
+    for (int nt = 0; nt < NT; nt++) {
+      mb_wait(acc_empty, ((unsigned)nt & 1u) ^ 1u);
+      tc_fence_after();
+      const int nch = (nt + 1) * CPT;
+      for (int c = 0; c < nch; c++, g++) {
+        const int sa = g % NSA, sbk = g % NSB;
+        mb_wait(b_full + 8 * sbk, (unsigned)(g / NSB) & 1u);
+        mb_wait_relaxed(a_full + 8 * sa, (unsigned)(g / NSA) & 1u, 32);
         tc_fence_after();
-        const int nch = (nt + 1) * CPT;
-        for (int c = 0; c < nch; c++, g++) {
-          const int sa = g % NSA, sbk = g % NSB;
-          mb_wait(b_full + sbk, (unsigned)(g / NSB) & 1u);
-          mb_wait(a_full + sa, (unsigned)(g / NSA) & 1u);
-          tc_fence_after();
-          const unsigned bbase = s32(smem + (size_t)sbk * C::SLOT);
-          const unsigned abase = tmem + C::A_BASE + sa * C::ACOLS;
+        const unsigned bbase = smem0 + sbk * C::SLOT;
+        const unsigned abase = tmem + C::A_BASE + sa * C::ACOLS;
+        if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < BK / 32; ks++)
+          for (int d = 0; d < S; d++)
 #pragma unroll
-            for (int d = 0; d < S; d++)
+            for (int i = 0; i <= d; i++)
 #pragma unroll
-              for (int i = 0; i <= d; i++) {
+              for (int ks = 0; ks < BK / 32; ks++) {
                 const uint64_t db = tc_desc(bbase + (d - i) * C::B_SLICE + ks * (2 * I8_TN * 16), I8_TN * 16, 128);
                 tc_mma_i8_ts(tmem + d * I8_TN, abase + i * (BK / 4) + ks * 8, db, idesc, (c > 0 || ks > 0 || i > 0) ? 1u : 0u);
               }
-          tc_commit(a_empty + sa);
-          tc_commit(b_empty + sbk);
+          tc_commit(a_empty + 8 * sa);
+          tc_commit(b_empty + 8 * sbk);
+          if (c == nch - 1) tc_commit(acc_full);
         }
-        tc_commit(acc_full);
+        __syncwarp();
       }
     }
   } else {
@@ -368,9 +386,12 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
         tc_wait_ld();
 #pragma unroll
         for (int e = 0; e < 8; e++) {
-          double h = (double)r[0][e];
+          // sum_d 256^(S-1-d) acc_d: integer Horner for the leading S-2 terms and the last two (two conversions, not S)
+          long long hi = r[0][e];
 #pragma unroll
-          for (int d = 1; d < S; d++) h = fma(h, 256.0, (double)r[d][e]);
+          for (int d = 1; d < S - 2; d++) hi = (hi << 8) + r[d][e];
+          const long long lo = ((long long)r[S - 2][e] << 8) + r[S - 1][e];
+          double h = fma((double)hi, 65536.0, (double)lo);
           h *= __ldg(sb + nt * I8_TN + cg * 8 + e);
           ss = fma(h, h, ss);
         }

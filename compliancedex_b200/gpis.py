@@ -110,7 +110,7 @@ class GPIS:
                                               _ptr(gstd), _stream(self._device)))
 
     def set_var_mode(self, mode):
-        """-1: std always by FP64 tensor MMA; 0: auto (tcgen05 INT8 slices for large TPS states and batches);
+        """-1: std always by FP64 tensor MMA; 0: auto (tcgen05 INT8 slices for TPS states with padded N in 1024..8192);
         4..6: INT8 path with that many byte slices whenever eligible (include/cdx.h cdx_gpis_set_var_mode)."""
         self._var_mode = int(mode)
         if self._ctx is not None:

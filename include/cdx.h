@@ -63,8 +63,9 @@ int cdx_gpis_query(cdx_ctx* ctx, const double* X_dev, int64_t M, double* mean_de
                    double* std_dev, double* grad_std_dev, void* stream);
 /* which arithmetic evaluates std when grad_std is not requested (the contraction L^-1 k* is N^2 flop/query):
  *   -1  FP64 tensor MMA (mma.sync m8n8k4) always - bit-identical across batch sizes;
- *    0  auto: TPS states with 1024 <= padded N <= 8192 and M >= 16384 use the tcgen05 INT8 path with 5 byte slices
- *       (error-free integer products of a 38-bit fixed-point k* and L^-1; measured |d var| < 1e-8 prior), else FP64 MMA;
+ *    0  auto: TPS states with 1024 <= padded N <= 8192 use the tcgen05 INT8 path with 5 byte slices (error-free integer
+ *       products of a 38-bit fixed-point k* and L^-1; measured |d var| < 2e-8 prior), else FP64 MMA.  The choice depends on
+ *       the state only, so a query's result does not depend on the batch it is part of;
  *  4..6 INT8 path with that many slices whenever the state is eligible (TPS, padded N <= 8192), any M. */
 int cdx_gpis_set_var_mode(cdx_ctx* ctx, int mode);
 /* same through HOST buffers (copies on `stream`, synchronises before returning) - the e2e path of bench.py */

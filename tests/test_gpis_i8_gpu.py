@@ -1,0 +1,124 @@
+"""GPU parity of the tcgen05 INT8-sliced std path (csrc/cdx_query_i8.cu) against the reference-generated golden vectors,
+the oracle and the FP64 tensor-MMA path.  Gate (BASELINE.json): std^2 within 1e-6 * prior (R^3) absolute; mean and
+grad_mean <= 1e-5 relative (they come from the FP64 mean kernel on this path)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+NAMES = ["mug", "mug2", "coffeebottle", "lego", "hammer", "banana", "dummy"]
+
+
+def _gpis(name, mode):
+    from compliancedex_b200 import GPIS, state_path
+    g = GPIS(0.08, 1.0)
+    g.set_var_mode(mode)
+    g.load_state_data(state_path(f"{name}_state"))
+    return g
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("slices", [5, 6])
+def test_shipped_states_against_reference_golden(name, slices, golden_dir):
+    """every shipped state (N = 196..401, padded to 256..448): forced INT8 path vs the reference's own outputs"""
+    ref = np.load(os.path.join(golden_dir, f"gpis_{name}.npz"))
+    g = _gpis(name, slices)
+    X = torch.from_numpy(ref["X"]).cuda()
+    prior = float(g.R) ** 3
+    with torch.no_grad():
+        mean, std = g.pred(X)
+    mean, std = mean.cpu().numpy(), std.cpu().numpy()
+    assert np.abs(std ** 2 - ref["std"] ** 2).max() <= 1e-6 * prior
+    # measured margin: 5 slices stay a factor 20 inside the gate, 6 slices a factor 2000
+    assert np.abs(std ** 2 - ref["std"] ** 2).max() <= (5e-8 if slices == 5 else 5e-10) * prior
+    assert np.abs(mean - ref["mean"]).max() <= 1e-5 * np.abs(ref["mean"]).max()
+
+
+@pytest.mark.parametrize("M", [1, 127, 128, 129, 1000])
+def test_ragged_batches(M):
+    """query counts around the 128-row tile: tail rows are masked, results match the FP64 MMA path"""
+    g = _gpis("hammer", 5)
+    gen = torch.Generator().manual_seed(M)
+    X = ((torch.rand(M, 3, generator=gen, dtype=torch.float64) - 0.5) * 0.36).cuda()
+    with torch.no_grad():
+        m1, s1 = g.pred(X)
+        g.set_var_mode(-1)
+        m0, s0 = g.pred(X)
+    prior = float(g.R) ** 3
+    assert not torch.isnan(s1).any()
+    assert ((s1 ** 2 - s0 ** 2).abs().max() / prior).item() <= 5e-8
+    assert torch.equal(m1, m0) or ((m1 - m0).abs().max() / m0.abs().max()).item() <= 1e-10
+
+
+def test_far_queries_scale():
+    """queries far outside the training box (k* > R^3): the per-query fixed-point scale follows the cubic's bound"""
+    g = _gpis("mug", 5)
+    gen = torch.Generator().manual_seed(3)
+    X = ((torch.rand(512, 3, generator=gen, dtype=torch.float64) - 0.5) * 2.0).cuda()   # up to ~1.7 m away, R ~ 0.35
+    with torch.no_grad():
+        _, s1 = g.pred(X)
+        g.set_var_mode(-1)
+        _, s0 = g.pred(X)
+    # far away |v|^2 and k(x,x) are both huge compared with the prior: compare relative to the computed magnitude
+    scale = torch.maximum(s0 ** 2, torch.full_like(s0, float(g.R) ** 3))
+    assert (((s1 ** 2 - s0 ** 2).abs() / scale).max()).item() <= 1e-6
+
+
+@pytest.mark.parametrize("N", [1024, 2048])
+def test_synthetic_large_state_auto_mode(N):
+    """auto mode (padded N >= 1024, any batch) runs the INT8 path; parity vs the FP64 MMA path and vs the oracle on a sample"""
+    from compliancedex_b200 import GPIS
+    from compliancedex_b200.synthetic import synthetic_training_set, synthetic_queries
+    from oracle.gpis_oracle import GPISOracle
+    X1, y1, noise = synthetic_training_set(N)
+    g = GPIS(0.08, 1.0)
+    g.fit(X1.cuda(), y1.cuda(), noise.cuda())
+    M = 20000
+    X = synthetic_queries(M, 0, M).cuda()
+    X[:2000] = X1[torch.randint(0, N, (2000,), generator=torch.Generator().manual_seed(1))].cuda() \
+        + 1e-4 * torch.randn(2000, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(2)).cuda()
+    prior = float(g.R) ** 3
+    from compliancedex_b200 import _lib
+    before = _lib.load().cdx_launch_count(g._ctx)
+    with torch.no_grad():
+        m1, s1 = g.pred(X)                      # auto -> INT8 (prepare kernels + std kernel + mean kernel)
+    launched = _lib.load().cdx_launch_count(g._ctx) - before
+    assert launched == 5, launched               # rowscale + slice + points + std_i8 + mean
+    with torch.no_grad():
+        g.set_var_mode(-1)
+        m0, s0 = g.pred(X)
+        g.set_var_mode(6)
+        _, s6 = g.pred(X)
+    assert ((s1 ** 2 - s0 ** 2).abs().max() / prior).item() <= 5e-8
+    assert ((s6 ** 2 - s0 ** 2).abs().max() / prior).item() <= 5e-10
+    assert ((m1 - m0).abs().max() / m0.abs().max()).item() <= 1e-10
+    g.set_var_mode(0)
+    with torch.no_grad():
+        m2, s2 = g.pred(X[777:1500])           # chunking invariance: same arithmetic for any batch
+    assert torch.equal(m2, m1[777:1500]) and torch.equal(s2, s1[777:1500])
+    o = GPISOracle(0.08, 1.0)
+    o.fit(X1, y1, noise)
+    idx = torch.arange(0, M, 40)
+    mo, so = o.pred(X[idx].cpu())
+    assert ((s1[idx].cpu() ** 2 - so ** 2).abs().max() / prior).item() <= 1e-6
+    assert ((m1[idx].cpu() - mo).abs().max() / mo.abs().max()).item() <= 1e-5
+
+
+def test_refit_invalidates_slices():
+    """the sliced copy of L^-1 belongs to one fitted state: a second fit must rebuild it"""
+    from compliancedex_b200 import GPIS
+    from compliancedex_b200.synthetic import synthetic_training_set
+    g = GPIS(0.08, 1.0)
+    g.set_var_mode(5)
+    outs = []
+    X = ((torch.rand(300, 3, generator=torch.Generator().manual_seed(0), dtype=torch.float64) - 0.5) * 0.2).cuda()
+    for seed in (0, 1, 0):
+        X1, y1, noise = synthetic_training_set(512, seed=seed)
+        g.fit(X1.cuda(), y1.cuda(), noise.cuda())
+        with torch.no_grad():
+            outs.append(g.pred(X)[1].clone())
+    assert torch.equal(outs[0], outs[2])
+    assert not torch.equal(outs[0], outs[1])
