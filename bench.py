@@ -33,6 +33,8 @@ def parse():
     ap.add_argument("--ntrain", type=int, default=4096)
     ap.add_argument("--candidates", type=int, default=1024)
     ap.add_argument("--iters", type=int, default=200)
+    ap.add_argument("--hand", default="leap", choices=["leap", "allegro"])
+    ap.add_argument("--object", default="mug", help="shipped GPIS state of the pregrasp workload (mug, hammer, lego, ...)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--var-mode", type=int, default=0,
                     help="gpis_c3: 0 auto (tcgen05 INT8 slices), -1 FP64 tensor MMA, 4..6 INT8 with that many slices")
@@ -80,6 +82,24 @@ def measured_peaks():
     if os.path.isfile(p):
         return json.load(open(p)), "measured"
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+def ncu_traffic(summary_file, kernel_substr):
+    """DRAM bytes (read + write) per launch of a kernel from the committed ncu --set full summary under profiles/
+    (scripts/ncu_summary.py); None when no capture of that kernel is committed."""
+    p = os.path.join(ROOT, "profiles", summary_file)
+    if not os.path.isfile(p):
+        return None
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for key, d in json.load(open(p)).items():
+        if kernel_substr in key:
+            tot = 0.0
+            for f in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                v, u = d.get(f, "0 byte").split()[:2]
+                tot += float(v) * mult.get(u, 1.0)
+            return {"bytes_per_launch": tot, "source": "profiles/%s (%s, grid %s)" % (summary_file, key.split(":")[0],
+                                                                                     d.get("launch__grid_size", "?").strip())}
+    return None
 
 
 def fp64_pipe_peaks():
@@ -239,7 +259,9 @@ def run_gpis_c3(args, rank, world, local):
                 "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json "
                                "has no FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0))}
     roof.update({"flop_per_query": flop_per_query, "queries_per_launch": M, "kernel_ms": kernel_ms,
-                 "kernel_share_of_step": kernel_ms / ms_step, "traffic": None, "fp64_pipes": pipes})
+                 "kernel_share_of_step": kernel_ms / ms_step,
+                 "traffic": ncu_traffic("r01_ncu_gpis_c3_i8_summary.json", "gpis_std_i8_kernel") if i8 else None,
+                 "fp64_pipes": pipes})
     out = {
         "metric": "GPIS mean+var+grad queries/sec", "value": total_q / (ms_step * 1e-3), "unit": "queries/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
@@ -322,7 +344,7 @@ def main():
                                               "one compute_normal (explicit inverse), %.1f s" % dt}
     else:
         from bench_pregrasp import run_bench_c2
-        line = run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks)
+        line = run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks, ncu_traffic)
         if rank == 0 and not args.no_cpu_baseline:
             from bench_pregrasp import cpu_pregrasp
             cpu_pregrasp(16, 2, threads)                          # warm-up (torch thread pool, LAPACK)

@@ -14,34 +14,36 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 METRIC = "pregrasp candidate-iters/sec"
 
 
-def _workload_name(B, iters, world):
-    return ("pregrasp_c2: ProbabilisticGraspOptimizer (optimize_target, optimize_palm), Leap hand on the mug GPIS state "
-            "(N=196), %d candidates x %d iterations per GPU, %d GPU(s)" % (B, iters, world))
+def _workload_name(B, iters, world, hand="leap", obj="mug", N=196):
+    tag = "pregrasp_c2" if (hand, obj) == ("leap", "mug") else "pregrasp_c5_shape"
+    return ("%s: ProbabilisticGraspOptimizer (optimize_target, optimize_palm), %s hand on the %s GPIS state "
+            "(N=%d), %d candidates x %d iterations per GPU, %d GPU(s)" % (tag, hand.capitalize(), obj, N, B, iters, world))
 
 
-def _make(rank, B, iters, device):
+def _make(rank, B, iters, device, hand="leap", obj="mug"):
     from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
     from compliancedex_b200.synthetic import surface_center, synthetic_candidates
     gp = GPIS(0.08, 1.0)
-    gp.load_state_data(state_path("mug_state"), device=device)
-    doc = load_hand("leap")
-    d = np.load(state_path("mug_state"))
+    gp.load_state_data(state_path(f"{obj}_state"), device=device)
+    doc = load_hand(hand)
+    d = np.load(state_path(f"{obj}_state"))
     center = surface_center(d["X1"], d["y1"])
     q0, T0, k0, palm = synthetic_candidates(doc, B, center, seed=100 + rank)
-    opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+    opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
                                       palm_offset=palm, num_iters=iters, optimize_target=True, ref_q=doc["ref_q"],
                                       mass=0.1, com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True,
                                       device=device, noise_seed=2024, env_offset=rank * B)
     return gp, opt, q0, T0, k0, palm, int(d["X1"].shape[0])
 
 
-def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks):
+def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks,
+                 ncu_traffic=lambda *a: None):
     from compliancedex_b200 import _lib
     from compliancedex_b200.distributed import global_argmin
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     B, iters = args.candidates, args.iters
-    gp, opt, q0, T0, k0, palm, N = _make(rank, B, iters, dev)
+    gp, opt, q0, T0, k0, palm, N = _make(rank, B, iters, dev, args.hand, args.object)
     lib = _lib.load()
     q0d, T0d, k0d = q0.to(dev), T0.to(dev), k0.to(dev)
 
@@ -110,7 +112,7 @@ def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks
         "metric": METRIC, "value": total_units / (ms_step * 1e-3), "unit": "candidate-iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": _workload_name(B, iters, world), "ms_per_iteration": ms_step / iters,
+        "config": {"workload": _workload_name(B, iters, world, args.hand, args.object, N), "ms_per_iteration": ms_step / iters,
                    "l2_policy": "latency-bound loop: the 0.6 MB state (L, E11^-1) and the per-candidate buffers are re-used "
                                 "every iteration by design (resident working set), no flush applies",
                    "argmin": {"value": best[0], "global_index": best[1]}},
@@ -121,7 +123,10 @@ def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if peak else None,
                      "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json has no "
                                     "FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0)),
-                     "flop_per_query": flop_ext, "queries_per_launch": ext_queries, "traffic": None,
+                     "flop_per_query": flop_ext, "queries_per_launch": ext_queries,
+                     "traffic": ncu_traffic("r01_ncu_pregrasp_v4_summary.json", "gpis_var_kernel") if B == 1024 and N == 196 else None,
+                     "dominant_by_time": "pg_step_kernel (latency-bound scalar FP64: Kabsch SVD, costs, analytic reverse pass, Adam, "
+                                         "float32 FK of the new iterate; ~2e4 flop per candidate) - see kernel_share",
                      "kernel_ms_per_iteration": kernel_ms, "kernel_share": share,
                      "note": "per-kernel times from one extra step with CUDA events around each launch (cdx_pregrasp_profile); the mean-only query runs on a forked stream, overlapped with the extended query; kernel_share is over the main-stream critical path",
                      "fp64_pipes": pipes},
