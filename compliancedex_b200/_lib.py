@@ -52,8 +52,10 @@ SIGNATURES = {
     "cdx_gpis_set_var_mode": (c_int, [c_void_p, c_int]),
     "cdx_gpis_query_host": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_gpis_query_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p]),
+    "cdx_grid_surface": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "cdx_hand_load": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "cdx_hand_fk": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
+    "cdx_collision_cost": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_init": (c_int, [c_void_p, ctypes.POINTER(PregraspParams), c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_run": (c_int, [c_void_p, c_int, c_void_p]),
     "cdx_pregrasp_eval": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -311,6 +311,42 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   pg_emit_points(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
 }
 
+// ProbabilisticGraspOptimizer.compute_collision_loss (optimize_pregrasp.py:684-701) on anchor poses [B,A,3]: thread per
+// candidate; masked-out terms are multiplied by 0.0 exactly as the reference does (so NaN / inf propagate the same way)
+__global__ void __launch_bounds__(128) pg_collision_kernel(const double* __restrict__ anchor, int64_t B, int A,
+                                                           const int* __restrict__ left, const int* __restrict__ right, int npairs,
+                                                           double threshold, const double* __restrict__ palm,
+                                                           double* __restrict__ cost) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const double* a = anchor + b * A * 3;
+  double c = 0.0;
+  for (int p = 0; p < npairs; p++) {
+    const double* l = a + left[p] * 3;
+    const double* r = a + right[p] * 3;
+    const double dx = l[0] - r[0], dy = l[1] - r[1], dz = l[2] - r[2];
+    const double dist = sqrt(dx * dx + dy * dy + dz * dz);
+    double inv = 1.0 / dist;
+    if (!(dist < threshold)) inv *= 0.0;
+    c += inv;
+  }
+  double zc = 0.0;
+  for (int i = 0; i < A; i++) {
+    const double z = a[i * 3 + 2];
+    double v = 1.0 / z * 0.1;
+    if (!(z < 0.02)) v *= 0.0;
+    zc += v;
+  }
+  c += zc;
+  if (palm) {
+    const double z = palm[b * 6 + 2];
+    double v = 1.0 / z;
+    if (!(z < 0.02)) v *= 0.0;
+    c += v;
+  }
+  cost[b] = c;
+}
+
 // arg-min with lowest-index tie-break over opt_value (NaN / inf never win unless everything is)
 __global__ void __launch_bounds__(1024) pg_argmin_kernel(const double* __restrict__ v, int64_t B, int64_t offset,
                                                          double* __restrict__ out) {
@@ -405,6 +441,20 @@ extern "C" int cdx_hand_fk(cdx_ctx* ctx, const double* q, const double* palm, in
   S.n_dofs = s->setup.n_dofs;
   pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(s->hand_dev, B, 1, S, q, nullptr, palm, nullptr,
                                                                               nullptr, nullptr, nullptr, tips);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}
+
+extern "C" int cdx_collision_cost(cdx_ctx* ctx, const double* anchor, int64_t B, int A, const int* left, const int* right,
+                                  int npairs, double threshold, const double* palm, double* cost, void* stream) {
+  if (!ctx || B < 0 || A < 1 || npairs < 0 || (B > 0 && (!anchor || !cost)) || (npairs > 0 && (!left || !right))) {
+    cdx_set_error("cdx_collision_cost: bad argument");
+    return CDX_ERR_ARG;
+  }
+  if (B == 0) return CDX_OK;
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  pg_collision_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(anchor, B, A, left, right, npairs, threshold,
+                                                                                 palm, cost);
   CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
 }

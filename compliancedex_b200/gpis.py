@@ -235,3 +235,38 @@ class GPIS:
         n = g / (torch.norm(g, dim=1, keepdim=True) + 1e-8)
         return (mean.view(steps, steps, steps).float().cpu().numpy(), std.view(steps, steps, steps).float().cpu().numpy(),
                 n.view(steps, steps, steps, 3).float().cpu().numpy(), np.asarray(lb), np.asarray(ub))
+
+    def topcd(self, test_mean, test_normal, lb, ub, steps=100):
+        """gpis.py:127-150: surface point cloud of a mean grid - voxels with mean < 0 that have a 6-neighbour with
+        mean >= 0 (interior voxels only), in C index order, with their normals.  Like the reference, TENSOR inputs are
+        flipped along the last axis first (`[:,:,::-1]`), numpy inputs are used as they are.  The stencil and the ordered
+        compaction run on the GPU (csrc/cdx_grid.cu); the coordinates come from numpy's linspace so that they are the
+        reference's bit for bit."""
+        lb, ub = np.asarray(lb), np.asarray(ub)
+        if torch.is_tensor(test_mean):
+            test_mean = test_mean.cpu().numpy()[:, :, ::-1]
+        if torch.is_tensor(test_normal):
+            test_normal = test_normal.cpu().numpy()[:, :, ::-1]
+        if self._ctx is None:
+            self._ensure_ctx(self.X1.device if hasattr(self, "X1") and torch.is_tensor(self.X1) else "cuda")
+        dev = torch.device("cuda", self._device)
+        m = torch.from_numpy(np.ascontiguousarray(test_mean, dtype=np.float32)).to(dev)
+        if tuple(m.shape) != (steps, steps, steps):
+            raise ValueError(f"topcd: test_mean must be [{steps},{steps},{steps}], got {tuple(m.shape)}")
+        idx = torch.empty(steps ** 3, dtype=torch.int64, device=dev)
+        cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+        _lib.check(_lib.load().cdx_grid_surface(self._ctx, _ptr(m), int(steps), _ptr(idx), _ptr(cnt), _stream(self._device)))
+        lin = idx[:int(cnt.item())].cpu().numpy()
+        i, j, k = lin // (steps * steps), (lin // steps) % steps, lin % steps
+        xs, ys, zs = (np.linspace(lb[a], ub[a], steps) for a in range(3))
+        points = np.stack([xs[j], ys[i], zs[k]], axis=1)          # meshgrid(indexing="xy"): [i,j,k] -> (x[j], y[i], z[k])
+        normals = np.asarray(test_normal)[i, j, k]
+        return points, normals
+
+    def save_visualization_data(self, name, lb, ub, steps=100):
+        """what train_gpis_completion.py:60-61 / gpis.py:264-266 write next to the state: gpis_states/{name}.npz with
+        float32 grids mean, var (the std, as the reference names it), normal and the box ub, lb."""
+        mean, std, normal, lb, ub = self.get_visualization_data(lb, ub, steps)
+        np.savez(f"gpis_states/{name}.npz" if not str(name).endswith(".npz") else name, mean=mean, var=std, normal=normal,
+                 ub=ub, lb=lb)
+        return mean, std, normal, lb, ub

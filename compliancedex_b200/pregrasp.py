@@ -49,6 +49,7 @@ class ProbabilisticGraspOptimizer:
                  optimize_palm=False, device="cuda", noise_seed=0, env_offset=0):
         """robot_urdf: URDF path (as the reference), or 'leap' / 'allegro' / a hand JSON of data/hands."""
         self.device = torch.device(device)
+        self._robot_urdf = robot_urdf
         self.tree = tree_for(robot_urdf, ee_link_names, ee_link_offsets)
         self.ref_q = torch.tensor(ref_q)                                         # float32 (:634)
         self.num_iters = num_iters
@@ -214,8 +215,34 @@ class ProbabilisticGraspOptimizer:
         _lib.check(_lib.load().cdx_pregrasp_argmin(self._ctx, _ptr(out), self._stream()))
 
     def compute_collision_loss(self, joint_angles, palm_poses=None):
-        # optimize_pregrasp.py:671-701 is dead code on this path (its call at :765 is commented out)
-        raise NotImplementedError("compute_collision_loss is not on the prob path (call commented out at optimize_pregrasp.py:765)")
+        """optimize_pregrasp.py:671-701 (dormant on the prob path: its call at :765 is commented out, so it is not part
+        of the fused step; provided for API parity).  float32 FK of the 4 anchor links -> world frame -> pair / floor /
+        palm barriers.  joint_angles [B,16], palm_poses [B,6] (default: the constructor's palm_offset) -> cost [B]."""
+        if self.anchor_link_names is None or self.collision_pairs is None:
+            raise ValueError("compute_collision_loss needs anchor_link_names, anchor_link_offsets and collision_pairs")
+        dev = torch.device("cuda", self._dev_index())
+        lib = _lib.load()
+        if getattr(self, "_anchor_ctx", None) is None:
+            t = tree_for(self._robot_urdf, self.anchor_link_names, self.anchor_link_offsets)   # 4 anchors, like the shipped hands
+            ctx = _lib.new_context(self._dev_index())
+            _lib.check(lib.cdx_hand_load(ctx, t.n_bodies, _np_ptr(t.parent), _np_ptr(t.dof), _np_ptr(t.axis), _np_ptr(t.sign),
+                                         _np_ptr(t.rot), _np_ptr(t.xyz), t.n_dofs, _np_ptr(t.tip_body), _np_ptr(t.tip_offset)))
+            pairs = np.asarray(self.collision_pairs, dtype=np.int32).reshape(-1, 2)
+            self._anchor_ctx = ctx
+            self._pair_left = torch.from_numpy(np.ascontiguousarray(pairs[:, 0])).to(dev)
+            self._pair_right = torch.from_numpy(np.ascontiguousarray(pairs[:, 1])).to(dev)
+        if palm_poses is None:
+            palm_poses = self.palm_offset
+        q = joint_angles.detach().to(dev).double().contiguous()
+        palm = palm_poses.detach().to(dev).double().contiguous()
+        B = q.shape[0]
+        anchors = torch.empty(B, 4, 3, dtype=torch.float64, device=dev)
+        cost = torch.empty(B, dtype=torch.float64, device=dev)
+        _lib.check(lib.cdx_hand_fk(self._anchor_ctx, _ptr(q), _ptr(palm), B, _ptr(anchors), self._stream()))
+        _lib.check(lib.cdx_collision_cost(self._anchor_ctx, _ptr(anchors), B, 4, _ptr(self._pair_left), _ptr(self._pair_right),
+                                          int(self._pair_left.numel()), float(self.collision_pair_threshold),
+                                          _ptr(palm) if self.optimize_palm else None, _ptr(cost), self._stream()))
+        return cost
 
 
 optimizers = {"prob": ProbabilisticGraspOptimizer}   # optimize_pregrasp.py:842-848; other modes are out of scope (DESIGN.md)

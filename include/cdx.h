@@ -76,6 +76,11 @@ int cdx_gpis_query_host(cdx_ctx* ctx, const double* X_host, int64_t M, double* m
 int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha_dev, const double* X_dev, int64_t M, double* mean_dev,
                            double* grad_mean_dev, void* stream);
 
+/* GPIS.topcd (gpis.py:127-150): surface voxels of a [steps,steps,steps] float32 mean grid (row-major) - mean < 0 and at
+ * least one 6-neighbour with mean >= 0, interior voxels only.  Writes the linear indices in ascending order to
+ * idx_dev (capacity steps^3) and their number to count_dev[0]. */
+int cdx_grid_surface(cdx_ctx* ctx, const float* mean_dev, int steps, long long* idx_dev, long long* count_dev, void* stream);
+
 /* ------------------------------------------------------------------ hand model + pregrasp -------------- */
 /* Kinematic tree in URDF link order (robot_model.py:115-127, urdf_utils.py:28-83): body i has parent[i] < i
  * (-1 for the root), dof[i] = column of q driving it or -1 (fixed), axis[i] in {0,1,2} with axis_sign[i] = +-1
@@ -89,6 +94,13 @@ int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, const int* dof,
 /* ProbabilisticGraspOptimizer.forward_kinematics (optimize_pregrasp.py:657-669): q_dev [B,n_dofs] f64,
  * palm_dev [B,6] f64 (xyz + XYZ Euler) -> tips_dev [B,4,3] f64 (FK evaluated in float32 like the reference). */
 int cdx_hand_fk(cdx_ctx* ctx, const double* q_dev, const double* palm_dev, int64_t B, double* tips_dev, void* stream);
+
+/* ProbabilisticGraspOptimizer.compute_collision_loss (optimize_pregrasp.py:684-701) on world-frame anchor positions
+ * anchor_dev [B,A,3] (cdx_hand_fk of the anchor links): sum over pairs of 1/dist where dist < threshold, + 0.1/z for
+ * anchors below z = 0.02, + 1/z of the palm below 0.02 when palm_dev [B,6] is given (optimize_palm).  left_dev /
+ * right_dev: int32 [npairs] DEVICE arrays of anchor indices.  cost_dev [B]. */
+int cdx_collision_cost(cdx_ctx* ctx, const double* anchor_dev, int64_t B, int A, const int* left_dev, const int* right_dev,
+                       int npairs, double threshold, const double* palm_dev, double* cost_dev, void* stream);
 
 typedef struct cdx_pregrasp_params {
   int32_t num_copies;            /* len(pregrasp_coefficients), optimize_pregrasp.py:623-625 (<= 4) */

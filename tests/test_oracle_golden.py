@@ -104,3 +104,34 @@ def test_pregrasp_oracle_matches_reference(tag, hand, state, golden_dir):
     for a, nm in zip(res[:5], ["opt_q", "opt_compliance", "opt_target", "opt_palm", "opt_margin"]):
         assert np.array_equal(np.isnan(a.detach().numpy()), np.isnan(g[nm]))
         assert np.nanmax(np.abs(a.detach().numpy() - g[nm])) < 1e-4
+
+
+def test_topcd_oracle_matches_reference_loop(golden_dir):
+    """oracle.topcd (vectorised) against the reference's triple loop (gpis.py:127-150), numpy and tensor inputs"""
+    import numpy as np
+    import torch
+    from oracle.gpis_oracle import topcd
+    ref = np.load(os.path.join(golden_dir, "gpis_topcd_banana18.npz"))
+    steps = ref["mean"].shape[0]
+    pts, nrm = topcd(ref["mean"], ref["normal"], ref["lb"], ref["ub"], steps)
+    assert np.array_equal(pts, ref["points"]) and np.array_equal(nrm, ref["normals"])
+    pts, nrm = topcd(torch.from_numpy(ref["mean"]), torch.from_numpy(ref["normal"]), ref["lb"], ref["ub"], steps)
+    assert np.array_equal(pts, ref["points_tensor_in"]) and np.array_equal(nrm, ref["normals_tensor_in"])
+    assert len(ref["points"]) > 20
+
+
+@pytest.mark.parametrize("hand", ["leap", "allegro"])
+def test_collision_loss_oracle_matches_reference(hand, golden_dir):
+    """oracle compute_collision_loss vs the reference's (optimize_pregrasp.py:671-701): pair, floor and palm barriers"""
+    from compliancedex_b200 import hand_path
+    ref = np.load(os.path.join(golden_dir, "pregrasp_collision.npz"))
+    q, palm = torch.from_numpy(ref[f"{hand}_q"]), torch.from_numpy(ref[f"{hand}_palm"])
+    for opt_palm in (True, False):
+        o = PregraspOracle(hand_path(hand), palm.numpy(), 1, optimize_palm=opt_palm)
+        got = o.compute_collision_loss(q, palm).numpy()
+        want = ref[f"{hand}_cost_palm{int(opt_palm)}"]
+        assert np.allclose(got, want, rtol=1e-6, atol=1e-9), np.abs(got - want).max()
+    o = PregraspOracle(hand_path(hand), palm.numpy(), 1, optimize_palm=True)
+    got = o.compute_collision_loss(q, palm, threshold=0.08).numpy()
+    assert np.allclose(got, ref[f"{hand}_cost_thr008"], rtol=1e-6, atol=1e-9)
+    assert (ref[f"{hand}_cost_thr008"] != ref[f"{hand}_cost_palm1"]).any()      # the pair term is exercised

@@ -146,3 +146,25 @@ def test_errors():
                                       palm_offset=np.zeros((2, 6)), num_iters=1, ref_q=doc["ref_q"])
     with pytest.raises(RuntimeError):
         opt.optimize(torch.zeros(2, 16), torch.zeros(2, 4, 3), torch.ones(2, 4), 1, GPIS(0.08, 1.0))   # unfitted GPIS
+
+
+@pytest.mark.parametrize("hand", ["leap", "allegro"])
+def test_collision_loss_against_reference_golden(hand, golden_dir):
+    """compute_collision_loss (optimize_pregrasp.py:671-701; dormant on the prob path, provided for API parity): CUDA FK of
+    the anchor links + barrier kernel vs the reference's own outputs.  float32 FK: libdevice sin/cos differ from torch
+    CPU's in the last bit, amplified by 1/z near the floor -> 1e-4 relative."""
+    from compliancedex_b200 import ProbabilisticGraspOptimizer, load_hand
+    ref = np.load(os.path.join(golden_dir, "pregrasp_collision.npz"))
+    doc = load_hand(hand)
+    q, palm = torch.from_numpy(ref[f"{hand}_q"]), torch.from_numpy(ref[f"{hand}_palm"])
+    for opt_palm, thr, key in ((True, 0.02, "cost_palm1"), (False, 0.02, "cost_palm0"), (True, 0.08, "cost_thr008")):
+        opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                          palm_offset=palm.numpy(), num_iters=1, ref_q=doc["ref_q"], optimize_palm=opt_palm,
+                                          anchor_link_names=doc["collision_links"], anchor_link_offsets=doc["collision_offsets"],
+                                          collision_pairs=doc["collision_pairs"], collision_pair_threshold=thr)
+        got = opt.compute_collision_loss(q.cuda(), palm.cuda()).cpu().numpy()
+        want = ref[f"{hand}_{key}"]
+        assert got.shape == want.shape
+        assert np.allclose(got, want, rtol=1e-4, atol=1e-7), np.abs(got - want).max()
+        got2 = opt.compute_collision_loss(q.cuda()).cpu().numpy()            # default palm_poses = palm_offset (:672-673)
+        assert np.array_equal(got, got2)
