@@ -24,5 +24,5 @@ def hand_path(hand):
 
 
 from .hand import load_hand
-from .pregrasp import (ProbabilisticGraspOptimizer, optimizers, EE_OFFSETS, WRIST_OFFSET, FINGERTIP_LB,
+from .pregrasp import (ProbabilisticGraspOptimizer, KinGPISGraspOptimizer, GPISGraspOptimizer, optimizers, EE_OFFSETS, WRIST_OFFSET, FINGERTIP_LB,
                        FINGERTIP_UB)

@@ -34,6 +34,8 @@ class PregraspParams(ctypes.Structure):
         ("eps", c_double),
         ("compliance_min", c_double),
         ("track_after", ctypes.c_int32),
+        ("variant", ctypes.c_int32),
+        ("rms_alpha", ctypes.c_double),
     ]
 
 
@@ -55,12 +57,14 @@ SIGNATURES = {
     "cdx_grid_surface": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "cdx_hand_load": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "cdx_hand_fk": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
+    "cdx_hand_fk_recursive": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "cdx_collision_cost": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_init": (c_int, [c_void_p, ctypes.POINTER(PregraspParams), c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_run": (c_int, [c_void_p, c_int, c_void_p]),
     "cdx_pregrasp_eval": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_results": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cdx_pregrasp_latched_margin": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_argmin": (c_int, [c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_profile": (c_int, [c_void_p, c_int]),
     "cdx_pregrasp_profile_read": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_int), c_void_p]),

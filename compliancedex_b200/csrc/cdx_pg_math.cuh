@@ -106,17 +106,32 @@ CDX_HD float cdx_quat_raw(const float* R, int branch, float one, float* q) {
 // (the quaternion normaliser 0.5/math.sqrt(.) is a python float, i.e. a constant).
 //   q32: joint angles already cast to float32 (optimize_pregrasp.py:665)
 //   tip[3], J[a][c] = d tip[a] / d q[ch.dofs[c]]   (float32 arithmetic throughout, like the reference)
-CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, float (*J)[CDX_MAX_CHAIN_DOF]) {
+//   q64 (optional): the angles as float64 - then cos/sin are evaluated in double and rounded to float32, which is what
+//   x_rot/y_rot/z_rot do with a float64 q (their buffer is float32, spatial_vector_algebra.py:19-24): the Kin optimizers
+//   pass q without the .float() cast (optimize_pregrasp.py:436)
+//   With q64 the chain is also composed the way compute_forward_kinematics(recursive=True) does it (rigid_body.py:85-127:
+//   every body applies its joint pose to the poses of its descendants, i.e. tip-to-root association
+//   J_0 (J_1 (... (J_{n-1} I)))); the Jacobian keeps using the root-to-tip prefix frames (same quantities up to float32
+//   rounding).
+CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, float (*J)[CDX_MAX_CHAIN_DOF],
+                          const double* q64 = nullptr) {
   float R[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
   float p[3] = {0.f, 0.f, 0.f};
   float om[CDX_MAX_CHAIN_DOF][3], org[CDX_MAX_CHAIN_DOF][3];
+  float jall[CDX_MAX_CHAIN][9];
   int nd = 0;
   for (int i = 0; i < ch.n; i++) {
-    float jr[9];
+    float* jr = jall[i];
     const float* F = ch.fixed_rot[i];
     if (ch.dof[i] >= 0) {
       const float ang = CDX_FM(ch.sign[i], q32[ch.dof[i]]);
-      const float c = cosf(ang), s = sinf(ang);   // torch.cos/sin on a CUDA float32 tensor are these libdevice functions
+      float c, s;
+      if (q64) {
+        const double a64 = (double)ch.sign[i] * q64[ch.dof[i]];
+        c = (float)cos(a64); s = (float)sin(a64);
+      } else {
+        c = cosf(ang); s = sinf(ang);             // torch.cos/sin on a CUDA float32 tensor are these libdevice functions
+      }
       // fixed @ R_axis(ang): the two columns orthogonal to the axis mix, the axis column is kept
       const int a = ch.axis[i], u = (a + 1) % 3, v = (a + 2) % 3;
       for (int r = 0; r < 3; r++) {
@@ -139,6 +154,20 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
       for (int r = 0; r < 3; r++) { om[nd][r] = ch.sign[i] * R[r * 3 + a]; org[nd][r] = p[r]; }
       nd++;
     }
+  }
+  if (q64) {   // recursive=True association (rigid_body.py:118-127)
+    float Ra[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f}, pa[3] = {0.f, 0.f, 0.f};
+    for (int i = ch.n - 1; i >= 0; i--) {
+      const float* jr = jall[i];
+      float Rn[9], pn[3];
+      cdx_mmf(jr, Ra, Rn);
+      for (int r = 0; r < 3; r++)
+        pn[r] = CDX_FA(CDX_FA(CDX_FA(CDX_FM(jr[r * 3], pa[0]), CDX_FM(jr[r * 3 + 1], pa[1])), CDX_FM(jr[r * 3 + 2], pa[2])), ch.xyz[i][r]);
+      for (int e = 0; e < 9; e++) Ra[e] = Rn[e];
+      for (int r = 0; r < 3; r++) pa[r] = pn[r];
+    }
+    for (int e = 0; e < 9; e++) R[e] = Ra[e];
+    for (int r = 0; r < 3; r++) p[r] = pa[r];
   }
   // tip = pos + quat_rotate(quat, offset)   (robot_model.py:255-263, se3_so3_util.py:241-250)
   const float t = R[0] + R[4] + R[8] + 1.f;
@@ -265,6 +294,10 @@ struct cdx_pg_const {
   double dummy_M;      // M = 2.0 (:73)
   int gravity;         // 0: no dummy finger (:98-99)
   double uncertainty;  // :630
+  // weights of the objective's terms; the defaults are ProbabilisticGraspOptimizer.compute_loss (:719-737), the Kin / GPIS
+  // optimizers (:468-479, :377-387) use other values and a centre term instead of the contact-margin term
+  double w_reward = 200.0, w_cm = 200.0, w_tar = 20.0, force_clamp = 10.0, w_center = 0.0;
+  int var_sum = 0;     // 0: uncertainty * max_f log(100 std)   1: uncertainty * sum_f std (:386)
 };
 
 // One row (copy p of candidate b) of compute_loss (optimize_pregrasp.py:713-739) without the ref_cost term, and
@@ -333,7 +366,7 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
   for (int f = 0; f < 4; f++) {
     sm[f] = ex[f] / esum;
     z[f] = fn[f] * sm[f];
-    force_cost -= (z[f] > 10.0 ? 10.0 : z[f]);
+    force_cost -= (z[f] > C.force_clamp ? C.force_clamp : z[f]);
   }
   // ---- compute_contact_margin (:703-710), GPIS terms (:733-736)
   double vv[4][3], rr[4], dd[4][3], ang2[4], m2[4], cm = 0.0, dist_cost = 0.0, tar_cost = 0.0;
@@ -344,13 +377,21 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
     for (int r = 0; r < 3; r++) dd[f][r] = vv[f][r] / rr[f];
     ang2[f] = cdx_dot3(dd[f], n[f]);
     m2[f] = ang2[f] - C.cos_mu;
-    cm += 0.1 * log(ang2[f] + 1.0) + 0.9 * log(m2[f] + 1.0);
+    if (C.w_cm != 0.0) cm += 0.1 * log(ang2[f] + 1.0) + 0.9 * log(m2[f] + 1.0);   // prob only (:703-710)
     dist_cost += fabs(dist[f]);
     tar_cost += tdist[f];
     if (log(100.0 * sd[f]) > log(100.0 * sd[fstar])) fstar = f;
   }
-  const double var_cost = C.uncertainty * log(100.0 * sd[fstar]);
-  loss = -200.0 * reward + 1000.0 * dist_cost + 20.0 * tar_cost + (-200.0 * cm) + force_cost + var_cost;
+  const double var_cost = C.var_sum ? C.uncertainty * (sd[0] + sd[1] + sd[2] + sd[3]) : C.uncertainty * log(100.0 * sd[fstar]);
+  // centre term of the Kin / GPIS optimizers (:474-477): w |mean_f a_f - mean_f T_f|
+  double cd[3] = {0, 0, 0}, cn = 0.0;
+  if (C.w_center != 0.0) {
+    for (int f = 0; f < 4; f++)
+      for (int r = 0; r < 3; r++) cd[r] += a[f][r] - T[f][r];
+    for (int r = 0; r < 3; r++) cd[r] *= 0.25;
+    cn = sqrt(cdx_dot3(cd, cd));
+  }
+  loss = -C.w_reward * reward + 1000.0 * dist_cost + C.w_tar * tar_cost + (-C.w_cm * cm) + force_cost + var_cost + C.w_center * cn;
 
   // ================================================================================ reverse pass
   double gS1[5][3], gS2[5][3], gw[5], gR[9], gt[3] = {0, 0, 0};
@@ -359,12 +400,12 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
   for (int f = 0; f < 4; f++) { gk[f] = 0.0; for (int r = 0; r < 3; r++) { ga[f][r] = 0.0; gTo[f][r] = 0.0; } }
   // softmin / clamp(max=10) adjoint:  force_cost = -sum_f min(z_f, 10),  z_f = fn_f sm_f
   double gz[4], gfn[4], zs = 0.0;
-  for (int f = 0; f < 4; f++) { gz[f] = (z[f] <= 10.0) ? -1.0 : 0.0; zs += gz[f] * z[f]; }
+  for (int f = 0; f < 4; f++) { gz[f] = (z[f] <= C.force_clamp) ? -1.0 : 0.0; zs += gz[f] * z[f]; }
   for (int f = 0; f < 4; f++) gfn[f] = gz[f] * sm[f] * (1.0 - fn[f]) + sm[f] * zs;
   for (int f = 0; f < 4; f++) {
     // reward terms
     const double pass = (mraw[f] >= -0.9999) ? 1.0 : 0.0;
-    const double Gang = -200.0 * (0.2 / (ang[f] + 1.0) + 0.8 * pass / (margin[f] + 1.0));
+    const double Gang = -C.w_reward * (0.2 / (ang[f] + 1.0) + 0.8 * pass / (margin[f] + 1.0));
     double gdir[3], gdiff[3];
     for (int r = 0; r < 3; r++) gdir[r] = Gang * neq[f][r];
     // neq = R n
@@ -388,20 +429,29 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
     cdx_mtv(R, gdiff, rt);
     for (int r = 0; r < 3; r++) gS1[f][r] += rt[r];
     // contact margin (static pose)
-    const double G2 = -200.0 * (0.1 / (ang2[f] + 1.0) + 0.9 / (m2[f] + 1.0));
-    for (int r = 0; r < 3; r++) {
-      const double gv = G2 * (n[f][r] - ang2[f] * dd[f][r]) / rr[f];
-      ga[f][r] += gv;
-      gTo[f][r] -= gv;
+    if (C.w_cm != 0.0) {
+      const double G2 = -C.w_cm * (0.1 / (ang2[f] + 1.0) + 0.9 / (m2[f] + 1.0));
+      for (int r = 0; r < 3; r++) {
+        const double gv = G2 * (n[f][r] - ang2[f] * dd[f][r]) / rr[f];
+        ga[f][r] += gv;
+        gTo[f][r] -= gv;
+      }
     }
     // GPIS terms
     const double sg = dist[f] > 0.0 ? 1.0 : (dist[f] < 0.0 ? -1.0 : 0.0);
     for (int r = 0; r < 3; r++) {
       ga[f][r] += 1000.0 * sg * gmu[f][r];
-      gTo[f][r] += 20.0 * gT[f][r];
+      gTo[f][r] += C.w_tar * gT[f][r];
+      if (C.w_center != 0.0 && cn > 0.0) {
+        const double gc = C.w_center * 0.25 * cd[r] / cn;
+        ga[f][r] += gc;
+        gTo[f][r] -= gc;
+      }
+      if (C.var_sum) ga[f][r] += C.uncertainty * gsd[f][r];
     }
   }
-  for (int r = 0; r < 3; r++) ga[fstar][r] += C.uncertainty / sd[fstar] * gsd[fstar][r];
+  if (!C.var_sum)
+    for (int r = 0; r < 3; r++) ga[fstar][r] += C.uncertainty / sd[fstar] * gsd[fstar][r];
   // t = sum_i w_i (S2_i - R S1_i) / W
   double rgt[3];
   cdx_mtv(R, gt, rgt);
@@ -461,6 +511,11 @@ struct cdx_pg_setup {
   double ref_q[16];                  // float32 values widened (:634)
   int n_dofs;
   int optimize_palm;
+  // optimizer variant (cdx_pregrasp_params.variant): 0 = ProbabilisticGraspOptimizer, 1 = KinGPISGraspOptimizer,
+  // 2 = GPISGraspOptimizer (the "q" slot holds tip_pose [4,3] directly: no hand, no FK)
+  int variant = 0;
+  double w_ref = 10.0;               // weight of |q - ref_q| (:731 10, :478 20, GPIS variant 0)
+  double w_pre = 5.0;                // weight of the pregrasp tips' own distance (:757-759; Kin / GPIS variants 0)
   cdx_pg_const C;
 };
 
@@ -493,7 +548,7 @@ CDX_HD void cdx_pg_closure(const cdx_pg_setup& P, const cdx_hand_dev& hand, cons
   double refn = 0.0;
   for (int i = 0; i < P.n_dofs; i++) refn += (q[i] - P.ref_q[i]) * (q[i] - P.ref_q[i]);
   refn = sqrt(refn);
-  const double ref_cost = 10.0 * refn;
+  const double ref_cost = P.w_ref * refn;
   total = 0.0;
   double gtips[4][3], wsum = 0.0;
   for (int f = 0; f < 4; f++) {
@@ -528,8 +583,8 @@ CDX_HD void cdx_pg_closure(const cdx_pg_setup& P, const cdx_hand_dev& hand, cons
   }
   // :757-763
   for (int f = 0; f < 4; f++) {
-    total -= 5.0 * G.mean9[4 + f];
-    for (int r = 0; r < 3; r++) gtips[f][r] -= 5.0 * G.gmean9[(4 + f) * 3 + r];
+    total -= P.w_pre * G.mean9[4 + f];
+    for (int r = 0; r < 3; r++) gtips[f][r] -= P.w_pre * G.gmean9[(4 + f) * 3 + r];
   }
   for (int r = 0; r < 6; r++) gpalm[r] = 0.0;
   if (P.optimize_palm) {
@@ -539,7 +594,7 @@ CDX_HD void cdx_pg_closure(const cdx_pg_setup& P, const cdx_hand_dev& hand, cons
   }
   // tips = Rw tl + palm_pos (:667-668)
   double gRw[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-  for (int i = 0; i < P.n_dofs; i++) gq[i] = refn > 0.0 ? wsum * 10.0 * (q[i] - P.ref_q[i]) / refn : 0.0;  // norm'(0) = 0 in torch
+  for (int i = 0; i < P.n_dofs; i++) gq[i] = refn > 0.0 ? wsum * P.w_ref * (q[i] - P.ref_q[i]) / refn : 0.0;  // norm'(0) = 0 in torch
   for (int f = 0; f < 4; f++) {
     double gl[3];
     cdx_mtv(Rw, gtips[f], gl);

@@ -31,6 +31,9 @@ struct cdx_pg_state {
   double *dist = nullptr, *sd = nullptr, *gmu = nullptr, *gsd = nullptr;   // [B*U*4], [.. ,3]
   double *mean9 = nullptr, *gmean9 = nullptr;                               // [B*9], [B*9,3]
   double *loss = nullptr, *margin = nullptr, *grad = nullptr;               // [B], [B,4], [B,38]
+  // Kin / GPIS variants: `opt_margin = margin` of the WHOLE batch whenever any candidate improved (:491-494)
+  double *mring = nullptr, *latched = nullptr;   // [2][B,4] margins of the last two iterations, [B,4] latched copy
+  int* latch = nullptr;                          // [0],[1]: iteration that improved (by parity), [2]: latched iteration
   int it_host = 0;           // absolute iteration index (keys the noise stream, Adam bias correction, s > 20)
   bool points_valid = false; // tl / J / Xext / Xmean describe the current iterate
   cudaStream_t side = nullptr;              // forked stream for the mean-only GPIS query
@@ -38,6 +41,7 @@ struct cdx_pg_state {
   double* adam_tab = nullptr;  // [tab_cap][2]: 1 - beta1^t, sqrt(1 - beta2^t) for t = index + 1
   int tab_cap = 0;
   cdx_hand_dev* hand_dev = nullptr;
+  int hand_n_dofs = 0;
   bool prof = false;
   std::vector<cudaEvent_t> prof_ev;   // 5 events per profiled iteration
 };
@@ -54,17 +58,25 @@ __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ 
                                                int f, const double* q, const double* Tf, const double* palm6,
                                                double* __restrict__ tl, float* __restrict__ J, double* __restrict__ Xext,
                                                double* __restrict__ Xmean, double* __restrict__ tips_out) {
-  float q32[16];
-#pragma unroll
-  for (int i = 0; i < 16; i++) q32[i] = i < S.n_dofs ? (float)q[i] : 0.f;                    // q.float(), :665
-  float tip[3], Jf[3][CDX_MAX_CHAIN_DOF];
-  cdx_fk_finger(hand->finger[f], q32, tip, Jf);
-  const double tlf[3] = {(double)tip[0], (double)tip[1], (double)tip[2]};                    // .double(), :666
-  double Rw[9], tw[3];
-  cdx_euler_xyz(palm6 + 3, Rw, nullptr, nullptr, nullptr);
-  cdx_mv(Rw, tlf, tw);
-  for (int r = 0; r < 3; r++) tw[r] += palm6[r];
   const int64_t gid = b * 4 + f;
+  double tlf[3], tw[3];
+  float Jf[3][CDX_MAX_CHAIN_DOF];
+  if (S.variant == 2) {   // GPISGraspOptimizer: tip_pose itself is the parameter (:345,:361)
+    for (int r = 0; r < 3; r++) { tlf[r] = q[f * 3 + r]; tw[r] = tlf[r]; }
+    for (int r = 0; r < 3; r++)
+      for (int c = 0; c < CDX_MAX_CHAIN_DOF; c++) Jf[r][c] = 0.f;
+  } else {
+    float q32[16], tip[3];
+#pragma unroll
+    for (int i = 0; i < 16; i++) q32[i] = i < S.n_dofs ? (float)q[i] : 0.f;                  // q.float(), :665
+    // Kin variant: q stays float64 and the chain is composed recursively (:436, robot_model.py:243-251)
+    cdx_fk_finger(hand->finger[f], q32, tip, Jf, S.variant == 1 ? q : nullptr);
+    for (int r = 0; r < 3; r++) tlf[r] = (double)tip[r];                                     // .double(), :666
+    double Rw[9];
+    cdx_euler_xyz(palm6 + 3, Rw, nullptr, nullptr, nullptr);
+    cdx_mv(Rw, tlf, tw);
+    for (int r = 0; r < 3; r++) tw[r] += palm6[r];
+  }
   if (tips_out) {
     for (int r = 0; r < 3; r++) tips_out[gid * 3 + r] = tw[r];
     return;
@@ -79,7 +91,7 @@ __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ 
     if (u < seen) continue;   // this coefficient row already has its query block
     seen = u + 1;
     double* x = Xext + ((b * U + u) * 4 + f) * 3;
-    for (int r = 0; r < 3; r++) x[r] = Tf[r] + S.coeff[p][f] * (tw[r] - Tf[r]);              // :750
+    for (int r = 0; r < 3; r++) x[r] = S.variant ? tw[r] : Tf[r] + S.coeff[p][f] * (tw[r] - Tf[r]);   // :750 / tips (:462)
   }
   double* xm = Xmean + b * 27;
   for (int r = 0; r < 3; r++) {
@@ -129,7 +141,8 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
                const double* __restrict__ adam_tab, double* __restrict__ m1, double* __restrict__ m2,
                double* __restrict__ oq, double* __restrict__ ok, double* __restrict__ oT, double* __restrict__ opalm,
                double* __restrict__ omargin, double* __restrict__ ovalue, double* __restrict__ Xext,
-               double* __restrict__ Xmean) {
+               double* __restrict__ Xmean, double* __restrict__ mring, double* __restrict__ latched,
+               int* __restrict__ latch) {
   __shared__ double sp[CPB][NPAR];      // the candidate's parameters: q16 | k4 | T12 | palm6
   __shared__ double sr[CPB][NRED];      // reduced per-copy results
   __shared__ double sg[CPB][NPAR];      // gradient
@@ -151,12 +164,21 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   for (int f = 0; f < 4; f++) {
     cdx_mv(Rw, tlp[f], tips[f]);
     for (int r = 0; r < 3; r++) tips[f][r] += par[32 + r];
+    if (S.variant == 2)
+      for (int r = 0; r < 3; r++) tips[f][r] = par[f * 3 + r];
   }
   double refn = 0.0;
-  for (int i = l; i < nd; i += 4) refn += (par[i] - S.ref_q[i]) * (par[i] - S.ref_q[i]);
-  refn += __shfl_xor_sync(gmask, refn, 1);
-  refn += __shfl_xor_sync(gmask, refn, 2);
-  refn = sqrt(refn);
+  if (S.w_ref != 0.0) {
+    for (int i = l; i < nd; i += 4) refn += (par[i] - S.ref_q[i]) * (par[i] - S.ref_q[i]);
+    refn += __shfl_xor_sync(gmask, refn, 1);
+    refn += __shfl_xor_sync(gmask, refn, 2);
+    refn = sqrt(refn);
+  }
+  // Kin / GPIS variants: the margin of the previous iteration becomes the latched opt_margin if anything improved then
+  if (S.variant != 0 && do_step && it > 0 && latch[(it - 1) & 1] == it - 1) {
+    latched[b * 4 + l] = mring[((it - 1) & 1) * B * 4 + b * 4 + l];
+    if (b == 0 && l == 0) latch[2] = it - 1;
+  }
   const double* m9 = mean9 + b * 9;
   const double* g9 = gmean9 + b * 27;
   // ---- copy p = l
@@ -170,7 +192,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     double a[4][3], noise[9], lossp, mg[4], ga[4][3], gTr[4][3], gkr[4];
 #pragma unroll
     for (int f = 0; f < 4; f++)
-      for (int r = 0; r < 3; r++) a[f][r] = Tp[f][r] + S.coeff[p][f] * (tips[f][r] - Tp[f][r]);
+      for (int r = 0; r < 3; r++) a[f][r] = S.variant ? tips[f][r] : Tp[f][r] + S.coeff[p][f] * (tips[f][r] - Tp[f][r]);
     const int64_t gb = prm.env_offset + b;
 #pragma unroll
     for (int e = 0; e < 9; e++) noise[e] = cdx_kabsch_noise(prm.noise_seed, it, p, gb, e);
@@ -179,7 +201,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
                reinterpret_cast<const double (*)[3]>(gsd + e0 * 3), m9, reinterpret_cast<const double (*)[3]>(g9), noise, S.C,
                lossp, mg, ga, gTr, gkr);
     const double wp = S.weight[p];
-    red[0] = wp * (lossp + 10.0 * refn);
+    red[0] = wp * (lossp + S.w_ref * refn);
 #pragma unroll
     for (int f = 0; f < 4; f++) {
       red[1 + f] = wp * mg[f];
@@ -203,7 +225,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   __syncwarp(gmask);
   // ---- :757-763 and the chain rule of finger f = l
   double total = red[0];
-  for (int f = 0; f < 4; f++) total -= 5.0 * m9[4 + f];
+  for (int f = 0; f < 4; f++) total -= S.w_pre * m9[4 + f];
   double gpalm_pm[3] = {0.0, 0.0, 0.0};
   if (S.optimize_palm) {
     const double pm = m9[8];
@@ -212,7 +234,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   }
   const int f = l;
   double gt[3], gl[3], acc[12];
-  for (int r = 0; r < 3; r++) gt[r] = sr[cl][9 + f * 3 + r] - 5.0 * g9[(4 + f) * 3 + r];
+  for (int r = 0; r < 3; r++) gt[r] = sr[cl][9 + f * 3 + r] - S.w_pre * g9[(4 + f) * 3 + r];
   cdx_mtv(Rw, gt, gl);
   for (int r = 0; r < 3; r++) {
     acc[r] = gt[r];
@@ -225,18 +247,24 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   }
   // back through .double() (:666) into the float32 FK graph; fingers take turns so shared joints would accumulate
   const float g32[3] = {(float)gl[0], (float)gl[1], (float)gl[2]};
-  const cdx_chain& ch = hand->finger[f];
-  const float* Jf = J + (b * 4 + f) * 3 * CDX_MAX_CHAIN_DOF;
-  for (int turn = 0; turn < 4; turn++) {
-    if (turn == f)
-      for (int c = 0; c < ch.ndof; c++) {
-        const float gj = Jf[c] * g32[0] + Jf[CDX_MAX_CHAIN_DOF + c] * g32[1] + Jf[2 * CDX_MAX_CHAIN_DOF + c] * g32[2];
-        sg[cl][ch.dofs[c]] += (double)gj;
-      }
+  if (S.variant == 2) {
+    for (int r = 0; r < 3; r++) sg[cl][f * 3 + r] = gt[r];       // tip_pose is the leaf
     __syncwarp(gmask);
+  } else {
+    const cdx_chain& ch = hand->finger[f];
+    const float* Jf = J + (b * 4 + f) * 3 * CDX_MAX_CHAIN_DOF;
+    for (int turn = 0; turn < 4; turn++) {
+      if (turn == f)
+        for (int c = 0; c < ch.ndof; c++) {
+          const float gj = Jf[c] * g32[0] + Jf[CDX_MAX_CHAIN_DOF + c] * g32[1] + Jf[2 * CDX_MAX_CHAIN_DOF + c] * g32[2];
+          sg[cl][ch.dofs[c]] += (double)gj;
+        }
+      __syncwarp(gmask);
+    }
   }
   double* g = sg[cl];
-  for (int i = l; i < nd; i += 4) g[i] += refn > 0.0 ? wsum * 10.0 * (par[i] - S.ref_q[i]) / refn : 0.0;
+  if (S.w_ref != 0.0)
+    for (int i = l; i < nd; i += 4) g[i] += refn > 0.0 ? wsum * S.w_ref * (par[i] - S.ref_q[i]) / refn : 0.0;
   g[16 + f] = sr[cl][5 + f];
   for (int r = 0; r < 3; r++) g[20 + f * 3 + r] = sr[cl][21 + f * 3 + r];
   for (int i = l; i < 6; i += 4) {
@@ -259,6 +287,10 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   // ---- best-iterate tracking (:822-829): BEFORE the optimiser step, only for s > track_after; NaN never updates
   const bool better = it > prm.track_after && total < ovalue[b];
   __syncwarp(gmask);                                    // every lane has read ovalue[b] before lane 0 overwrites it
+  if (S.variant != 0) {
+    mring[(it & 1) * B * 4 + b * 4 + l] = sr[cl][1 + l];
+    if (better && l == 0) latch[it & 1] = it;          // benign race: every writer stores the same value
+  }
   if (better) {
     if (l == 0) {
       ovalue[b] = total;
@@ -284,7 +316,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     else if (i < 32) { upd = prm.optimize_target != 0; grp = 2; }
     else { upd = prm.optimize_palm != 0; grp = i < 35 ? 3 : 4; }
     double pv = par[i];
-    if (upd) {
+    if (upd && S.variant == 0) {
       const double gi = g[i];
       double m = m1[b * NPAR + i], v = m2[b * NPAR + i];
       m = m + omb1 * (gi - m);
@@ -294,9 +326,19 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
       const double step = prm.lr[grp] / bc1;
       const double denom = sqrt(v) / bc2s + prm.eps;
       pv = pv - step * (m / denom);
+    } else if (upd) {
+      // torch.optim.RMSprop (:451-456, :347-352; alpha 0.99, eps 1e-8, no momentum, not centered):
+      //   square_avg = alpha square_avg + (1 - alpha) g^2;  p -= lr * g / (sqrt(square_avg) + eps)
+      const double gi = g[i];
+      double v = m2[b * NPAR + i];
+      v = v * prm.rms_alpha + (1.0 - prm.rms_alpha) * gi * gi;
+      m2[b * NPAR + i] = v;
+      pv = pv + (-prm.lr[grp] * gi) / (sqrt(v) + prm.eps);   // addcdiv_(g, avg, value=-lr): (value * g) / avg
     }
+    if (S.variant == 2 && i < 12)   // tip_pose.clamp_(box) (:402)
+      pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[i / 3][i % 3]), (double)prm.box_hi[i / 3][i % 3]);
     if (i >= 16 && i < 20) pv = clamp_lo(pv, prm.compliance_min);
-    if (i >= 20 && i < 32) {
+    if (i >= 20 && i < 32 && S.variant != 2) {   // target clamp: prob (:834) and Kin (:505); commented out at :404
       const int e = i - 20;
       pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[e / 3][e % 3]), (double)prm.box_hi[e / 3][e % 3]);
     }
@@ -375,14 +417,27 @@ __global__ void __launch_bounds__(1024) pg_argmin_kernel(const double* __restric
   }
 }
 
+// opt_margin of the Kin / GPIS variants after the last iteration: the step kernel moves an improving iteration's margins into
+// `latched` one iteration later, so the final iteration (index last) is still pending in its ring slot
+__global__ void pg_latch_read_kernel(const double* __restrict__ mring, const double* __restrict__ latched,
+                                     const int* __restrict__ latch, int64_t B, int last, double* __restrict__ out,
+                                     int* __restrict__ iter_out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool pending = last >= 0 && latch[last & 1] == last;
+  if (i < B * 4 && out) out[i] = pending ? mring[(int64_t)(last & 1) * B * 4 + i] : latched[i];
+  if (i == 0 && iter_out) iter_out[0] = pending ? last : latch[2];
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ host side
 static void pg_free_buffers(cdx_pg_state* s) {
   void* ptrs[] = {s->q, s->k, s->T, s->palm, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm, s->omargin, s->ovalue, s->tl,
                   s->J, s->Xext, s->Xmean, s->dist, s->sd, s->gmu, s->gsd, s->mean9, s->gmean9, s->loss, s->margin,
-                  s->grad};
+                  s->grad, s->mring, s->latched, s->latch};
   for (void* p : ptrs) cudaFree(p);
+  s->mring = s->latched = nullptr;
+  s->latch = nullptr;
   s->q = s->k = s->T = s->palm = s->m1 = s->m2 = s->oq = s->ok = s->oT = s->opalm = s->omargin = s->ovalue = nullptr;
   s->tl = s->Xext = s->Xmean = s->dist = s->sd = s->gmu = s->gsd = s->mean9 = s->gmean9 = s->loss = s->margin = s->grad = nullptr;
   s->J = nullptr;
@@ -425,7 +480,7 @@ extern "C" int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, cons
   cdx_pg_state* s = pg_get(ctx);
   if (!s->hand_dev) CDX_CUDA(cudaMalloc((void**)&s->hand_dev, sizeof(cdx_hand_dev)));
   CDX_CUDA(cudaMemcpy(s->hand_dev, &h, sizeof(h), cudaMemcpyHostToDevice));
-  s->setup.n_dofs = n_dofs;
+  s->setup.n_dofs = s->hand_n_dofs = n_dofs;
   ctx->hand_ready = true;
   return CDX_OK;
 }
@@ -438,9 +493,28 @@ extern "C" int cdx_hand_fk(cdx_ctx* ctx, const double* q, const double* palm, in
   cdx_pg_state* s = ctx->pg;
   cdx_pg_setup S;
   memset(&S, 0, sizeof(S));
-  S.n_dofs = s->setup.n_dofs;
+  S.n_dofs = s->hand_n_dofs;
   pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(s->hand_dev, B, 1, S, q, nullptr, palm, nullptr,
                                                                               nullptr, nullptr, nullptr, tips);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}
+
+// KinGPISGraspOptimizer.forward_kinematics (optimize_pregrasp.py:429-436): recursive FK on float64 angles; palm [B,6] =
+// the constant palm offset (xyz, zero Euler angles) repeated per candidate
+extern "C" int cdx_hand_fk_recursive(cdx_ctx* ctx, const double* q, const double* palm_offset3, int64_t B, double* tips,
+                                     void* stream) {
+  if (!ctx || !ctx->hand_ready) { cdx_set_error("cdx_hand_fk_recursive: no hand loaded"); return CDX_ERR_STATE; }
+  if (B < 0 || (B > 0 && (!q || !palm_offset3 || !tips))) { cdx_set_error("cdx_hand_fk_recursive: bad argument"); return CDX_ERR_ARG; }
+  if (B == 0) return CDX_OK;
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  cdx_pg_state* s = ctx->pg;
+  cdx_pg_setup S;
+  memset(&S, 0, sizeof(S));
+  S.n_dofs = s->hand_n_dofs;
+  S.variant = 1;
+  pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(s->hand_dev, B, 1, S, q, nullptr, palm_offset3,
+                                                                              nullptr, nullptr, nullptr, nullptr, tips);
   CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
 }
@@ -463,17 +537,42 @@ extern "C" int cdx_collision_cost(cdx_ctx* ctx, const double* anchor, int64_t B,
 
 extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int64_t B, const double* q0,
                                  const double* k0, const double* T0, const double* palm0, void* stream) {
-  if (!ctx || !ctx->hand_ready) { cdx_set_error("cdx_pregrasp_init: cdx_hand_load first"); return CDX_ERR_STATE; }
-  if (!p || B < 1 || !q0 || !k0 || !T0 || !palm0 || p->num_copies < 1 || p->num_copies > CDX_MAX_COPIES) {
-    cdx_set_error("cdx_pregrasp_init: bad argument (1 <= num_copies <= %d, B >= 1)", CDX_MAX_COPIES);
+  if (!ctx || !p) { cdx_set_error("cdx_pregrasp_init: NULL argument"); return CDX_ERR_ARG; }
+  if (p->variant < 0 || p->variant > 2) { cdx_set_error("cdx_pregrasp_init: variant must be 0, 1 or 2"); return CDX_ERR_ARG; }
+  if (p->variant != 2 && !ctx->hand_ready) { cdx_set_error("cdx_pregrasp_init: cdx_hand_load first"); return CDX_ERR_STATE; }
+  if (B < 1 || !q0 || !k0 || !T0 || !palm0 || p->num_copies < 1 || p->num_copies > CDX_MAX_COPIES ||
+      (p->variant != 0 && p->num_copies != 1)) {
+    cdx_set_error("cdx_pregrasp_init: bad argument (1 <= num_copies <= %d, exactly 1 for the Kin / GPIS variants, B >= 1)",
+                  CDX_MAX_COPIES);
     return CDX_ERR_ARG;
   }
   CDX_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = (cudaStream_t)stream;
-  cdx_pg_state* s = ctx->pg;
+  cdx_pg_state* s = pg_get(ctx);
   s->prm = *p;
   cdx_pg_setup& S = s->setup;
+  if (p->variant == 2) {   // GPISGraspOptimizer: the 12 tip coordinates take the place of the joint angles; no hand
+    S.n_dofs = 12;
+    if (!s->hand_dev) {
+      CDX_CUDA(cudaMalloc((void**)&s->hand_dev, sizeof(cdx_hand_dev)));
+      CDX_CUDA(cudaMemset(s->hand_dev, 0, sizeof(cdx_hand_dev)));
+    }
+  }
+  else S.n_dofs = s->hand_n_dofs;
   const int nd = S.n_dofs;
+  S.variant = p->variant;
+  S.C = cdx_pg_const();
+  if (p->variant == 0) { S.w_ref = 10.0; S.w_pre = 5.0; }
+  else {                  // :468-479 (Kin) / :377-387 (GPIS)
+    S.w_ref = p->variant == 1 ? 20.0 : 0.0;
+    S.w_pre = 0.0;
+    S.C.w_reward = p->variant == 1 ? 5.0 : 25.0;
+    S.C.w_cm = 0.0;
+    S.C.w_tar = 10.0;
+    S.C.force_clamp = 1.0;
+    S.C.w_center = 10.0;
+    S.C.var_sum = p->variant == 2 ? 1 : 0;
+  }
   S.P = p->num_copies;
   S.U = 0;
   for (int a = 0; a < S.P; a++) {       // identical coefficient rows share one block of GPIS queries
@@ -504,6 +603,7 @@ extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int
     PG_ALLOC(s->dist, B * U * 4); PG_ALLOC(s->sd, B * U * 4); PG_ALLOC(s->gmu, B * U * 12); PG_ALLOC(s->gsd, B * U * 12);
     PG_ALLOC(s->mean9, B * 9); PG_ALLOC(s->gmean9, B * 27);
     PG_ALLOC(s->loss, B); PG_ALLOC(s->margin, B * 4); PG_ALLOC(s->grad, B * NPAR);
+    PG_ALLOC(s->mring, B * 8); PG_ALLOC(s->latched, B * 4); PG_ALLOC(s->latch, 4);
     s->cap = B;
     s->U = U;
   }
@@ -525,6 +625,8 @@ extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int
   CDX_CUDA(cudaMemsetAsync(s->omargin, 0, sizeof(double) * B * 4, st));
   CDX_CUDA(cudaMemsetAsync(s->m1, 0, sizeof(double) * B * NPAR, st));
   CDX_CUDA(cudaMemsetAsync(s->m2, 0, sizeof(double) * B * NPAR, st));
+  CDX_CUDA(cudaMemsetAsync(s->latched, 0, sizeof(double) * B * 4, st));
+  CDX_CUDA(cudaMemsetAsync(s->latch, 0xFF, sizeof(int) * 4, st));     // -1: nothing improved yet
   pg_fill_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(s->ovalue, B, INFINITY);
   CDX_CHECK_LAUNCH(ctx);
   s->it_host = 0;
@@ -568,7 +670,7 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   pg_step_kernel<<<(unsigned)((B + CPB - 1) / CPB), CPB * 4, 0, st>>>(
       s->hand_dev, B, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd, s->mean9,
       s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,
-      s->omargin, s->ovalue, s->Xext, s->Xmean);
+      s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch);
   CDX_CHECK_LAUNCH(ctx);
   mark(st);
   return CDX_OK;
@@ -659,6 +761,21 @@ extern "C" int cdx_pregrasp_state(cdx_ctx* ctx, double* q, double* k, double* T,
   cdx_pg_state* s = ctx->pg;
   const int64_t B = s->B;
   PG_COPY(q, s->q, B * s->setup.n_dofs); PG_COPY(k, s->k, B * 4); PG_COPY(T, s->T, B * 12); PG_COPY(palm, s->palm, B * 6);
+  return CDX_OK;
+}
+
+extern "C" int cdx_pregrasp_latched_margin(cdx_ctx* ctx, double* margin, int* iter, void* stream) {
+  if (!ctx || !ctx->pg || ctx->pg->B == 0) { cdx_set_error("cdx_pregrasp_latched_margin: cdx_pregrasp_init first"); return CDX_ERR_STATE; }
+  cdx_pg_state* s = ctx->pg;
+  if (s->setup.variant == 0) {
+    cdx_set_error("cdx_pregrasp_latched_margin: only the Kin / GPIS variants latch a whole-batch margin");
+    return CDX_ERR_STATE;
+  }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  const int64_t B = s->B;
+  pg_latch_read_kernel<<<(unsigned)((B * 4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(s->mring, s->latched, s->latch, B,
+                                                                                   s->it_host - 1, margin, iter);
+  CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
 }
 

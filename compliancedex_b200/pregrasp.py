@@ -245,4 +245,129 @@ class ProbabilisticGraspOptimizer:
         return cost
 
 
-optimizers = {"prob": ProbabilisticGraspOptimizer}   # optimize_pregrasp.py:842-848; other modes are out of scope
+class KinGPISGraspOptimizer(ProbabilisticGraspOptimizer):
+    """Drop-in `KinGPISGraspOptimizer` (optimize_pregrasp.py:408-511): the fused step kernel with variant 1 -
+    recursive FK on float64 angles + a constant palm offset [3], one copy (the tips themselves are the contact points),
+    loss = -5 reward + 1000 sum|dist| + 10 sum tar_dist + 10 |centre diff| + force_cost(max 1) + 20 |q - ref_q|
+    + max_f uncertainty log(100 std), torch.optim.RMSprop, compliance >= 40, best-iterate tracking from iteration 0,
+    `flag = (opt_margin > 0).all()` with opt_margin the whole batch's margin at the last improving iteration."""
+    _variant = 1
+
+    def __init__(self, robot_urdf, ee_link_names, ee_link_offsets=EE_OFFSETS, palm_offset=WRIST_OFFSET, num_iters=1000,
+                 optimize_target=False, ref_q=None, tip_bounding_box=[FINGERTIP_LB, FINGERTIP_UB], mass=0.1,
+                 com=[0.0, 0.0, 0.0], gravity=True, uncertainty=10.0, device="cuda", noise_seed=0, env_offset=0):
+        palm = np.asarray(palm_offset, dtype=np.float64).reshape(-1)
+        if palm.size != 3:
+            raise ValueError("KinGPISGraspOptimizer adds palm_offset to [B*4,3] tip positions (:437): it must have 3 entries")
+        super().__init__(robot_urdf, ee_link_names, ee_link_offsets, palm_offset=np.zeros((1, 6)), num_iters=num_iters,
+                         optimize_target=optimize_target, ref_q=ref_q, tip_bounding_box=tip_bounding_box,
+                         pregrasp_coefficients=[[1.0, 1.0, 1.0, 1.0]], pregrasp_weights=[1.0], mass=mass, com=com,
+                         gravity=gravity, uncertainty=uncertainty, optimize_palm=False, device=device,
+                         noise_seed=noise_seed, env_offset=env_offset)
+        self.palm_offset = torch.from_numpy(palm)                                # float64 [3] (:423)
+        self.opt_margin = None
+
+    def _params(self, friction_mu):
+        p = super()._params(friction_mu)
+        p.variant = self._variant
+        lrs = [2e-3, 0.2, 1e-3] if self.optimize_target else [1e-2, 0.2, 0.0]    # :454-459
+        for i, lr in enumerate(lrs + [0.0, 0.0]):
+            p.lr[i] = lr
+        p.rms_alpha, p.eps = 0.99, 1e-8                                          # torch.optim.RMSprop defaults
+        p.compliance_min = 40.0                                                  # :506
+        p.track_after = -1                                                       # :496: every iteration
+        return p
+
+    def _palm6(self, B):
+        palm = torch.zeros(B, 6, dtype=torch.float64)
+        palm[:, :3] = self.palm_offset
+        return palm
+
+    def forward_kinematics(self, joint_angles):
+        """optimize_pregrasp.py:431-438: [B,n_dofs] -> fingertip positions [B*4,3] float64."""
+        ctx = self._own_ctx()
+        dev = self.device
+        q = joint_angles.detach().double().to(dev).contiguous()
+        B = q.shape[0]
+        palm = self._palm6(B).to(dev)
+        tips = torch.empty(B * 4, 3, dtype=torch.float64, device=dev)
+        _lib.check(_lib.load().cdx_hand_fk_recursive(ctx, _ptr(q), _ptr(palm), B, _ptr(tips), self._stream()))
+        return tips
+
+    def _init(self, joint_angles, target_pose, compliance, friction_mu, gpis):
+        self.palm6 = self._palm6(joint_angles.shape[0])
+        saved, self.palm_offset = self.palm_offset, self.palm6
+        try:
+            return super()._init(joint_angles, target_pose, compliance, friction_mu, gpis)
+        finally:
+            self.palm_offset = saved
+
+    def latched_margin(self):
+        """(opt_margin [B,4], iteration at which it was taken; -1 = never)"""
+        m = torch.empty(self._B, 4, dtype=torch.float64, device=self.device)
+        it = torch.empty(1, dtype=torch.int32, device=self.device)
+        _lib.check(_lib.load().cdx_pregrasp_latched_margin(self._ctx, _ptr(m), _ptr(it), self._stream()))
+        return m, it
+
+    def optimize(self, joint_angles, target_pose, compliance, friction_mu, gpis, verbose=True):
+        """optimize_pregrasp.py:440-511 -> (opt_joint_angle [B,n_dofs], opt_compliance [B,4], opt_target_pose [B,4,3], flag)."""
+        self._init(joint_angles, target_pose, compliance, friction_mu, gpis)
+        self.step(self.num_iters)
+        oq, ok, oT, _, _, ovalue = self.results()
+        self.opt_value = ovalue
+        self.opt_margin, _ = self.latched_margin()
+        if verbose:
+            print(self.opt_margin)
+        flag = (self.opt_margin > 0.0).all()
+        return oq, ok, oT, flag
+
+
+class _NoHand:
+    n_dofs = 12
+
+
+class GPISGraspOptimizer(KinGPISGraspOptimizer):
+    """Drop-in `GPISGraspOptimizer` (optimize_pregrasp.py:322-406): the fingertip positions [B,4,3] themselves are optimised
+    (no hand, no FK): variant 2 of the fused step - reward x25, variance cost = uncertainty * sum_f std, no ref cost,
+    RMSprop 1e-3 / 1e-3 / 0.2, tips clamped to the bounding box, compliance >= 40, target NOT clamped (:402)."""
+    _variant = 2
+
+    def __init__(self, tip_bounding_box, num_iters=2000, optimize_target=False, mass=0.1, com=[0.0, 0.0, 0.0], gravity=True,
+                 uncertainty=20.0, device="cuda", noise_seed=0, env_offset=0):
+        self.device = torch.device(device)
+        self.tree = _NoHand()
+        self.ref_q = torch.zeros(12)
+        self.num_iters = num_iters
+        self.palm_offset = torch.zeros(3, dtype=torch.float64)
+        self.optimize_target, self.optimize_palm = optimize_target, False
+        self.tip_bounding_box = [torch.tensor(tip_bounding_box[0]).view(-1, 3), torch.tensor(tip_bounding_box[1]).view(-1, 3)]
+        self.pregrasp_coefficients = torch.tensor([[1.0, 1.0, 1.0, 1.0]])
+        self.pregrasp_weights = torch.tensor([1.0]).double()
+        self.mass, self.com, self.gravity, self.uncertainty = mass, com, gravity, uncertainty
+        self.noise_seed, self.env_offset = int(noise_seed), int(env_offset)
+        self.opt_value = self.opt_margin = None
+        self._ctx = None
+        self._hand_loaded_for = None
+
+    def _bind(self, ctx):
+        self._ctx = ctx                                                          # no hand to load
+
+    def _params(self, friction_mu):
+        p = super()._params(friction_mu)
+        lrs = [1e-3, 0.2, 1e-3 if self.optimize_target else 0.0, 0.0, 0.0]       # :348-353
+        for i, lr in enumerate(lrs):
+            p.lr[i] = lr
+        return p
+
+    def forward_kinematics(self, tip_pose):
+        return tip_pose.view(-1, 3)
+
+    def optimize(self, tip_pose, target_pose, compliance, friction_mu, gpis, verbose=True):
+        """optimize_pregrasp.py:335-406 -> (opt_tip_pose [B,4,3], opt_compliance [B,4], opt_target_pose [B,4,3], flag)."""
+        B = tip_pose.shape[0]
+        otip, ok, oT, flag = super().optimize(tip_pose.reshape(B, 12), target_pose, compliance, friction_mu, gpis, verbose)
+        return otip.view(B, 4, 3), ok, oT, flag
+
+
+# optimize_pregrasp.py:842-848; "sdf" / "kin" (mesh SDF) and "wc" (cvxpy conic solve per step) are out of scope (DESIGN.md)
+optimizers = {"prob": ProbabilisticGraspOptimizer, "kingpis": KinGPISGraspOptimizer, "gpis": GPISGraspOptimizer}

@@ -95,6 +95,13 @@ int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, const int* dof,
  * palm_dev [B,6] f64 (xyz + XYZ Euler) -> tips_dev [B,4,3] f64 (FK evaluated in float32 like the reference). */
 int cdx_hand_fk(cdx_ctx* ctx, const double* q_dev, const double* palm_dev, int64_t B, double* tips_dev, void* stream);
 
+/* KinGPISGraspOptimizer.forward_kinematics (optimize_pregrasp.py:431-438): compute_forward_kinematics(recursive=True) on
+ * float64 angles (rigid_body.py:85-127: cos/sin in double, rounded into the float32 joint rotation; chain composed from the
+ * tip towards the root) + palm_dev[b, 0:3].  palm_dev [B,6] f64 with zero Euler angles (the reference adds a constant
+ * offset, no rotation).  -> tips_dev [B,4,3] f64. */
+int cdx_hand_fk_recursive(cdx_ctx* ctx, const double* q_dev, const double* palm_dev, int64_t B, double* tips_dev,
+                          void* stream);
+
 /* ProbabilisticGraspOptimizer.compute_collision_loss (optimize_pregrasp.py:684-701) on world-frame anchor positions
  * anchor_dev [B,A,3] (cdx_hand_fk of the anchor links): sum over pairs of 1/dist where dist < threshold, + 0.1/z for
  * anchors below z = 0.02, + 1/z of the palm below 0.02 when palm_dev [B,6] is given (optimize_palm).  left_dev /
@@ -120,7 +127,15 @@ typedef struct cdx_pregrasp_params {
   double lr[5];                  /* q, compliance, target, palm pos, palm ori (:782-796) */
   double beta1, beta2, eps;      /* torch.optim.Adam defaults 0.9, 0.999, 1e-8 (:796) */
   double compliance_min;         /* 80.0 (:833) */
-  int32_t track_after;           /* best-iterate tracking for s > 20 (:823) */
+  int32_t track_after;           /* best-iterate tracking for s > 20 (:823); -1 = every iteration (Kin optimizers, :490) */
+  int32_t variant;               /* 0: ProbabilisticGraspOptimizer (:614-839, Adam).  1: KinGPISGraspOptimizer (:408-511):
+                                  * one copy with coefficient 1, reward x5, centre cost x10, force clamp 1, ref cost x20,
+                                  * tar_dist x10, no contact-margin / pregrasp / palm terms, q used without the .float()
+                                  * cast (:436), torch.optim.RMSprop (alpha below, eps), whole-batch margin latched at the
+                                  * last improving iteration (:491-494).  2: GPISGraspOptimizer (:322-406): no hand - the
+                                  * "q" slot holds tip_pose [B,12]; reward x25, variance cost = uncertainty * sum_f std,
+                                  * no ref cost, tips clamped to the box (:400), target NOT clamped (:402), RMSprop */
+  double rms_alpha;              /* torch.optim.RMSprop default 0.99 */
 } cdx_pregrasp_params;
 
 /* ProbabilisticGraspOptimizer.optimize setup (optimize_pregrasp.py:771-804): copies the initial iterate, zeroes
@@ -139,6 +154,9 @@ int cdx_pregrasp_results(cdx_ctx* ctx, double* opt_q_dev, double* opt_compliance
 /* current iterate (for tests) */
 int cdx_pregrasp_state(cdx_ctx* ctx, double* q_dev, double* compliance_dev, double* target_dev, double* palm_dev,
                        void* stream);
+/* KinGPISGraspOptimizer's `opt_margin` (:493): the WHOLE batch's margin [B,4] at the last iteration in which any candidate
+ * improved, and that iteration's index (-1: never) in iter_dev[0] (int32).  flag = (opt_margin > 0).all() is the caller's. */
+int cdx_pregrasp_latched_margin(cdx_ctx* ctx, double* margin_dev, int* iter_dev, void* stream);
 /* local arg-min over opt_value with lowest-index tie-break: out_dev[0] = value, out_dev[1] = (double) GLOBAL index
  * (env_offset + local).  The cross-rank step is an all-gather of these 16 bytes. */
 int cdx_pregrasp_argmin(cdx_ctx* ctx, double* out_dev, void* stream);

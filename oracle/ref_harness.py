@@ -180,7 +180,7 @@ def ref_pred_chunked(g, X2, chunk=2048, with_grad=False):
 
 
 @contextlib.contextmanager
-def pinned_kabsch_noise(seed, num_envs_offset=0):
+def pinned_kabsch_noise(seed, num_envs_offset=0, num_copies=3):
     """Replace torch.rand_like by the keyed stream of oracle/noise.py for the duration of a reference
     run.  The reference calls rand_like exactly once per closure (optimize_pregrasp.py:61) on a
     [3B,3,3] tensor; call k of the context = optimizer iteration k."""
@@ -190,7 +190,7 @@ def pinned_kabsch_noise(seed, num_envs_offset=0):
 
     def fake(t, *a, **k):
         E = t.shape[0]
-        out = kabsch_noise(seed, counter["it"], E, num_envs_offset)
+        out = kabsch_noise(seed, counter["it"], E, num_envs_offset, num_copies)
         counter["it"] += 1
         return out.to(t.dtype)
 

@@ -15,14 +15,16 @@ MAXD = 6  # CDX_MAX_CHAIN_DOF
 
 class PgConst(ctypes.Structure):
     _fields_ = [("cos_mu", ctypes.c_double), ("com", ctypes.c_double * 3), ("dummy_k", ctypes.c_double),
-                ("dummy_M", ctypes.c_double), ("gravity", ctypes.c_int), ("uncertainty", ctypes.c_double)]
+                ("dummy_M", ctypes.c_double), ("gravity", ctypes.c_int), ("uncertainty", ctypes.c_double),
+                ("w_reward", ctypes.c_double), ("w_cm", ctypes.c_double), ("w_tar", ctypes.c_double),
+                ("force_clamp", ctypes.c_double), ("w_center", ctypes.c_double), ("var_sum", ctypes.c_int)]
 
 
 class PgSetup(ctypes.Structure):
     _fields_ = [("P", ctypes.c_int), ("U", ctypes.c_int), ("uniq", ctypes.c_int * 4),
                 ("coeff", (ctypes.c_double * 4) * 4), ("weight", ctypes.c_double * 4),
                 ("ref_q", ctypes.c_double * 16), ("n_dofs", ctypes.c_int), ("optimize_palm", ctypes.c_int),
-                ("C", PgConst)]
+                ("variant", ctypes.c_int), ("w_ref", ctypes.c_double), ("w_pre", ctypes.c_double), ("C", PgConst)]
 
 
 def build():
@@ -97,4 +99,7 @@ def make_setup(coeffs, weights, ref_q, n_dofs, optimize_palm, cos_mu, com, dummy
     s.C.dummy_M = 2.0
     s.C.gravity = int(gravity)
     s.C.uncertainty = float(uncertainty)
+    # ProbabilisticGraspOptimizer weights (optimize_pregrasp.py:719-737, :757-759)
+    s.variant, s.w_ref, s.w_pre = 0, 10.0, 5.0
+    s.C.w_reward, s.C.w_cm, s.C.w_tar, s.C.force_clamp, s.C.w_center, s.C.var_sum = 200.0, 200.0, 20.0, 10.0, 0.0, 0
     return s

@@ -129,3 +129,40 @@ def test_closure_value_and_gradients(tag, hand, state, perturb, golden_dir):
             err = np.nanmax(np.abs(got - want)) if not np.all(np.isnan(want)) else 0.0
             # the q gradient passes through the float32 FK graph: float32 rounding of O(1e4) values
             assert err <= (2e-5 if nm == "q" else 2e-6) * sc, (nm, b, err, sc)
+
+
+@pytest.mark.parametrize("tag,hand,state", [("kin_leap_mug", "leap", "mug"), ("kin_allegro_hammer", "allegro", "hammer")])
+def test_kin_variant_closure_against_reference_golden(tag, hand, state, golden_dir):
+    """the same per-candidate math with KinGPISGraspOptimizer's weights (optimize_pregrasp.py:468-489) against
+    the loss and leaf gradients the REFERENCE's autograd produced at the initial iterate (tests/golden/variant_*.npz)."""
+    g = np.load(os.path.join(golden_dir, f"variant_{tag}.npz"))
+    gp = GPISOracle(0.08, 1.0).load_npz(os.path.join(STATES, f"{state}_state.npz"))
+    host, doc = _host(hand)
+    mu, mass, com, seed = g["friction_mu"].item(), float(g["mass"]), g["com"].tolist(), int(g["noise_seed"])
+    q, T, k = g["q0"], g["target0"], g["compliance0"]
+    B = q.shape[0]
+    palm = np.zeros((B, 6))
+    palm[:, :3] = g["palm3"]
+    cos_mu = float(torch.sqrt(1 / (1 + torch.tensor(mu) ** 2)))
+    setup = hc.make_setup(((1.0,) * 4,), (1.0,), doc["ref_q"], 16, False, cos_mu, com, 10.0 * mass / 2.0, True, 10.0)
+    setup.variant, setup.w_ref, setup.w_pre = 1, 20.0, 0.0
+    setup.C.w_reward, setup.C.w_cm, setup.C.w_tar, setup.C.force_clamp, setup.C.w_center = 5.0, 0.0, 10.0, 1.0, 10.0
+    tips = g["tips0"].reshape(B, 4, 3)
+    tl = tips - g["palm3"]                                   # hand-frame tips of the reference's recursive FK
+    want_T = g["grad0_target"] if int(g["optimize_target"]) else None
+    for b in range(B):
+        X = torch.from_numpy(tips[b])
+        dist, sd = gp.pred_diag(X)
+        gmu, gsd = gp.grads(X)
+        X9 = torch.vstack([torch.from_numpy(T[b]), X, torch.zeros(1, 3, dtype=torch.float64)])
+        m9, _ = gp.pred_diag(X9)
+        g9, _ = gp.grads(X9)
+        tot, tm, gq, gk, gT, _ = host.closure(setup, q[b], k[b], T[b], palm[b], dist.numpy(), sd.numpy(), gmu.numpy(),
+                                              gsd.numpy(), m9.numpy(), g9.numpy(), seed, 0, b, tl=tl[b])
+        ref = g["losses"][0][b]
+        assert abs(tot - ref) <= 1e-8 * max(100.0, abs(ref)), (b, tot, ref)
+        assert np.abs(tm - g["margins"][0][b]).max() < 1e-6
+        for got, want, nm in [(gq, g["grad0_q"][b], "q"), (gk, g["grad0_compliance"][b], "k")] + \
+                ([(gT, want_T[b], "T")] if want_T is not None else []):
+            sc = max(1e-30, np.abs(g["grad0_" + {"q": "q", "k": "compliance", "T": "target"}[nm]]).max())
+            assert np.abs(got - want).max() <= (5e-5 if nm == "q" else 2e-6) * sc, (nm, b, np.abs(got - want).max(), sc)
