@@ -35,6 +35,8 @@ def parse():
     ap.add_argument("--iters", type=int, default=200)
     ap.add_argument("--hand", default="leap", choices=["leap", "allegro"])
     ap.add_argument("--object", default="mug", help="shipped GPIS state of the pregrasp workload (mug, hammer, lego, ...)")
+    ap.add_argument("--points", type=int, default=1_000_000, help="sdf workload: query points")
+    ap.add_argument("--subdiv", type=int, default=5, help="sdf workload: icosphere subdivisions (20 * 4^n faces)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--var-mode", type=int, default=0,
                     help="gpis_c3: 0 auto (tcgen05 INT8 slices), -1 FP64 tensor MMA, 4..6 INT8 with that many slices")
@@ -43,14 +45,46 @@ def parse():
 
 # ------------------------------------------------------------------------------------------ helpers
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock / throttle reasons sampled DURING the timed region: NVML in a thread every 5 ms (the pregrasp workload's
+    timed region is tens of milliseconds - an `nvidia-smi -lms` child process would not even have started), falling back to
+    an nvidia-smi loop when pynvml is unusable."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.nv, self.h = index, [], None, None, None
+        self.sm, self.mx, self.bits, self.stop_flag = [], None, 0, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode() if not uuid.startswith("GPU-") else uuid.encode())
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.nv = pynvml
+        except Exception:
+            self.nv = None
+
+    def _poll(self):
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def start(self):
+        if self.nv is not None:
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
@@ -64,6 +98,16 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
+        if self.nv is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            nv = self.nv
+            masks = [("hw_slowdown", getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8)),
+                     ("hw_thermal_slowdown", getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40)),
+                     ("sw_thermal_slowdown", getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20)),
+                     ("sw_power_cap", getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4))]
+            return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx,
+                    "reasons": [n for n, m in masks if self.bits & m], "samples": len(self.sm), "source": "nvml, 5 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -74,7 +118,7 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
 def measured_peaks():
@@ -327,6 +371,17 @@ def main():
                     "cpu_baseline": {"value": v, "unit": "queries/s", "cores": threads, "kind": "port",
                                      "sample": "2048 queries per step: one pred (LU) + one compute_normal (inverse)"},
                     "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        elif workload == "sdf":
+            from bench_sdf import METRIC, cpu_sdf
+            vals = [cpu_sdf(1000, args.subdiv, 1) for _ in range(args.warmup + args.steps)][args.warmup:]
+            v, ms = float(np.mean([a for a, _ in vals])), float(np.mean([b for _, b in vals])) * 1e3
+            line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+                    "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                    "dtype": "f32", "data": "synthetic",
+                    "config": {"workload": "sdf: 1000-point sample against the icosphere of %d faces; the reference has no CPU "
+                                           "implementation of this op, so this is the numpy port" % (20 * 4 ** args.subdiv)},
+                    "cpu_baseline": {"value": v, "unit": "queries/s", "cores": 1, "kind": "port", "sample": "1000 points per step"},
+                    "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         else:
             from bench_pregrasp import run_reference_c2
             line = run_reference_c2(args, threads, world)
@@ -342,6 +397,14 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "queries/s", "cores": threads, "kind": "port",
                                     "sample": "2048 of the queries: one pred (LU of the 4096^2 matrix + MxM covariance) + "
                                               "one compute_normal (explicit inverse), %.1f s" % dt}
+    elif workload == "sdf":
+        from bench_sdf import cpu_sdf, run_bench_sdf
+        line = run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks)
+        if rank == 0 and not args.no_cpu_baseline:
+            v, dt = cpu_sdf(1000, args.subdiv, 1)
+            line["cpu_baseline"] = {"value": v, "unit": "queries/s", "cores": 1, "kind": "port",
+                                    "sample": "1000 of the points against the same mesh through the numpy port of the reference "
+                                              "kernel (the reference has no CPU path for this op), %.1f s" % dt}
     else:
         from bench_pregrasp import run_bench_c2
         line = run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks, ncu_traffic)

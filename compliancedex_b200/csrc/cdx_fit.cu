@@ -302,6 +302,7 @@ extern "C" int cdx_destroy(cdx_ctx* ctx) {
   cudaFree(ctx->hx); cudaFree(ctx->hout);
   cdx_i8_free(ctx);
   cdx_pregrasp_free(ctx);
+  cdx_sdf_free(ctx);
   delete ctx;
   return CDX_OK;
 }

@@ -69,6 +69,7 @@ struct cdx_gpis_state {
 };
 
 struct cdx_pg_state;  // cdx_pregrasp.cu
+struct cdx_sdf_state; // cdx_sdf.cu
 
 struct cdx_ctx {
   int device = 0;
@@ -78,6 +79,7 @@ struct cdx_ctx {
   cdx_hand hand;
   bool hand_ready = false;
   cdx_pg_state* pg = nullptr;
+  cdx_sdf_state* sdf = nullptr;
   // scratch for host-pointer entry points
   double* hx = nullptr; double* hout = nullptr; int64_t hcap = 0;
 };
@@ -151,6 +153,7 @@ __device__ __forceinline__ void cdx_cp_async_wait() { asm volatile("cp.async.wai
 bool cdx_i8_eligible(const cdx_ctx* ctx);
 int cdx_i8_std(cdx_ctx* ctx, int S, const double* X, int64_t M, double* stdv, cudaStream_t st);
 void cdx_i8_free(cdx_ctx* ctx);
+void cdx_sdf_free(cdx_ctx* ctx);
 
 int cdx_dgemm(cdx_ctx* ctx, bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int64_t lda,
               const double* B, int64_t ldb, double beta, double* C, int64_t ldc, bool lower_only, int ktri, int batch,

@@ -74,3 +74,29 @@ def synthetic_candidates(hand_doc, B, center, seed=0):
     target = c.view(1, 1, 3).repeat(B, 4, 1)
     compliance = torch.tensor([[10.0, 10.0, 10.0, 20.0]], dtype=torch.float64).repeat(B, 1)
     return q, target, compliance, palm.numpy()
+
+
+def icosphere_faces(subdiv=3, radius=1.0, dtype=np.float32):
+    """Synthetic closed mesh for the compute_sdf workload: an icosahedron subdivided `subdiv` times, vertices pushed to the
+    sphere of `radius` -> face_vertices [20 * 4^subdiv, 3, 3] with outward-facing normals."""
+    t = (1.0 + 5.0 ** 0.5) / 2.0
+    verts = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t), (0, 1, -t), (t, 0, -1),
+             (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    verts = [np.asarray(v, dtype=np.float64) / np.linalg.norm(v) for v in verts]
+    faces = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4), (11, 10, 2), (10, 7, 6),
+             (7, 1, 8), (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9), (4, 9, 5), (2, 4, 11), (6, 2, 10), (8, 6, 7),
+             (9, 8, 1)]
+    for _ in range(subdiv):
+        midpoint, split = {}, []
+        for tri in faces:
+            m = []
+            for a, b in ((tri[0], tri[1]), (tri[1], tri[2]), (tri[2], tri[0])):
+                key = (a, b) if a < b else (b, a)
+                if key not in midpoint:
+                    v = verts[a] + verts[b]
+                    verts.append(v / np.linalg.norm(v))
+                    midpoint[key] = len(verts) - 1
+                m.append(midpoint[key])
+            split += [(tri[0], m[0], m[2]), (tri[1], m[1], m[0]), (tri[2], m[2], m[1]), (m[0], m[1], m[2])]
+        faces = split
+    return (np.asarray(verts)[np.asarray(faces)] * radius).astype(dtype)

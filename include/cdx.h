@@ -81,6 +81,19 @@ int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha_dev, const double* 
  * idx_dev (capacity steps^3) and their number to count_dev[0]. */
 int cdx_grid_surface(cdx_ctx* ctx, const float* mean_dev, int steps, long long* idx_dev, long long* count_dev, void* stream);
 
+/* ------------------------------------------------------------------ mesh distance (TorchSDF) ----------- */
+/* compute_sdf (thirdparty/TorchSDF/torchsdf/sdf.py:34-64; binding csrc/bindings.cpp:22-27 ->
+ * unbatched_triangle_distance_forward_cuda, kernel csrc/unbatched_triangle_distance_cuda.cu:176-254): points_dev [P,3],
+ * face_vertices_dev [F,3,3], both of `dtype` (0 = float32, 1 = float64) -> dist_dev [P] SQUARED distance to the closest
+ * triangle (rounded to float like the reference, :235), sign_dev [P] int32 (+1 on the side the face normal points to),
+ * normals_dev [P,3] unit vector closest point -> point, closest_dev [P,3].  First face wins ties (:236,:243).  Any output
+ * may be NULL.  F = 0 zero-fills the outputs (what the reference's pre-zeroed tensors keep). */
+int cdx_sdf_forward(cdx_ctx* ctx, const void* points_dev, int64_t P, const void* face_vertices_dev, int64_t F, int dtype,
+                    void* dist_dev, int32_t* sign_dev, void* normals_dev, void* closest_dev, void* stream);
+/* unbatched_triangle_distance_backward_cuda (:256-270): grad_points [P,3] = 2 grad_dist (points - closest) */
+int cdx_sdf_backward(cdx_ctx* ctx, const void* grad_dist_dev, const void* points_dev, const void* closest_dev, int64_t P,
+                     int dtype, void* grad_points_dev, void* stream);
+
 /* ------------------------------------------------------------------ hand model + pregrasp -------------- */
 /* Kinematic tree in URDF link order (robot_model.py:115-127, urdf_utils.py:28-83): body i has parent[i] < i
  * (-1 for the root), dof[i] = column of q driving it or -1 (fixed), axis[i] in {0,1,2} with axis_sign[i] = +-1
