@@ -113,20 +113,21 @@ CDX_HD float cdx_quat_raw(const float* R, int branch, float one, float* q) {
 //   every body applies its joint pose to the poses of its descendants, i.e. tip-to-root association
 //   J_0 (J_1 (... (J_{n-1} I)))); the Jacobian keeps using the root-to-tip prefix frames (same quantities up to float32
 //   rounding).
+template <bool REC = false>   // REC: q64 given (compile-time so that the non-recursive path keeps no per-joint rotation array)
 CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, float (*J)[CDX_MAX_CHAIN_DOF],
                           const double* q64 = nullptr) {
   float R[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
   float p[3] = {0.f, 0.f, 0.f};
   float om[CDX_MAX_CHAIN_DOF][3], org[CDX_MAX_CHAIN_DOF][3];
-  float jall[CDX_MAX_CHAIN][9];
+  float jall[REC ? CDX_MAX_CHAIN : 1][9];
   int nd = 0;
   for (int i = 0; i < ch.n; i++) {
-    float* jr = jall[i];
+    float* jr = jall[REC ? i : 0];
     const float* F = ch.fixed_rot[i];
     if (ch.dof[i] >= 0) {
       const float ang = CDX_FM(ch.sign[i], q32[ch.dof[i]]);
       float c, s;
-      if (q64) {
+      if (REC) {
         const double a64 = (double)ch.sign[i] * q64[ch.dof[i]];
         c = (float)cos(a64); s = (float)sin(a64);
       } else {
@@ -155,7 +156,7 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
       nd++;
     }
   }
-  if (q64) {   // recursive=True association (rigid_body.py:118-127)
+  if (REC) {   // recursive=True association (rigid_body.py:118-127)
     float Ra[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f}, pa[3] = {0.f, 0.f, 0.f};
     for (int i = ch.n - 1; i >= 0; i--) {
       const float* jr = jall[i];

@@ -54,6 +54,7 @@ struct pg_lr { double v[5]; };
 
 // FK of finger f for candidate b at joint angles q (float64, n_dofs entries), palm pose palm6, target Tf; writes the
 // per-iteration scratch (tl, J) and the GPIS query points of this finger (pregrasp blend :747-750, target, tip, palm).
+template <int V>   // V = optimizer variant (cdx_pregrasp_params.variant), compile-time so that the prob path carries no variant code
 __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ hand, const cdx_pg_setup& S, int U, int64_t b,
                                                int f, const double* q, const double* Tf, const double* palm6,
                                                double* __restrict__ tl, float* __restrict__ J, double* __restrict__ Xext,
@@ -61,7 +62,7 @@ __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ 
   const int64_t gid = b * 4 + f;
   double tlf[3], tw[3];
   float Jf[3][CDX_MAX_CHAIN_DOF];
-  if (S.variant == 2) {   // GPISGraspOptimizer: tip_pose itself is the parameter (:345,:361)
+  if (V == 2) {   // GPISGraspOptimizer: tip_pose itself is the parameter (:345,:361)
     for (int r = 0; r < 3; r++) { tlf[r] = q[f * 3 + r]; tw[r] = tlf[r]; }
     for (int r = 0; r < 3; r++)
       for (int c = 0; c < CDX_MAX_CHAIN_DOF; c++) Jf[r][c] = 0.f;
@@ -70,7 +71,7 @@ __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ 
 #pragma unroll
     for (int i = 0; i < 16; i++) q32[i] = i < S.n_dofs ? (float)q[i] : 0.f;                  // q.float(), :665
     // Kin variant: q stays float64 and the chain is composed recursively (:436, robot_model.py:243-251)
-    cdx_fk_finger(hand->finger[f], q32, tip, Jf, S.variant == 1 ? q : nullptr);
+    cdx_fk_finger<V == 1>(hand->finger[f], q32, tip, Jf, V == 1 ? q : nullptr);
     for (int r = 0; r < 3; r++) tlf[r] = (double)tip[r];                                     // .double(), :666
     double Rw[9];
     cdx_euler_xyz(palm6 + 3, Rw, nullptr, nullptr, nullptr);
@@ -91,7 +92,7 @@ __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ 
     if (u < seen) continue;   // this coefficient row already has its query block
     seen = u + 1;
     double* x = Xext + ((b * U + u) * 4 + f) * 3;
-    for (int r = 0; r < 3; r++) x[r] = S.variant ? tw[r] : Tf[r] + S.coeff[p][f] * (tw[r] - Tf[r]);   // :750 / tips (:462)
+    for (int r = 0; r < 3; r++) x[r] = V ? tw[r] : Tf[r] + S.coeff[p][f] * (tw[r] - Tf[r]);   // :750 / tips (:462)
   }
   double* xm = Xmean + b * 27;
   for (int r = 0; r < 3; r++) {
@@ -101,6 +102,7 @@ __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ 
   }
 }
 
+template <int V>
 __global__ void __launch_bounds__(128)
 pg_points_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_setup S, const double* __restrict__ q,
                  const double* __restrict__ T, const double* __restrict__ palm, double* __restrict__ tl,
@@ -109,7 +111,7 @@ pg_points_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= B * 4) return;
   const int64_t b = gid >> 2;
-  pg_emit_points(hand, S, U, b, (int)(gid & 3), q + b * S.n_dofs, T ? T + gid * 3 : nullptr, palm + b * 6, tl, J, Xext,
+  pg_emit_points<V>(hand, S, U, b, (int)(gid & 3), q + b * S.n_dofs, T ? T + gid * 3 : nullptr, palm + b * 6, tl, J, Xext,
                  Xmean, tips_out);
 }
 
@@ -131,6 +133,7 @@ constexpr int NRED = 33;    // total | margin 4 | gk 4 | gtips 12 | gT 12
 //   lane f then owns finger f: chain rule through the palm transform and the float32 FK Jacobian, its share of the
 //   38 parameters in best-iterate tracking (:822-829), Adam (:831) and the clamps (:833-834), and - when stepping - the FK
 //   and query points of the NEW iterate, so the next iteration needs no separate points launch.
+template <int V>
 __global__ void __launch_bounds__(CPB * 4)
 pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_setup S, cdx_pregrasp_params prm,
                double* __restrict__ q, double* __restrict__ k, double* __restrict__ T, double* __restrict__ palm,
@@ -164,7 +167,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   for (int f = 0; f < 4; f++) {
     cdx_mv(Rw, tlp[f], tips[f]);
     for (int r = 0; r < 3; r++) tips[f][r] += par[32 + r];
-    if (S.variant == 2)
+    if (V == 2)
       for (int r = 0; r < 3; r++) tips[f][r] = par[f * 3 + r];
   }
   double refn = 0.0;
@@ -175,7 +178,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     refn = sqrt(refn);
   }
   // Kin / GPIS variants: the margin of the previous iteration becomes the latched opt_margin if anything improved then
-  if (S.variant != 0 && do_step && it > 0 && latch[(it - 1) & 1] == it - 1) {
+  if (V != 0 && do_step && it > 0 && latch[(it - 1) & 1] == it - 1) {
     latched[b * 4 + l] = mring[((it - 1) & 1) * B * 4 + b * 4 + l];
     if (b == 0 && l == 0) latch[2] = it - 1;
   }
@@ -192,7 +195,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     double a[4][3], noise[9], lossp, mg[4], ga[4][3], gTr[4][3], gkr[4];
 #pragma unroll
     for (int f = 0; f < 4; f++)
-      for (int r = 0; r < 3; r++) a[f][r] = S.variant ? tips[f][r] : Tp[f][r] + S.coeff[p][f] * (tips[f][r] - Tp[f][r]);
+      for (int r = 0; r < 3; r++) a[f][r] = V ? tips[f][r] : Tp[f][r] + S.coeff[p][f] * (tips[f][r] - Tp[f][r]);
     const int64_t gb = prm.env_offset + b;
 #pragma unroll
     for (int e = 0; e < 9; e++) noise[e] = cdx_kabsch_noise(prm.noise_seed, it, p, gb, e);
@@ -247,7 +250,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   }
   // back through .double() (:666) into the float32 FK graph; fingers take turns so shared joints would accumulate
   const float g32[3] = {(float)gl[0], (float)gl[1], (float)gl[2]};
-  if (S.variant == 2) {
+  if (V == 2) {
     for (int r = 0; r < 3; r++) sg[cl][f * 3 + r] = gt[r];       // tip_pose is the leaf
     __syncwarp(gmask);
   } else {
@@ -287,7 +290,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   // ---- best-iterate tracking (:822-829): BEFORE the optimiser step, only for s > track_after; NaN never updates
   const bool better = it > prm.track_after && total < ovalue[b];
   __syncwarp(gmask);                                    // every lane has read ovalue[b] before lane 0 overwrites it
-  if (S.variant != 0) {
+  if (V != 0) {
     mring[(it & 1) * B * 4 + b * 4 + l] = sr[cl][1 + l];
     if (better && l == 0) latch[it & 1] = it;          // benign race: every writer stores the same value
   }
@@ -316,7 +319,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     else if (i < 32) { upd = prm.optimize_target != 0; grp = 2; }
     else { upd = prm.optimize_palm != 0; grp = i < 35 ? 3 : 4; }
     double pv = par[i];
-    if (upd && S.variant == 0) {
+    if (upd && V == 0) {
       const double gi = g[i];
       double m = m1[b * NPAR + i], v = m2[b * NPAR + i];
       m = m + omb1 * (gi - m);
@@ -335,10 +338,10 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
       m2[b * NPAR + i] = v;
       pv = pv + (-prm.lr[grp] * gi) / (sqrt(v) + prm.eps);   // addcdiv_(g, avg, value=-lr): (value * g) / avg
     }
-    if (S.variant == 2 && i < 12)   // tip_pose.clamp_(box) (:402)
+    if (V == 2 && i < 12)   // tip_pose.clamp_(box) (:402)
       pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[i / 3][i % 3]), (double)prm.box_hi[i / 3][i % 3]);
     if (i >= 16 && i < 20) pv = clamp_lo(pv, prm.compliance_min);
-    if (i >= 20 && i < 32 && S.variant != 2) {   // target clamp: prob (:834) and Kin (:505); commented out at :404
+    if (i >= 20 && i < 32 && V != 2) {   // target clamp: prob (:834) and Kin (:505); commented out at :404
       const int e = i - 20;
       pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[e / 3][e % 3]), (double)prm.box_hi[e / 3][e % 3]);
     }
@@ -350,7 +353,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   }
   __syncwarp(gmask);
   // ---- FK + GPIS query points of the NEW iterate (what pg_points_kernel does for the first iteration)
-  pg_emit_points(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
+  pg_emit_points<V>(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
 }
 
 // ProbabilisticGraspOptimizer.compute_collision_loss (optimize_pregrasp.py:684-701) on anchor poses [B,A,3]: thread per
@@ -494,8 +497,8 @@ extern "C" int cdx_hand_fk(cdx_ctx* ctx, const double* q, const double* palm, in
   cdx_pg_setup S;
   memset(&S, 0, sizeof(S));
   S.n_dofs = s->hand_n_dofs;
-  pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(s->hand_dev, B, 1, S, q, nullptr, palm, nullptr,
-                                                                              nullptr, nullptr, nullptr, tips);
+  pg_points_kernel<0><<<(unsigned)((B * 4 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(s->hand_dev, B, 1, S, q, nullptr, palm, nullptr,
+                                                                                 nullptr, nullptr, nullptr, tips);
   CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
 }
@@ -513,8 +516,8 @@ extern "C" int cdx_hand_fk_recursive(cdx_ctx* ctx, const double* q, const double
   memset(&S, 0, sizeof(S));
   S.n_dofs = s->hand_n_dofs;
   S.variant = 1;
-  pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(s->hand_dev, B, 1, S, q, nullptr, palm_offset3,
-                                                                              nullptr, nullptr, nullptr, nullptr, tips);
+  pg_points_kernel<1><<<(unsigned)((B * 4 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(s->hand_dev, B, 1, S, q, nullptr, palm_offset3,
+                                                                                 nullptr, nullptr, nullptr, nullptr, tips);
   CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
 }
@@ -649,8 +652,10 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
     s->prof_ev.push_back(e);
   };
   if (!s->points_valid) {
-    pg_points_kernel<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(s->hand_dev, B, U, s->setup, s->q, s->T, s->palm, s->tl,
-                                                                    s->J, s->Xext, s->Xmean, nullptr);
+#define PG_POINTS(V) pg_points_kernel<V><<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(s->hand_dev, B, U, s->setup, s->q, s->T, \
+                                                                                        s->palm, s->tl, s->J, s->Xext, s->Xmean, nullptr)
+    if (s->setup.variant == 0) PG_POINTS(0); else if (s->setup.variant == 1) PG_POINTS(1); else PG_POINTS(2);
+#undef PG_POINTS
     CDX_CHECK_LAUNCH(ctx);
     s->points_valid = true;
   }
@@ -667,10 +672,12 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   CDX_CUDA(cudaEventRecord(s->ev_join, s->side));
   CDX_CUDA(cudaStreamWaitEvent(st, s->ev_join, 0));
   mark(st);
-  pg_step_kernel<<<(unsigned)((B + CPB - 1) / CPB), CPB * 4, 0, st>>>(
-      s->hand_dev, B, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd, s->mean9,
-      s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,
-      s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch);
+#define PG_STEP(V) pg_step_kernel<V><<<(unsigned)((B + CPB - 1) / CPB), CPB * 4, 0, st>>>(                                      \
+      s->hand_dev, B, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd, s->mean9,   \
+      s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,            \
+      s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch)
+  if (s->setup.variant == 0) PG_STEP(0); else if (s->setup.variant == 1) PG_STEP(1); else PG_STEP(2);
+#undef PG_STEP
   CDX_CHECK_LAUNCH(ctx);
   mark(st);
   return CDX_OK;

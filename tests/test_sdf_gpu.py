@@ -82,6 +82,12 @@ def test_against_reference_kernel_live(dtype):
         (got[0] * gd).sum().backward()
         ref_g = ref_torchsdf.backward(gd, p, got[3].detach())
         assert torch.equal(pr.grad, ref_g)                                   # same closest points in -> bit-identical gradient
+        # measured on B200: every output agrees bit for bit with the reference's kernel
+        assert torch.equal(got[0].detach(), want[0]) and torch.equal(got[1], want[1]) and torch.equal(got[3], want[3])
+        assert torch.equal(got[2], want[2])
+    # the reference's binding rejects the mixed dtypes its SDF / Kin optimizers would pass (optimize_pregrasp.py:165,186-188)
+    with pytest.raises(RuntimeError):
+        ref_torchsdf.compute_sdf(p.double(), f.float())
 
 
 def test_api_contract():
