@@ -4,7 +4,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcdx.so")
+LIB_PATH = os.environ.get("CDX_LIB") or os.path.join(_HERE, "libcdx.so")   # CDX_LIB: developer override (kernel experiments)
 
 c_void_p, c_int, c_i64, c_double, c_u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double, ctypes.c_uint64
 

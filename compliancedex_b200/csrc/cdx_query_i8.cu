@@ -33,19 +33,35 @@ constexpr int I8_GEN_WARPS = 16, I8_WARP_MMA = 16, I8_WARP_LOAD = 17, I8_WARP_EP
 constexpr int I8_THREADS = 22 * 32;
 constexpr double I8_MAGIC = 6755399441055744.0;  // 1.5 * 2^52: adding it leaves rint(x) in the low mantissa bits
 
+#ifndef CDX_I8_BK5
+#define CDX_I8_BK5 64      // training points per stage for S <= 5
+#endif
+#ifndef CDX_I8_NSA
+#define CDX_I8_NSA 2       // A stages in tensor memory
+#endif
+#ifndef CDX_I8_LATE_ARRIVE
+#define CDX_I8_LATE_ARRIVE 0   // 1: a stage's tcgen05.st are completed (wait::st + arrive) after the NEXT stage has been generated
+#endif
+#ifndef CDX_I8_EXP
+#define CDX_I8_EXP 0   // timing experiments only (results are wrong): 1 = no tcgen05.mma issued, 2 = no k* arithmetic in the generators,
+                       // 3 = no MMA and no tcgen05.st, 4 = no MMA, generators do not wait for / read the TMA-staged points
+#endif
+#ifndef CDX_I8_NSB
+#define CDX_I8_NSB 6       // shared-memory stages of (U slices, points)
+#endif
 template <int S> struct i8cfg {
-  static constexpr int BK = S >= 6 ? 32 : 64;          // training points per stage (TMEM budget: S*64 + 2*S*BK/4 <= 512 columns)
+  static constexpr int BK = S >= 6 ? 32 : CDX_I8_BK5;  // training points per stage (TMEM budget: S*64 + NSA*S*BK/4 <= 512 columns)
   static constexpr int KG = BK / 16;                   // 16-byte k groups per stage
   static constexpr int GSPLIT = 4 / KG;                // generator warps are split over this many consecutive stages
   static constexpr int ACOLS = S * BK / 4;             // TMEM columns of one A stage (4 int8 per 32-bit column)
-  static constexpr int NSA = 2;                        // A stages in TMEM
+  static constexpr int NSA = S >= 6 ? 2 : CDX_I8_NSA;  // A stages in TMEM
   static constexpr int ACC_COLS = S * I8_TN, A_BASE = ACC_COLS;
   static constexpr int TMEM_COLS = 512;
   static constexpr int B_SLICE = I8_TN * BK;           // bytes of one slice of one U tile
   static constexpr int B_BYTES = S * B_SLICE;
   static constexpr int P_BYTES = BK * 32;              // the stage's training points (-2x,-2y,-2z,|x|^2)
   static constexpr int SLOT = B_BYTES + P_BYTES;
-  static constexpr int NSB = 6;                        // smem stages of (U slices, points)
+  static constexpr int NSB = CDX_I8_NSB;               // smem stages of (U slices, points)
   static constexpr size_t SMEM = (size_t)NSB * SLOT + 256;
   static_assert(ACC_COLS + NSA * ACOLS <= 512, "TMEM budget");
 };
@@ -266,13 +282,16 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
     const double c2 = 2.0 * sc, c3 = -3.0 * R * sc, c0m = R3 * sc + I8_MAGIC;
     const unsigned trow = tmem + ((unsigned)((warp & 3) * 32) << 16) + C::A_BASE + kg * 4;
     int g = 0;
+#if CDX_I8_LATE_ARRIVE
+    int pending = -1;
+#endif
     for (int nt = 0; nt < NT; nt++) {
       const int nch = (nt + 1) * CPT;
       for (int c = 0; c < nch; c++, g++) {
         if (C::GSPLIT > 1 && (g % C::GSPLIT) != sub) continue;
         const int sa = g % NSA, sbk = g % NSB;
-        mb_wait(b_full + 8 * sbk, (unsigned)(g / NSB) & 1u);     // the stage's training points arrive with the U slices
-        const double2* P2 = reinterpret_cast<const double2*>(smem + (size_t)sbk * C::SLOT + C::B_BYTES) + kg * 32;
+        if (CDX_I8_EXP != 4) mb_wait(b_full + 8 * sbk, (unsigned)(g / NSB) & 1u);     // the stage's training points arrive with the U slices
+        const double2* P2 = reinterpret_cast<const double2*>(smem + (size_t)(CDX_I8_EXP == 4 ? 0 : sbk) * C::SLOT + C::B_BYTES) + kg * 32;
         unsigned ow[S][4];
 #pragma unroll
         for (int gq = 0; gq < 4; gq++) {
@@ -281,6 +300,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
           for (int p = 0; p < 4; p++) {
             const int j = gq * 4 + p;
             const double2 a = P2[2 * j], b = P2[2 * j + 1];
+            if (CDX_I8_EXP == 2) { L[p] = (unsigned)__double2loint(a.x); H[p] = (unsigned)__double2hiint(b.y); continue; }
             const double s = fma(xq, a.x, fma(yq, a.y, fma(zq, b.x, b.y + qq)));
             const unsigned shi = (unsigned)__double2hiint(s), slo = (unsigned)__double2loint(s);
             const unsigned fb = __funnelshift_l(slo, shi - 0x38000000u, 3);     // float(s) by bit moves (no F2F)
@@ -305,18 +325,46 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
 #pragma unroll
           for (int i = 0; i < S; i++) ow[i][gq] = by[S - 1 - i];
         }
+#if CDX_I8_LATE_ARRIVE
+        // the stores of the previous owned stage have had this stage's whole generation to land: complete them now
+        if (pending >= 0) {
+          tc_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mb_arrive(a_full + 8 * pending);
+        }
+#endif
         // the TMEM stage is free once the MMAs of stage g - NSA have completed (the values above did not need it)
         if (lane == 0) mb_wait(a_empty + 8 * sa, ((unsigned)(g / NSA) & 1u) ^ 1u);
         __syncwarp();
         tc_fence_after();
+        if (CDX_I8_EXP == 3) {   // timing experiment: no tensor-memory stores (keep the values alive)
+          unsigned x = 0;
 #pragma unroll
-        for (int i = 0; i < S; i++) tc_st4(trow + sa * C::ACOLS + i * (BK / 4), ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
+          for (int i = 0; i < S; i++) x ^= ow[i][0] ^ ow[i][1] ^ ow[i][2] ^ ow[i][3];
+          if (x == 0x12345677u) stdv[0] = 0.0;
+        } else {
+#pragma unroll
+          for (int i = 0; i < S; i++) tc_st4(trow + sa * C::ACOLS + i * (BK / 4), ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
+        }
+#if CDX_I8_LATE_ARRIVE
+        pending = sa;
+#else
         tc_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mb_arrive(a_full + 8 * sa);
+#endif
       }
     }
+#if CDX_I8_LATE_ARRIVE
+    if (pending >= 0) {
+      tc_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mb_arrive(a_full + 8 * pending);
+    }
+#endif
   } else if (warp == I8_WARP_LOAD) {
     // ===================================================== U slices + points: two bulk copies per stage
     if (lane == 0) {
@@ -357,7 +405,8 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
 #pragma unroll
               for (int ks = 0; ks < BK / 32; ks++) {
                 const uint64_t db = tc_desc(bbase + (d - i) * C::B_SLICE + ks * (2 * I8_TN * 16), I8_TN * 16, 128);
-                tc_mma_i8_ts(tmem + d * I8_TN, abase + i * (BK / 4) + ks * 8, db, idesc, (c > 0 || ks > 0 || i > 0) ? 1u : 0u);
+                if (CDX_I8_EXP == 0 || CDX_I8_EXP == 2)
+                  tc_mma_i8_ts(tmem + d * I8_TN, abase + i * (BK / 4) + ks * 8, db, idesc, (c > 0 || ks > 0 || i > 0) ? 1u : 0u);
               }
           tc_commit(a_empty + 8 * sa);
           tc_commit(b_empty + 8 * sbk);
