@@ -44,7 +44,7 @@ constexpr double I8_MAGIC = 6755399441055744.0;  // 1.5 * 2^52: adding it leaves
 #endif
 #ifndef CDX_I8_EXP
 #define CDX_I8_EXP 0   // timing experiments only (results are wrong): 1 = no tcgen05.mma issued, 2 = no k* arithmetic in the generators,
-                       // 3 = no MMA and no tcgen05.st, 4 = no MMA, generators do not wait for / read the TMA-staged points
+                       // 3 = no MMA and no tcgen05.st, 5 = generator loop only (no synchronisation at all, other warps idle), 4 = no MMA, generators do not wait for / read the TMA-staged points
 #endif
 #ifndef CDX_I8_NSB
 #define CDX_I8_NSB 6       // shared-memory stages of (U slices, points)
@@ -290,7 +290,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
       for (int c = 0; c < nch; c++, g++) {
         if (C::GSPLIT > 1 && (g % C::GSPLIT) != sub) continue;
         const int sa = g % NSA, sbk = g % NSB;
-        if (CDX_I8_EXP != 4) mb_wait(b_full + 8 * sbk, (unsigned)(g / NSB) & 1u);     // the stage's training points arrive with the U slices
+        if (CDX_I8_EXP != 4 && CDX_I8_EXP != 5) mb_wait(b_full + 8 * sbk, (unsigned)(g / NSB) & 1u);     // the stage's training points arrive with the U slices
         const double2* P2 = reinterpret_cast<const double2*>(smem + (size_t)(CDX_I8_EXP == 4 ? 0 : sbk) * C::SLOT + C::B_BYTES) + kg * 32;
         unsigned ow[S][4];
 #pragma unroll
@@ -335,10 +335,12 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
         }
 #endif
         // the TMEM stage is free once the MMAs of stage g - NSA have completed (the values above did not need it)
-        if (lane == 0) mb_wait(a_empty + 8 * sa, ((unsigned)(g / NSA) & 1u) ^ 1u);
-        __syncwarp();
-        tc_fence_after();
-        if (CDX_I8_EXP == 3) {   // timing experiment: no tensor-memory stores (keep the values alive)
+        if (CDX_I8_EXP != 5) {
+          if (lane == 0) mb_wait(a_empty + 8 * sa, ((unsigned)(g / NSA) & 1u) ^ 1u);
+          __syncwarp();
+          tc_fence_after();
+        }
+        if (CDX_I8_EXP == 3 || CDX_I8_EXP == 5) {   // timing experiment: no tensor-memory stores (keep the values alive)
           unsigned x = 0;
 #pragma unroll
           for (int i = 0; i < S; i++) x ^= ow[i][0] ^ ow[i][1] ^ ow[i][2] ^ ow[i][3];
@@ -350,10 +352,12 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
 #if CDX_I8_LATE_ARRIVE
         pending = sa;
 #else
-        tc_wait_st();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mb_arrive(a_full + 8 * sa);
+        if (CDX_I8_EXP != 5) {
+          tc_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mb_arrive(a_full + 8 * sa);
+        }
 #endif
       }
     }
@@ -367,7 +371,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
 #endif
   } else if (warp == I8_WARP_LOAD) {
     // ===================================================== U slices + points: two bulk copies per stage
-    if (lane == 0) {
+    if (lane == 0 && CDX_I8_EXP != 5) {
       int g = 0;
       for (int nt = 0; nt < NT; nt++) {
         const int nch = (nt + 1) * CPT;
@@ -386,7 +390,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
     // INT32 accumulate (c_format 2 @4), A unsigned 8-bit (0 @7), B signed 8-bit (1 @10), K-major both, N>>3 @17, M>>4 @24
     constexpr unsigned idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((unsigned)(I8_TN >> 3) << 17) | ((unsigned)(I8_TQ >> 4) << 24);
     int g = 0;
-    for (int nt = 0; nt < NT; nt++) {
+    for (int nt = 0; nt < (CDX_I8_EXP == 5 ? 0 : NT); nt++) {
       mb_wait(acc_empty, ((unsigned)nt & 1u) ^ 1u);
       tc_fence_after();
       const int nch = (nt + 1) * CPT;
@@ -423,7 +427,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
     const double xq = ok ? Xq[q * 3] : 0.0, yq = ok ? Xq[q * 3 + 1] : 0.0, zq = ok ? Xq[q * 3 + 2] : 0.0;
     const double sc = i8_query_scale<S>(xq, yq, zq, bb, R, R3);
     double ss = 0.0;
-    for (int nt = 0; nt < NT; nt++) {
+    for (int nt = 0; nt < (CDX_I8_EXP == 5 ? 0 : NT); nt++) {
       mb_wait_relaxed(acc_full, (unsigned)nt & 1u);
       tc_fence_after();
       const unsigned trow = tmem + ((unsigned)(lq * 32) << 16);
