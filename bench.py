@@ -163,12 +163,24 @@ def dist_setup(args):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"          # NCCL prints its version banner to STDOUT; keep stdout = one JSON line
         backend = "nccl" if args.impl == "cdx" else "gloo"
         if args.impl == "cdx":
             torch.cuda.set_device(local)
-        dist.init_process_group(backend=backend, device_id=torch.device("cuda", local) if backend == "nccl" else None)
+        # NCCL prints its version banner to STDOUT when the first communicator is created: send fd 1 to stderr while the process
+        # group comes up (init + one warm-up collective), so that stdout carries exactly one JSON line
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group(backend=backend, device_id=torch.device("cuda", local) if backend == "nccl" else None)
+            if backend == "nccl":
+                t = torch.zeros(1, device="cuda")
+                dist.all_reduce(t)
+                torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     return rank, world, local
 
 
@@ -399,7 +411,7 @@ def main():
                                               "one compute_normal (explicit inverse), %.1f s" % dt}
     elif workload == "sdf":
         from bench_sdf import cpu_sdf, run_bench_sdf
-        line = run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks)
+        line = run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, ncu_traffic)
         if rank == 0 and not args.no_cpu_baseline:
             v, dt = cpu_sdf(1000, args.subdiv, 1)
             line["cpu_baseline"] = {"value": v, "unit": "queries/s", "cores": 1, "kind": "port",

@@ -25,7 +25,7 @@ def _inputs(P_total, subdiv, rank, world):
     return p, torch.from_numpy(fv)
 
 
-def run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks):
+def run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, ncu_traffic=lambda *a: None):
     from compliancedex_b200 import _lib
     from compliancedex_b200.sdf import compute_sdf
     dev = torch.device("cuda", local)
@@ -117,7 +117,8 @@ def run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_rank
         "roofline": {"bound": "fp32", "kernel": "sdf_pair_kernel<float> (FP32 FMA pipe; bulk-TMA staged face records)",
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                      "peak_source": "FFMA rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json has no FP32 figure)",
-                     "flop_per_pair": FLOP_PER_PAIR, "pairs_per_launch": pairs, "pairs_per_s": pairs / (ms * 1e-3), "traffic": None},
+                     "flop_per_pair": FLOP_PER_PAIR, "pairs_per_launch": pairs, "pairs_per_s": pairs / (ms * 1e-3),
+                     "traffic": ncu_traffic("r01_ncu_sdf_summary.json", "r01_prof_sdf_v2") if (P_total, subdiv, world) == (1_000_000, 5, 1) else None},
         "reference_kernel": ref,
     }
 
