@@ -644,12 +644,11 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   const int64_t B = s->B;
   const int U = s->U;
   const bool prof = s->prof && do_step;
-  auto mark = [&](cudaStream_t on) {
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  auto mark = [&](int slot, cudaStream_t on) {
     if (!prof) return;
-    cudaEvent_t e;
-    cudaEventCreate(&e);
-    cudaEventRecord(e, on);
-    s->prof_ev.push_back(e);
+    cudaEventCreate(&ev[slot]);
+    cudaEventRecord(ev[slot], on);
   };
   if (!s->points_valid) {
 #define PG_POINTS(V) pg_points_kernel<V><<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(s->hand_dev, B, U, s->setup, s->q, s->T, \
@@ -661,17 +660,19 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   }
   CDX_CUDA(cudaEventRecord(s->ev_fork, st));
   CDX_CUDA(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
-  mark(st);
-  int rc = cdx_gpis_query(ctx, s->Xext, B * U * 4, s->dist, s->gmu, s->sd, s->gsd, (void*)st);
+  // the short mean-only query is launched FIRST (forked stream): its CTAs take their SMs for ~10 us and are gone long before
+  // the extended query ends, instead of queueing behind the extended query's CTAs and finishing after it
+  mark(2, s->side);
+  int rc = cdx_gpis_query(ctx, s->Xmean, B * 9, s->mean9, s->gmean9, nullptr, nullptr, (void*)s->side);
   if (rc) return rc;
-  mark(st);
-  mark(s->side);
-  rc = cdx_gpis_query(ctx, s->Xmean, B * 9, s->mean9, s->gmean9, nullptr, nullptr, (void*)s->side);
-  if (rc) return rc;
-  mark(s->side);
+  mark(3, s->side);
   CDX_CUDA(cudaEventRecord(s->ev_join, s->side));
+  mark(0, st);
+  rc = cdx_gpis_query(ctx, s->Xext, B * U * 4, s->dist, s->gmu, s->sd, s->gsd, (void*)st);
+  if (rc) return rc;
+  mark(1, st);
   CDX_CUDA(cudaStreamWaitEvent(st, s->ev_join, 0));
-  mark(st);
+  mark(4, st);
 #define PG_STEP(V) pg_step_kernel<V><<<(unsigned)((B + CPB - 1) / CPB), CPB * 4, 0, st>>>(                                      \
       s->hand_dev, B, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd, s->mean9,   \
       s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,            \
@@ -679,7 +680,9 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   if (s->setup.variant == 0) PG_STEP(0); else if (s->setup.variant == 1) PG_STEP(1); else PG_STEP(2);
 #undef PG_STEP
   CDX_CHECK_LAUNCH(ctx);
-  mark(st);
+  mark(5, st);
+  if (prof)
+    for (int i = 0; i < 6; i++) s->prof_ev.push_back(ev[i]);
   return CDX_OK;
 }
 
