@@ -26,3 +26,4 @@ def hand_path(hand):
 from .hand import load_hand
 from .pregrasp import (ProbabilisticGraspOptimizer, KinGPISGraspOptimizer, GPISGraspOptimizer, optimizers, EE_OFFSETS, WRIST_OFFSET, FINGERTIP_LB,
                        FINGERTIP_UB)
+from .completion import assemble_training_set, exterior_points, fit_completion

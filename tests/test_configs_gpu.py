@@ -118,3 +118,34 @@ def test_c5_shape_sharding_across_tile_variants():
     assert finite.float().mean() > 0.5                       # tracking started (s > 20) for most candidates
     i = int(torch.argmin(torch.where(finite, v_full, torch.full_like(v_full, float("inf")))))
     assert best_full[1] == i and best_full[0] == float(v_full[i])
+
+
+def test_fit_completion_script_shape(golden_dir):
+    """train_gpis_completion.py:20-62 through the drop-in: assemble (reference-golden inputs) -> fit -> E11 / y1 / R as the
+    reference's fit defines them (gpis.py:33-40), state round trip, grid + surface extraction run."""
+    import tempfile
+    from compliancedex_b200 import GPIS
+    from compliancedex_b200.completion import fit_completion
+    from oracle.gpis_oracle import GPISOracle
+    g = np.load(os.path.join(golden_dir, "completion_coffeebottle.npz"))
+    gp = fit_completion(g["default_observed"], g["default_completed"], bias=1.0, weights=g["default_draws"])
+    o = GPISOracle(0.08, 1.0)
+    o.fit(torch.from_numpy(g["default_X1"]), torch.from_numpy(g["default_y1"]), torch.from_numpy(g["default_noise"]))
+    assert np.abs(gp.E11.cpu().numpy() - o.E11.numpy()).max() <= 1e-15 and float(gp.R) == float(o.R)
+    assert np.array_equal(gp.y1.cpu().numpy(), o.y1.numpy())
+    X = (torch.rand(200, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(2)) - 0.5) * 0.2
+    m, s = gp.pred(X.cuda())
+    mo, so = o.pred(X)
+    assert (m.cpu() - mo).abs().max() <= 1e-5 * mo.abs().max() and (s.cpu() ** 2 - so ** 2).abs().max() <= 1e-6 * float(o.R) ** 3
+    with tempfile.TemporaryDirectory() as d:          # the reference hard-codes the relative directory gpis_states/ (gpis.py:160,163)
+        cwd = os.getcwd()
+        os.makedirs(os.path.join(d, "gpis_states"))
+        os.chdir(d)
+        try:
+            gp.save_state_data("cb_state")
+            g2 = GPIS(0.08, 1.0)
+            g2.load_state_data("cb_state")
+        finally:
+            os.chdir(cwd)
+        m2, _ = g2.pred(X.cuda())
+        assert (m2 - m).abs().max() <= 1e-9

@@ -107,3 +107,22 @@ def test_hand_tree_flattening():
     assert (leap.sign[1:] == -1).all() and (leap.axis[1:] == 2).all()      # all Leap axes are 0 0 -1
     with pytest.raises(ValueError):
         tree_for(load_hand("leap"), ["fingertip"], [[0, 0, 0]])
+
+
+@pytest.mark.parametrize("tag", ["default", "box018"])
+def test_completion_assembly_matches_reference_script(tag, golden_dir):
+    """assemble_training_set vs the reference script's own statements (train_gpis_completion.py:24-58 executed
+    verbatim by oracle/make_golden_completion.py) - bit for bit."""
+    from compliancedex_b200.completion import assemble_training_set, exterior_points
+    g = np.load(os.path.join(golden_dir, "completion_coffeebottle.npz"))
+    num_obs, num_gen, obs_noise, gen_noise, num_internals, boundary, bias = g[f"{tag}_args"]
+    X1, y1, noise = assemble_training_set(g[f"{tag}_observed"], g[f"{tag}_completed"], int(num_obs), int(num_gen), float(obs_noise),
+                                          float(gen_noise), int(num_internals), float(boundary), weights=g[f"{tag}_draws"])
+    assert np.array_equal(X1.numpy(), g[f"{tag}_X1"]) and np.array_equal(y1.numpy(), g[f"{tag}_y1"])
+    assert np.array_equal(noise.numpy(), g[f"{tag}_noise"])
+    assert X1.dtype == torch.float64 and tuple(y1.shape) == (X1.shape[0], 1) and exterior_points(boundary).shape == (14, 3)
+    # seeded generator path: same draws as torch.manual_seed(7); torch.rand
+    gen = torch.Generator().manual_seed(7)
+    X1b, _, _ = assemble_training_set(g[f"{tag}_observed"], g[f"{tag}_completed"], int(num_obs), int(num_gen), float(obs_noise),
+                                      float(gen_noise), int(num_internals), float(boundary), generator=gen)
+    assert np.array_equal(X1b.numpy(), g[f"{tag}_X1"])
