@@ -37,6 +37,7 @@ def parse():
     ap.add_argument("--object", default="mug", help="shipped GPIS state of the pregrasp workload (mug, hammer, lego, ...)")
     ap.add_argument("--points", type=int, default=1_000_000, help="sdf workload: query points")
     ap.add_argument("--subdiv", type=int, default=5, help="sdf workload: icosphere subdivisions (20 * 4^n faces)")
+    ap.add_argument("--sdf-mode", type=int, default=0, help="sdf workload: 0 auto (culled search), 1 exhaustive scan, 2 culled")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--var-mode", type=int, default=0,
                     help="gpis_c3: 0 auto (tcgen05 INT8 slices), -1 FP64 tensor MMA, 4..6 INT8 with that many slices")

@@ -37,6 +37,9 @@ def run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_rank
     lib = _lib.load()
     ctx = _lib.context(local)
 
+    from compliancedex_b200.sdf import set_search_mode
+    set_search_mode(args.sdf_mode)
+
     def step():
         return compute_sdf(p, fv)
 
@@ -77,6 +80,19 @@ def run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_rank
     barrier(world)
     ms_e2e = max_over_ranks(e0.elapsed_time(e1), world) / args.steps
 
+    # the exhaustive scan (the reference's algorithm on this repo's kernels) for comparison when the culled search was timed
+    exhaustive_ms = None
+    if args.sdf_mode != 1:
+        set_search_mode(1)
+        out1 = step()
+        e0.record()
+        for _ in range(args.steps):
+            out1 = step()
+        e1.record()
+        torch.cuda.synchronize()
+        exhaustive_ms = e0.elapsed_time(e1) / args.steps
+        assert all(torch.equal(a, b) for a, b in zip(out, out1)), "culled search and exhaustive scan disagree"
+        set_search_mode(args.sdf_mode)
     # the reference's own kernel, recompiled for sm_100a, same inputs, same run
     ref = None
     try:
@@ -120,6 +136,10 @@ def run_bench_sdf(args, rank, world, local, ClockSampler, barrier, max_over_rank
                      "flop_per_pair": FLOP_PER_PAIR, "pairs_per_launch": pairs, "pairs_per_s": pairs / (ms * 1e-3),
                      "traffic": ncu_traffic("r01_ncu_sdf_summary.json", "r01_prof_sdf_v2") if (P_total, subdiv, world) == (1_000_000, 5, 1) else None},
         "reference_kernel": ref,
+        "search": {"mode": {0: "auto (culled for F >= 512 and P >= 128 x SMs)", 1: "exhaustive", 2: "culled"}[args.sdf_mode],
+                   "exhaustive_scan_ms_per_step": exhaustive_ms,
+                   "note": "roofline.achieved counts ALL P x F pairs (the work the reference does); the culled search visits only "
+                           "the face tiles whose bounding sphere can still hold the closest face, and returns the same face bit for bit"},
     }
 
 

@@ -14,6 +14,8 @@
 //                     smallest distance" rule (strict < inside a tile and between tiles, :236,:243);
 //   sdf_final_kernel  one thread per point re-evaluates the winning face with the same device function and writes the four
 //                     outputs.
+//   sdf_tile_kernel + sdf_cull_kernel  (large batches) bounding-sphere culled search instead of sdf_pair_kernel: same face,
+//                     bit for bit, visiting only the tiles that can still hold it (see the comment above sdf_tile_kernel).
 // The arithmetic follows the reference expression by expression, including its quirks: the edge parameter is truncated to
 // float (point_at takes `float t`, :170) and so is the squared distance (`float dist`, :235), also for float64 inputs.
 // Bound: FP32 (FP64 for double inputs) FMA pipe - ~1e2 instructions per pair against 12 bytes per point.
@@ -204,6 +206,184 @@ sdf_pair_kernel(const T* __restrict__ points, int64_t P, const T* __restrict__ r
   }
 }
 
+// ---- culled search -----------------------------------------------------------------------------------------------------
+// Per 64-face tile a bounding sphere (float centre, radius rounded up).  A point needs a tile only if the sphere's lower bound
+// on the distance can still beat (or tie) its current best; the first best is the tightest UPPER bound min_t (|p - c_t| + r_t).
+// The surviving (point, tile) pairs of a warp are evaluated cooperatively - the point is broadcast, every lane takes two of the
+// tile's faces, a 64-bit shuffle-min picks (distance, lowest face index) - so no coherence between the points of a warp is
+// needed; when most lanes of a warp need the same tile each lane scans it for its own point instead (never worse than the
+// exhaustive kernel).  Bounds are conservative (relative 1e-5 and absolute 1e-6 x coordinate-scale slack), faces that tie with
+// the minimum are never skipped and the packed (distance, index) minimum is order independent, so the result is the same
+// face, bit for bit, as the exhaustive search and as the reference.
+constexpr int SDF_BCHUNK = 2048;   // tile bounds staged per pass (32 KB)
+
+template <typename T>
+__global__ void __launch_bounds__(32) sdf_tile_kernel(const T* __restrict__ rec, int64_t F, float4* __restrict__ bounds) {
+  const int64_t t = blockIdx.x;
+  const int lane = threadIdx.x;
+  const int64_t f0 = t * SDF_FT;
+  const int cnt = (int)min((int64_t)SDF_FT, F - f0);
+  double sx = 0.0, sy = 0.0, sz = 0.0;
+  for (int f = lane; f < cnt; f += 32) {
+    const T* r = rec + (f0 + f) * SDF_REC;
+    sx += (double)r[0] + (double)r[4] + (double)r[8];
+    sy += (double)r[1] + (double)r[5] + (double)r[9];
+    sz += (double)r[2] + (double)r[6] + (double)r[10];
+  }
+  for (int o = 16; o; o >>= 1) {
+    sx += __shfl_xor_sync(0xffffffffu, sx, o); sy += __shfl_xor_sync(0xffffffffu, sy, o); sz += __shfl_xor_sync(0xffffffffu, sz, o);
+  }
+  const float cx = (float)(sx / (3.0 * cnt)), cy = (float)(sy / (3.0 * cnt)), cz = (float)(sz / (3.0 * cnt));
+  double r2 = 0.0;
+  for (int f = lane; f < cnt; f += 32) {
+    const T* r = rec + (f0 + f) * SDF_REC;
+    for (int v = 0; v < 3; v++) {
+      const double dx = (double)r[4 * v] - (double)cx, dy = (double)r[4 * v + 1] - (double)cy, dz = (double)r[4 * v + 2] - (double)cz;
+      r2 = fmax(r2, dx * dx + dy * dy + dz * dz);
+    }
+  }
+  for (int o = 16; o; o >>= 1) r2 = fmax(r2, __shfl_xor_sync(0xffffffffu, r2, o));
+  // NaN / inf vertices: an infinite radius makes every point visit the tile
+  float rad = (float)(sqrt(r2) * (1.0 + 1e-6)) * (1.f + 1e-6f) + 1e-37f;
+  if (!(rad < INFINITY)) rad = INFINITY;
+  if (lane == 0) bounds[t] = make_float4(cx, cy, cz, rad);
+}
+
+__device__ __forceinline__ unsigned long long sdf_pack(float d, unsigned f) {
+  return ((unsigned long long)__float_as_uint(d) << 32) | f;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+sdf_cull_kernel(const T* __restrict__ points, int64_t P, const T* __restrict__ rec, const float4* __restrict__ bounds,
+                int64_t ntiles, int64_t F, unsigned long long* __restrict__ keys) {
+  __shared__ float4 sb[SDF_BCHUNK];
+  const int lane = threadIdx.x & 31;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = i < P;
+  const int64_t ii = valid ? i : P - 1;
+  const v3<T> p = {points[ii * 3], points[ii * 3 + 1], points[ii * 3 + 2]};
+  const float px = (float)p.x, py = (float)p.y, pz = (float)p.z;
+  const float pabs = fabsf(px) + fabsf(py) + fabsf(pz);
+  // ---- pass 1: the tightest upper bound on the distance to the mesh
+  float ubmin = INFINITY;
+  int64_t tstar = 0;
+  for (int64_t c0 = 0; c0 < ntiles; c0 += SDF_BCHUNK) {
+    const int n = (int)min((int64_t)SDF_BCHUNK, ntiles - c0);
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) sb[k] = bounds[c0 + k];
+    __syncthreads();
+    for (int k = 0; k < n; k++) {
+      const float4 b = sb[k];
+      const float dx = px - b.x, dy = py - b.y, dz = pz - b.z;
+      const float d = sqrtf(dx * dx + dy * dy + dz * dz);
+      const float slack = 1e-6f * (pabs + fabsf(b.x) + fabsf(b.y) + fabsf(b.z) + b.w);
+      const float ub = d + b.w + slack;
+      if (ub < ubmin) { ubmin = ub; tstar = c0 + k; }
+    }
+  }
+  float best = ubmin * ubmin * (1.f + 1e-5f);
+  if (!(best < INFINITY)) best = INFINITY;           // NaN coordinates: no culling at all
+  unsigned long long key = sdf_pack(best, 0xFFFFFFFFu);
+  // the tile that gave the upper bound first (cooperatively, one point at a time): it usually holds the closest face or a
+  // neighbour of it, so pass 2 starts from a near-final best and visits ~half as many tiles
+  {
+    unsigned m = __ballot_sync(0xffffffffu, valid);
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const v3<T> q = {__shfl_sync(0xffffffffu, p.x, src), __shfl_sync(0xffffffffu, p.y, src), __shfl_sync(0xffffffffu, p.z, src)};
+      const int64_t f0 = __shfl_sync(0xffffffffu, tstar, src) * SDF_FT;
+      const int cnt = (int)min((int64_t)SDF_FT, F - f0);
+      unsigned long long kk = ~0ull;
+#pragma unroll
+      for (int h = 0; h < SDF_FT / 32; h++) {
+        const int f = lane + 32 * h;
+        if (f < cnt) {
+          v3<T> cp;
+          const float dd = sdf_closest<T>(q, rec + (f0 + f) * SDF_REC, cp);
+          const unsigned long long k2 = sdf_pack(dd, (unsigned)(f0 + f));
+          kk = k2 < kk ? k2 : kk;
+        }
+      }
+#pragma unroll
+      for (int o = 16; o; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, kk, o);
+        kk = other < kk ? other : kk;
+      }
+      if (lane == src) key = kk < key ? kk : key;
+    }
+    best = __uint_as_float((unsigned)(key >> 32));
+  }
+  // ---- pass 2: visit the tiles whose lower bound can still beat or tie the best
+  for (int64_t c0 = 0; c0 < ntiles; c0 += SDF_BCHUNK) {
+    const int n = (int)min((int64_t)SDF_BCHUNK, ntiles - c0);
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) sb[k] = bounds[c0 + k];
+    __syncthreads();
+    for (int k = 0; k < n; k++) {
+      const float4 b = sb[k];
+      const float dx = px - b.x, dy = py - b.y, dz = pz - b.z;
+      const float d = sqrtf(dx * dx + dy * dy + dz * dz);
+      const float slack = 1e-6f * (pabs + fabsf(b.x) + fabsf(b.y) + fabsf(b.z) + b.w);
+      const float lb = d - b.w - slack;
+      const bool skip = lb > 0.f && lb * lb * (1.f - 1e-5f) > best * (1.f + 1e-5f);     // false for NaN: visit
+      const bool need = valid && !skip;
+      const unsigned mask = __ballot_sync(0xffffffffu, need);
+      if (mask == 0u) continue;
+      const int64_t f0 = (c0 + k) * SDF_FT;
+      const int cnt = (int)min((int64_t)SDF_FT, F - f0);
+      if (__popc(mask) >= 16) {                       // most of the warp wants this tile: every lane scans it for its own point
+        if (need) {
+          for (int f = 0; f < cnt; f++) {
+            v3<T> cp;
+            const float dd = sdf_closest<T>(p, rec + (f0 + f) * SDF_REC, cp);
+            const unsigned long long kk = sdf_pack(dd, (unsigned)(f0 + f));
+            key = kk < key ? kk : key;
+          }
+        }
+      } else {                                        // few lanes: the warp evaluates the tile for one point at a time
+        unsigned m = mask;
+        while (m) {
+          const int src = __ffs(m) - 1;
+          m &= m - 1;
+          const v3<T> q = {__shfl_sync(0xffffffffu, p.x, src), __shfl_sync(0xffffffffu, p.y, src), __shfl_sync(0xffffffffu, p.z, src)};
+          unsigned long long kk = ~0ull;
+#pragma unroll
+          for (int h = 0; h < SDF_FT / 32; h++) {
+            const int f = lane + 32 * h;
+            if (f < cnt) {
+              v3<T> cp;
+              const float dd = sdf_closest<T>(q, rec + (f0 + f) * SDF_REC, cp);
+              const unsigned long long k2 = sdf_pack(dd, (unsigned)(f0 + f));
+              kk = k2 < kk ? k2 : kk;
+            }
+          }
+#pragma unroll
+          for (int o = 16; o; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, kk, o);
+            kk = other < kk ? other : kk;
+          }
+          if (lane == src) key = kk < key ? kk : key;
+        }
+      }
+      best = __uint_as_float((unsigned)(key >> 32));
+    }
+  }
+  if (valid) {
+    if ((unsigned)(key & 0xFFFFFFFFull) == 0xFFFFFFFFu) {     // safety net (NaN bounds): exhaustive scan
+      key = ~0ull;
+      for (int64_t f = 0; f < F; f++) {
+        v3<T> cp;
+        const float dd = sdf_closest<T>(p, rec + f * SDF_REC, cp);
+        const unsigned long long kk = sdf_pack(dd, (unsigned)f);
+        if (f == 0 || kk < key) key = kk;
+      }
+    }
+    keys[i] = key;
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 sdf_final_kernel(const T* __restrict__ points, int64_t P, const T* __restrict__ rec, const unsigned long long* __restrict__ keys,
@@ -244,12 +424,16 @@ struct cdx_sdf_state {
   size_t rec_bytes = 0;
   unsigned long long* keys = nullptr;   // [P]
   int64_t keys_cap = 0;
+  float4* bounds = nullptr;             // [ntiles] bounding spheres of the face tiles
+  int64_t bounds_cap = 0;
+  int mode = 0;                         // cdx_sdf_set_mode: 0 auto (culled search for F >= 512 and P >= 128 x SMs), 1 exhaustive, 2 culled
 };
 
 void cdx_sdf_free(cdx_ctx* ctx) {
   if (!ctx || !ctx->sdf) return;
   cudaFree(ctx->sdf->rec);
   cudaFree(ctx->sdf->keys);
+  cudaFree(ctx->sdf->bounds);
   delete ctx->sdf;
   ctx->sdf = nullptr;
 }
@@ -276,22 +460,41 @@ static int sdf_forward_t(cdx_ctx* ctx, cdx_sdf_state* s, const T* points, int64_
   T* rec = reinterpret_cast<T*>(s->rec);
   sdf_face_kernel<T><<<(unsigned)((Fpad + 127) / 128), 128, 0, st>>>(fv, F, Fpad, rec);
   CDX_CHECK_LAUNCH(ctx);
-  CDX_CUDA(cudaMemsetAsync(s->keys, 0xFF, sizeof(unsigned long long) * (size_t)P, st));
-  // two points per thread (each record load serves two evaluations) whenever point tiles x face tiles can still give ~4 CTAs
-  // per SM; the faces are split over blockIdx.y until they do
-  const bool two = ((P + SDF_THREADS * 2 - 1) / (SDF_THREADS * 2)) * ntiles >= (int64_t)ctx->sms * 4;
-  const int ppt = two ? 2 : 1;
-  const int64_t nx = (P + SDF_THREADS * ppt - 1) / (SDF_THREADS * ppt);
-  int64_t ny = (ctx->sms * 4 + nx - 1) / nx;
-  if (ny > ntiles) ny = ntiles;
-  if (ny > 65535) ny = 65535;
-  if (ny < 1) ny = 1;
-  const int tpc = (int)((ntiles + ny - 1) / ny);
-  ny = (ntiles + tpc - 1) / tpc;
-  dim3 grid((unsigned)nx, (unsigned)ny);
-  if (two) sdf_pair_kernel<T, 2><<<grid, SDF_THREADS, 0, st>>>(points, P, rec, F, tpc, s->keys);
-  else sdf_pair_kernel<T, 1><<<grid, SDF_THREADS, 0, st>>>(points, P, rec, F, tpc, s->keys);
-  CDX_CHECK_LAUNCH(ctx);
+  // the culled search is one serial walk per point: it pays once there are enough points to fill the chip (measured: 4,096
+  // points x 20,480 faces 1.18 ms culled against 0.29 ms exhaustive; 1 M points 14.4 ms against 52.4 ms)
+  const bool cull = s->mode == 2 || (s->mode == 0 && F >= 512 && P >= (int64_t)ctx->sms * 128);
+  if (cull) {
+    if (ntiles > s->bounds_cap) {
+      CDX_CUDA(cudaStreamSynchronize(st));
+      cudaFree(s->bounds);
+      s->bounds = nullptr; s->bounds_cap = 0;
+      CDX_CUDA(cudaMalloc((void**)&s->bounds, sizeof(float4) * (size_t)ntiles));
+      s->bounds_cap = ntiles;
+    }
+    sdf_tile_kernel<T><<<(unsigned)ntiles, 32, 0, st>>>(rec, F, s->bounds);
+    CDX_CHECK_LAUNCH(ctx);
+    // small batches: 64-thread CTAs so that the points spread over the SMs
+    const int bt = P >= (int64_t)ctx->sms * 512 ? 256 : 64;
+    sdf_cull_kernel<T><<<(unsigned)((P + bt - 1) / bt), bt, 0, st>>>(points, P, rec, s->bounds, ntiles, F, s->keys);
+    CDX_CHECK_LAUNCH(ctx);
+  } else {
+    CDX_CUDA(cudaMemsetAsync(s->keys, 0xFF, sizeof(unsigned long long) * (size_t)P, st));
+    // two points per thread (each record load serves two evaluations) whenever point tiles x face tiles can still give ~4 CTAs
+    // per SM; the faces are split over blockIdx.y until they do
+    const bool two = ((P + SDF_THREADS * 2 - 1) / (SDF_THREADS * 2)) * ntiles >= (int64_t)ctx->sms * 4;
+    const int ppt = two ? 2 : 1;
+    const int64_t nx = (P + SDF_THREADS * ppt - 1) / (SDF_THREADS * ppt);
+    int64_t ny = (ctx->sms * 4 + nx - 1) / nx;
+    if (ny > ntiles) ny = ntiles;
+    if (ny > 65535) ny = 65535;
+    if (ny < 1) ny = 1;
+    const int tpc = (int)((ntiles + ny - 1) / ny);
+    ny = (ntiles + tpc - 1) / tpc;
+    dim3 grid((unsigned)nx, (unsigned)ny);
+    if (two) sdf_pair_kernel<T, 2><<<grid, SDF_THREADS, 0, st>>>(points, P, rec, F, tpc, s->keys);
+    else sdf_pair_kernel<T, 1><<<grid, SDF_THREADS, 0, st>>>(points, P, rec, F, tpc, s->keys);
+    CDX_CHECK_LAUNCH(ctx);
+  }
   sdf_final_kernel<T><<<(unsigned)((P + 255) / 256), 256, 0, st>>>(points, P, rec, s->keys, dist, sgn, normals, closest);
   CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
@@ -320,6 +523,13 @@ extern "C" int cdx_sdf_forward(cdx_ctx* ctx, const void* points, int64_t P, cons
                                           sign, (double*)normals, (double*)closest, st);
   return sdf_forward_t<float>(ctx, ctx->sdf, (const float*)points, P, (const float*)face_vertices, F, (float*)dist, sign,
                               (float*)normals, (float*)closest, st);
+}
+
+extern "C" int cdx_sdf_set_mode(cdx_ctx* ctx, int mode) {
+  if (!ctx || mode < 0 || mode > 2) { cdx_set_error("cdx_sdf_set_mode: mode must be 0 (auto), 1 (exhaustive) or 2 (culled)"); return CDX_ERR_ARG; }
+  if (!ctx->sdf) ctx->sdf = new cdx_sdf_state();
+  ctx->sdf->mode = mode;
+  return CDX_OK;
 }
 
 extern "C" int cdx_sdf_backward(cdx_ctx* ctx, const void* grad_dist, const void* points, const void* closest, int64_t P,

@@ -69,5 +69,12 @@ class _UnbatchedTriangleDistanceCuda(torch.autograd.Function):
         return grad_points, None
 
 
+def set_search_mode(mode, device=None):
+    """0 auto (bounding-sphere culled search when the mesh has >= 512 faces and there are >= 128 x SMs points), 1 exhaustive point x face scan (the reference's
+    algorithm), 2 culled always.  Every mode returns the same face, bit for bit."""
+    index = torch.cuda.current_device() if device is None else torch.device(device).index
+    _lib.check(_lib.load().cdx_sdf_set_mode(_lib.context(index), int(mode)))
+
+
 def compute_sdf(pointclouds, face_vertices):
     return _UnbatchedTriangleDistanceCuda.apply(pointclouds, face_vertices)

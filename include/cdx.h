@@ -90,6 +90,9 @@ int cdx_grid_surface(cdx_ctx* ctx, const float* mean_dev, int steps, long long* 
  * may be NULL.  F = 0 zero-fills the outputs (what the reference's pre-zeroed tensors keep). */
 int cdx_sdf_forward(cdx_ctx* ctx, const void* points_dev, int64_t P, const void* face_vertices_dev, int64_t F, int dtype,
                     void* dist_dev, int32_t* sign_dev, void* normals_dev, void* closest_dev, void* stream);
+/* search strategy of cdx_sdf_forward: 0 auto (bounding-sphere culled search for F >= 512 faces and P >= 128 x SMs points), 1 exhaustive point x face
+ * scan (what the reference does), 2 culled always.  Both return the same face, bit for bit. */
+int cdx_sdf_set_mode(cdx_ctx* ctx, int mode);
 /* unbatched_triangle_distance_backward_cuda (:256-270): grad_points [P,3] = 2 grad_dist (points - closest) */
 int cdx_sdf_backward(cdx_ctx* ctx, const void* grad_dist_dev, const void* points_dev, const void* closest_dev, int64_t P,
                      int dtype, void* grad_points_dev, void* stream);

@@ -12,6 +12,15 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=[1, 2], ids=["exhaustive", "culled"], autouse=True)
+def search_mode(request):
+    """every test runs with the exhaustive scan and with the bounding-sphere culled search (cdx_sdf_set_mode)"""
+    from compliancedex_b200.sdf import set_search_mode
+    set_search_mode(request.param)
+    yield request.param
+    set_search_mode(0)
+
+
 def _soup(F, seed, dtype):
     rng = np.random.default_rng(seed)
     c = rng.random((F, 1, 3)) * 2 - 1
@@ -111,3 +120,27 @@ def test_api_contract():
     faces = torch.randint(0, 10, (7, 3), device="cuda")
     fvv = index_vertices_by_faces(verts, faces)
     assert fvv.shape == (7, 3, 3) and torch.equal(fvv[3, 1], verts[faces[3, 1]])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_culled_search_equals_exhaustive_scan(dtype):
+    """same face, bit for bit, on coherent (icosphere), incoherent (triangle soup: bounds useless, dense fallback) and
+    degenerate-bound inputs (points far outside / exactly on vertices / huge coordinates)"""
+    from compliancedex_b200.sdf import compute_sdf, set_search_mode
+    from oracle import sdf_oracle as so
+    npd = np.float32 if dtype == torch.float32 else np.float64
+    g = torch.Generator().manual_seed(4)
+    for fv in (so.icosphere(4, 0.1, npd), _soup(4000, 5, npd), so.icosphere(3, 50.0, npd)):
+        f = torch.from_numpy(fv).cuda()
+        scale = float(np.abs(fv).max())
+        pts = [(torch.rand(20000, 3, generator=g, dtype=torch.float64) * 2 - 1) * 2 * scale,
+               (torch.rand(2000, 3, generator=g, dtype=torch.float64) * 2 - 1) * 200 * scale,
+               torch.from_numpy(fv.reshape(-1, 3)[:3000].astype(np.float64)),                       # exactly on vertices: ties
+               torch.from_numpy(fv.mean(axis=1)[:3000].astype(np.float64))]                          # face centroids
+        p = torch.cat(pts).to(dtype).cuda()
+        set_search_mode(1)
+        a = compute_sdf(p, f)
+        set_search_mode(2)
+        b = compute_sdf(p, f)
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
