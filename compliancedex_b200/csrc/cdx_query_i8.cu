@@ -44,7 +44,7 @@ constexpr double I8_MAGIC = 6755399441055744.0;  // 1.5 * 2^52: adding it leaves
 #endif
 #ifndef CDX_I8_EXP
 #define CDX_I8_EXP 0   // timing experiments only (results are wrong): 1 = no tcgen05.mma issued, 2 = no k* arithmetic in the generators,
-                       // 3 = no MMA and no tcgen05.st, 5 = generator loop only (no synchronisation at all, other warps idle), 4 = no MMA, generators do not wait for / read the TMA-staged points
+                       // 3 = no MMA and no tcgen05.st, 6 = MMAs issued but no tcgen05.st (A operand = stale tensor memory), 5 = generator loop only (no synchronisation at all, other warps idle), 4 = no MMA, generators do not wait for / read the TMA-staged points
 #endif
 #ifndef CDX_I8_NSB
 #define CDX_I8_NSB 6       // shared-memory stages of (U slices, points)
@@ -340,7 +340,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
           __syncwarp();
           tc_fence_after();
         }
-        if (CDX_I8_EXP == 3 || CDX_I8_EXP == 5) {   // timing experiment: no tensor-memory stores (keep the values alive)
+        if (CDX_I8_EXP == 3 || CDX_I8_EXP == 5 || CDX_I8_EXP == 6) {   // timing experiment: no tensor-memory stores (keep the values alive)
           unsigned x = 0;
 #pragma unroll
           for (int i = 0; i < S; i++) x ^= ow[i][0] ^ ow[i][1] ^ ow[i][2] ^ ow[i][3];
@@ -409,7 +409,7 @@ gpis_std_i8_kernel(const double* __restrict__ Xq, int64_t M, const double* __res
 #pragma unroll
               for (int ks = 0; ks < BK / 32; ks++) {
                 const uint64_t db = tc_desc(bbase + (d - i) * C::B_SLICE + ks * (2 * I8_TN * 16), I8_TN * 16, 128);
-                if (CDX_I8_EXP == 0 || CDX_I8_EXP == 2)
+                if (CDX_I8_EXP == 0 || CDX_I8_EXP == 2 || CDX_I8_EXP == 6)
                   tc_mma_i8_ts(tmem + d * I8_TN, abase + i * (BK / 4) + ks * 8, db, idesc, (c > 0 || ks > 0 || i > 0) ? 1u : 0u);
               }
           tc_commit(a_empty + 8 * sa);
