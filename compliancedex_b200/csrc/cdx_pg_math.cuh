@@ -372,6 +372,8 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
   // ---- compute_contact_margin (:703-710), GPIS terms (:733-736)
   double vv[4][3], rr[4], dd[4][3], ang2[4], m2[4], cm = 0.0, dist_cost = 0.0, tar_cost = 0.0;
   int fstar = 0;
+  double lsd[4];   // log(100 std_f): evaluated once per finger, compared and reused below (same values as re-evaluating)
+  for (int f = 0; f < 4; f++) lsd[f] = C.var_sum ? sd[f] : log(100.0 * sd[f]);
   for (int f = 0; f < 4; f++) {
     for (int r = 0; r < 3; r++) vv[f][r] = a[f][r] - T[f][r];
     rr[f] = sqrt(cdx_dot3(vv[f], vv[f]));
@@ -381,9 +383,9 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
     if (C.w_cm != 0.0) cm += 0.1 * log(ang2[f] + 1.0) + 0.9 * log(m2[f] + 1.0);   // prob only (:703-710)
     dist_cost += fabs(dist[f]);
     tar_cost += tdist[f];
-    if (log(100.0 * sd[f]) > log(100.0 * sd[fstar])) fstar = f;
+    if (lsd[f] > lsd[fstar]) fstar = f;
   }
-  const double var_cost = C.var_sum ? C.uncertainty * (sd[0] + sd[1] + sd[2] + sd[3]) : C.uncertainty * log(100.0 * sd[fstar]);
+  const double var_cost = C.var_sum ? C.uncertainty * (sd[0] + sd[1] + sd[2] + sd[3]) : C.uncertainty * lsd[fstar];
   // centre term of the Kin / GPIS optimizers (:474-477): w |mean_f a_f - mean_f T_f|
   double cd[3] = {0, 0, 0}, cn = 0.0;
   if (C.w_center != 0.0) {
