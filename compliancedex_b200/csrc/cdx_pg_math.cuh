@@ -228,6 +228,11 @@ CDX_HD void cdx_euler_xyz(const double* e, double* R, double* dR0, double* dR1, 
   }
 }
 
+// timing hook for the step kernel's sections (scripts/pg_ticks.py builds with -DCDX_PG_TICKS); a no-op otherwise
+#ifndef CDX_PG_TICK
+#define CDX_PG_TICK(i)
+#endif
+
 // ------------------------------------------------------------------------------------------------ 3x3 SVD
 // One-sided (Hestenes) Jacobi: A V = U diag(S), S descending - keeps full RELATIVE accuracy of the tiny singular
 // values that decide the Kabsch rotation when the cross-covariance is rank one + 1e-6 noise
@@ -309,6 +314,7 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
                        const double (*gmu)[3], const double (*gsd)[3], const double* tdist, const double (*gT)[3],
                        const double* noise, const cdx_pg_const& C, double& loss, double* margin, double (*ga)[3],
                        double (*gTo)[3], double* gk) {
+  CDX_PG_TICK(0);
   const int np = C.gravity ? 5 : 4;
   double S1[5][3], S2[5][3], w[5], n[4][3];
   for (int f = 0; f < 4; f++) {
@@ -334,7 +340,9 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
       for (int c = 0; c < 3; c++) H[r * 3 + c] += A[i][r] * Bm[i][c];
   }
   double U[9], S[3], V[9];
+  CDX_PG_TICK(1);
   cdx_svd3(H, U, S, V);
+  CDX_PG_TICK(2);
   const double dsg = (cdx_det3(V) * cdx_det3(U) < 0.0) ? -1.0 : 1.0;   // det(V U^T) < 0 -> flip V[:, -1] (:64-67)
   double R[9];
   for (int r = 0; r < 3; r++)
@@ -396,6 +404,7 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
   }
   loss = -C.w_reward * reward + 1000.0 * dist_cost + C.w_tar * tar_cost + (-C.w_cm * cm) + force_cost + var_cost + C.w_center * cn;
 
+  CDX_PG_TICK(3);
   // ================================================================================ reverse pass
   double gS1[5][3], gS2[5][3], gw[5], gR[9], gt[3] = {0, 0, 0};
   for (int i = 0; i < 5; i++) { gw[i] = 0.0; for (int r = 0; r < 3; r++) { gS1[i][r] = 0.0; gS2[i][r] = 0.0; } }
@@ -455,6 +464,7 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
   }
   if (!C.var_sum)
     for (int r = 0; r < 3; r++) ga[fstar][r] += C.uncertainty / sd[fstar] * gsd[fstar][r];
+  CDX_PG_TICK(4);
   // t = sum_i w_i (S2_i - R S1_i) / W
   double rgt[3];
   cdx_mtv(R, gt, rgt);
@@ -482,6 +492,7 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
   cdx_mm(V, Z, Tm);
   cdx_mm(Tm, Vt, Y0);
   cdx_mm(Rt, Y0, GH);
+  CDX_PG_TICK(5);
   // H = sum_i A_i B_i^T,  A_i = w_i (S1_i - c1),  B_i = w_i (S2_i - c2)
   double sA[3] = {0, 0, 0}, sB[3] = {0, 0, 0}, gA[5][3], gB[5][3];
   for (int i = 0; i < np; i++) {
@@ -502,6 +513,7 @@ CDX_HD void cdx_pg_row(const double (*a)[3], const double (*T)[3], const double*
     gk[f] += gw[f];
     for (int r = 0; r < 3; r++) { ga[f][r] += gS1[f][r]; gTo[f][r] += gS2[f][r]; }
   }
+  CDX_PG_TICK(6);
 }
 
 // ------------------------------------------------------------------------------------------------ closure

@@ -12,7 +12,18 @@
 #include <vector>
 #include "cdx_internal.cuh"
 #include "cdx_noise.cuh"
+#ifdef CDX_PG_TICKS   // section timing of the step kernel (scripts/pg_ticks.py): thread 0 of CTA 0 records clock64()
+__device__ long long cdx_pg_ticks[16];
+#ifdef __CUDA_ARCH__
+#define CDX_PG_TICK(i) do { if (threadIdx.x == 0 && blockIdx.x == 0) cdx_pg_ticks[i] = clock64(); } while (0)
+#endif
+#endif
 #include "cdx_pg_math.cuh"
+#ifdef CDX_PG_TICKS
+extern "C" int cdx_debug_pg_ticks(long long* out16) {
+  return cudaMemcpyFromSymbol(out16, cdx_pg_ticks, sizeof(long long) * 16) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 struct cdx_pg_state {
   int64_t B = 0, cap = 0;
@@ -124,8 +135,19 @@ __global__ void pg_fill_kernel(double* p, int64_t n, double v) {
 __device__ __forceinline__ double clamp_lo(double x, double lo) { return x < lo ? lo : x; }
 __device__ __forceinline__ double clamp_hi(double x, double hi) { return x > hi ? hi : x; }
 
-constexpr int CPB = 16;     // candidates per CTA: 4 lanes each
+#ifndef CDX_PG_CPB
+#define CDX_PG_CPB 8
+#endif
+constexpr int CPB = CDX_PG_CPB;   // candidates per CTA: 4 lanes each
 constexpr int NRED = 33;    // total | margin 4 | gk 4 | gtips 12 | gT 12
+// the step kernel runs one or two warps per SM, so every global load's latency is exposed: everything it will need (GPIS
+// outputs, moments, its finger's Jacobian) is requested with cp.async at entry and lands in shared memory while the
+// prologue (Euler angles, noise keys) runs
+constexpr int NGP = 16 + 16 + 48 + 48 + 9 + 27;   // dist | sd | gmu | gsd (up to 4 copy blocks) | mean9 | gmean9
+__device__ __forceinline__ void pg_cp8(void* smem, const void* g) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g) : "memory");
+}
+__device__ __forceinline__ void pg_cp_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // One closure (+ optional optimiser step) per candidate, spread over a group of 4 lanes:
 //   lane p < P evaluates pregrasp copy p (cdx_pg_row: Kabsch equilibrium, costs, analytic reverse pass) - the copies are
@@ -149,11 +171,30 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   __shared__ double sp[CPB][NPAR];      // the candidate's parameters: q16 | k4 | T12 | palm6
   __shared__ double sr[CPB][NRED];      // reduced per-copy results
   __shared__ double sg[CPB][NPAR];      // gradient
+  CDX_PG_TICK(7);
   const int l = threadIdx.x & 3, cl = threadIdx.x >> 2;
   const int64_t b = (int64_t)blockIdx.x * CPB + cl;
   if (b >= B) return;                   // whole 4-lane groups leave together
   const unsigned gmask = 0xFu << ((threadIdx.x & 31) & ~3);
   const int nd = S.n_dofs;
+  __shared__ double sq[CPB][NGP];       // GPIS outputs of this candidate
+  __shared__ double sm1[CPB][NPAR], sm2[CPB][NPAR];
+  __shared__ __align__(8) float sJ[CPB][4][3 * CDX_MAX_CHAIN_DOF];
+  {
+    double* g = sq[cl];
+    for (int i = l; i < U * 4; i += 4) { pg_cp8(g + i, dist + b * U * 4 + i); pg_cp8(g + 16 + i, sd + b * U * 4 + i); }
+    for (int i = l; i < U * 12; i += 4) { pg_cp8(g + 32 + i, gmu + b * U * 12 + i); pg_cp8(g + 80 + i, gsd + b * U * 12 + i); }
+    for (int i = l; i < 9; i += 4) pg_cp8(g + 128 + i, mean9 + b * 9 + i);
+    for (int i = l; i < 27; i += 4) pg_cp8(g + 137 + i, gmean9 + b * 27 + i);
+    if (V != 2) {
+      const float* Jf = J + (b * 4 + l) * 3 * CDX_MAX_CHAIN_DOF;
+      for (int i = 0; i < 3 * CDX_MAX_CHAIN_DOF / 2; i++) pg_cp8(&sJ[cl][l][2 * i], Jf + 2 * i);
+    }
+    if (do_step)
+      for (int i = l; i < NPAR; i += 4) { pg_cp8(&sm1[cl][i], m1 + b * NPAR + i); pg_cp8(&sm2[cl][i], m2 + b * NPAR + i); }
+  }
+  double oval = 0.0, bc1 = 0.0, bc2s = 0.0;
+  if (do_step) { oval = ovalue[b]; bc1 = adam_tab[2 * it]; bc2s = adam_tab[2 * it + 1]; }
   double* par = sp[cl];
   for (int i = l; i < NPAR; i += 4)
     par[i] = i < 16 ? (i < nd ? q[b * nd + i] : 0.0) : (i < 20 ? k[b * 4 + i - 16] : (i < 32 ? T[b * 12 + i - 20] : palm[b * 6 + i - 32]));
@@ -182,14 +223,16 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     latched[b * 4 + l] = mring[((it - 1) & 1) * B * 4 + b * 4 + l];
     if (b == 0 && l == 0) latch[2] = it - 1;
   }
-  const double* m9 = mean9 + b * 9;
-  const double* g9 = gmean9 + b * 27;
+  const double* m9 = sq[cl] + 128;
+  const double* g9 = sq[cl] + 137;
   // ---- copy p = l
   double red[NRED];
 #pragma unroll
   for (int i = 0; i < NRED; i++) red[i] = 0.0;
   double wsum = 0.0;
   for (int p = 0; p < S.P; p++) wsum += S.weight[p];
+  pg_cp_wait();
+  __syncwarp(gmask);                    // the group's staged GPIS outputs are visible to its four lanes
   if (l < S.P) {
     const int p = l, u = S.uniq[p];
     double a[4][3], noise[9], lossp, mg[4], ga[4][3], gTr[4][3], gkr[4];
@@ -199,10 +242,11 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     const int64_t gb = prm.env_offset + b;
 #pragma unroll
     for (int e = 0; e < 9; e++) noise[e] = cdx_kabsch_noise(prm.noise_seed, it, p, gb, e);
-    const int64_t e0 = (b * U + u) * 4;
-    cdx_pg_row(a, Tp, par + 16, dist + e0, sd + e0, reinterpret_cast<const double (*)[3]>(gmu + e0 * 3),
-               reinterpret_cast<const double (*)[3]>(gsd + e0 * 3), m9, reinterpret_cast<const double (*)[3]>(g9), noise, S.C,
-               lossp, mg, ga, gTr, gkr);
+    const double* gq = sq[cl];
+    CDX_PG_TICK(8);
+    cdx_pg_row(a, Tp, par + 16, gq + u * 4, gq + 16 + u * 4, reinterpret_cast<const double (*)[3]>(gq + 32 + u * 12),
+               reinterpret_cast<const double (*)[3]>(gq + 80 + u * 12), m9, reinterpret_cast<const double (*)[3]>(g9), noise,
+               S.C, lossp, mg, ga, gTr, gkr);
     const double wp = S.weight[p];
     red[0] = wp * (lossp + S.w_ref * refn);
 #pragma unroll
@@ -226,6 +270,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   if (l == 0)
     for (int i = 0; i < NRED; i++) sr[cl][i] = red[i];
   __syncwarp(gmask);
+  CDX_PG_TICK(9);
   // ---- :757-763 and the chain rule of finger f = l
   double total = red[0];
   for (int f = 0; f < 4; f++) total -= S.w_pre * m9[4 + f];
@@ -255,7 +300,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     __syncwarp(gmask);
   } else {
     const cdx_chain& ch = hand->finger[f];
-    const float* Jf = J + (b * 4 + f) * 3 * CDX_MAX_CHAIN_DOF;
+    const float* Jf = sJ[cl][f];
     for (int turn = 0; turn < 4; turn++) {
       if (turn == f)
         for (int c = 0; c < ch.ndof; c++) {
@@ -286,9 +331,10 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     if (margin) for (int i = 0; i < 4; i++) margin[b * 4 + i] = sr[cl][1 + i];
   }
   if (grad) for (int i = l; i < NPAR; i += 4) grad[b * NPAR + i] = g[i];
+  CDX_PG_TICK(10);
   if (!do_step) return;
   // ---- best-iterate tracking (:822-829): BEFORE the optimiser step, only for s > track_after; NaN never updates
-  const bool better = it > prm.track_after && total < ovalue[b];
+  const bool better = it > prm.track_after && total < oval;
   __syncwarp(gmask);                                    // every lane has read ovalue[b] before lane 0 overwrites it
   if (V != 0) {
     mring[(it & 1) * B * 4 + b * 4 + l] = sr[cl][1 + l];
@@ -309,19 +355,19 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   }
   // ---- torch.optim.Adam (:796,:831): exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2 v + (1-b2) g^2;
   //      p -= (lr / (1-b1^t)) * m / (sqrt(v)/sqrt(1-b2^t) + eps);  then the clamps (:833-834)
-  const double bc1 = adam_tab[2 * it], bc2s = adam_tab[2 * it + 1];
   const double omb1 = 1.0 - prm.beta1, omb2 = 1.0 - prm.beta2;
-  for (int i = l; i < NPAR; i += 4) {
-    int grp;
-    bool upd = true;
-    if (i < 16) { upd = i < nd; grp = 0; }
-    else if (i < 20) grp = 1;
-    else if (i < 32) { upd = prm.optimize_target != 0; grp = 2; }
-    else { upd = prm.optimize_palm != 0; grp = i < 35 ? 3 : 4; }
+  // lane l owns parameters i = l + 4 j; unrolled over j the group of a parameter (q | k | T | palm xyz | palm rpy) is known
+  // at compile time except in the palm block, and the ten independent sqrt / divide chains overlap
+#pragma unroll
+  for (int j = 0; j < (NPAR + 3) / 4; j++) {
+    const int i = l + 4 * j;
+    if (i >= NPAR) break;
+    const int grp = j < 4 ? 0 : (j == 4 ? 1 : (j < 8 ? 2 : (i < 35 ? 3 : 4)));
+    const bool upd = j < 4 ? i < nd : (j == 4 ? true : (j < 8 ? prm.optimize_target != 0 : prm.optimize_palm != 0));
     double pv = par[i];
     if (upd && V == 0) {
       const double gi = g[i];
-      double m = m1[b * NPAR + i], v = m2[b * NPAR + i];
+      double m = sm1[cl][i], v = sm2[cl][i];
       m = m + omb1 * (gi - m);
       v = v * prm.beta2 + omb2 * gi * gi;
       m1[b * NPAR + i] = m;
@@ -333,27 +379,29 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
       // torch.optim.RMSprop (:451-456, :347-352; alpha 0.99, eps 1e-8, no momentum, not centered):
       //   square_avg = alpha square_avg + (1 - alpha) g^2;  p -= lr * g / (sqrt(square_avg) + eps)
       const double gi = g[i];
-      double v = m2[b * NPAR + i];
+      double v = sm2[cl][i];
       v = v * prm.rms_alpha + (1.0 - prm.rms_alpha) * gi * gi;
       m2[b * NPAR + i] = v;
       pv = pv + (-prm.lr[grp] * gi) / (sqrt(v) + prm.eps);   // addcdiv_(g, avg, value=-lr): (value * g) / avg
     }
-    if (V == 2 && i < 12)   // tip_pose.clamp_(box) (:402)
+    if (V == 2 && j < 3)    // tip_pose.clamp_(box) (:402)
       pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[i / 3][i % 3]), (double)prm.box_hi[i / 3][i % 3]);
-    if (i >= 16 && i < 20) pv = clamp_lo(pv, prm.compliance_min);
-    if (i >= 20 && i < 32 && V != 2) {   // target clamp: prob (:834) and Kin (:505); commented out at :404
+    if (j == 4) pv = clamp_lo(pv, prm.compliance_min);
+    if (j >= 5 && j < 8 && V != 2) {   // target clamp: prob (:834) and Kin (:505); commented out at :404
       const int e = i - 20;
       pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[e / 3][e % 3]), (double)prm.box_hi[e / 3][e % 3]);
     }
     par[i] = pv;
-    if (i < 16) { if (i < nd) q[b * nd + i] = pv; }
-    else if (i < 20) k[b * 4 + i - 16] = pv;
-    else if (i < 32) T[b * 12 + i - 20] = pv;
+    if (j < 4) { if (i < nd) q[b * nd + i] = pv; }
+    else if (j == 4) k[b * 4 + i - 16] = pv;
+    else if (j < 8) T[b * 12 + i - 20] = pv;
     else palm[b * 6 + i - 32] = pv;
   }
   __syncwarp(gmask);
+  CDX_PG_TICK(11);
   // ---- FK + GPIS query points of the NEW iterate (what pg_points_kernel does for the first iteration)
   pg_emit_points<V>(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
+  CDX_PG_TICK(12);
 }
 
 // ProbabilisticGraspOptimizer.compute_collision_loss (optimize_pregrasp.py:684-701) on anchor poses [B,A,3]: thread per
