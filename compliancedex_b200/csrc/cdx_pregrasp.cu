@@ -19,6 +19,7 @@ __device__ long long cdx_pg_ticks[16];
 #endif
 #endif
 #include "cdx_pg_math.cuh"
+#include "cdx_pg_row_coop.cuh"
 #ifdef CDX_PG_TICKS
 extern "C" int cdx_debug_pg_ticks(long long* out16) {
   return cudaMemcpyFromSymbol(out16, cdx_pg_ticks, sizeof(long long) * 16) == cudaSuccess ? 0 : -1;
@@ -138,7 +139,7 @@ __device__ __forceinline__ double clamp_hi(double x, double hi) { return x > hi 
 #ifndef CDX_PG_CPB
 #define CDX_PG_CPB 8
 #endif
-constexpr int CPB = CDX_PG_CPB;   // candidates per CTA: 4 lanes each
+constexpr int CPB = CDX_PG_CPB;   // candidates per CTA: 16 lanes each
 constexpr int NRED = 33;    // total | margin 4 | gk 4 | gtips 12 | gT 12
 // the step kernel runs one or two warps per SM, so every global load's latency is exposed: everything it will need (GPIS
 // outputs, moments, its finger's Jacobian) is requested with cp.async at entry and lands in shared memory while the
@@ -149,14 +150,15 @@ __device__ __forceinline__ void pg_cp8(void* smem, const void* g) {
 }
 __device__ __forceinline__ void pg_cp_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-// One closure (+ optional optimiser step) per candidate, spread over a group of 4 lanes:
-//   lane p < P evaluates pregrasp copy p (cdx_pg_row: Kabsch equilibrium, costs, analytic reverse pass) - the copies are
-//   independent given the GPIS outputs - and the weighted sum over copies (:755) is a 2-step shuffle reduction;
-//   lane f then owns finger f: chain rule through the palm transform and the float32 FK Jacobian, its share of the
-//   38 parameters in best-iterate tracking (:822-829), Adam (:831) and the clamps (:833-834), and - when stepping - the FK
-//   and query points of the NEW iterate, so the next iteration needs no separate points launch.
+// One closure (+ optional optimiser step) per candidate, spread over a group of 16 lanes (p, f) = (lane >> 2, lane & 3):
+//   the four lanes of copy p < P evaluate pregrasp copy p together (cdx_pg_row_coop: Kabsch equilibrium, costs, analytic
+//   reverse pass, lane f owning finger f) - the copies are independent given the GPIS outputs - and the weighted sum over
+//   copies (:755) is a 2-step shuffle reduction over p;
+//   lane (0, f) then owns finger f: chain rule through the palm transform and the float32 FK Jacobian, and - when stepping -
+//   the FK and query points of the NEW iterate, so the next iteration needs no separate points launch;
+//   the 38 parameters are spread over the 16 lanes for best-iterate tracking (:822-829), Adam (:831) and the clamps (:833-834).
 template <int V>
-__global__ void __launch_bounds__(CPB * 4)
+__global__ void __launch_bounds__(CPB * 16)
 pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_setup S, cdx_pregrasp_params prm,
                double* __restrict__ q, double* __restrict__ k, double* __restrict__ T, double* __restrict__ palm,
                double* __restrict__ tl, float* __restrict__ J, const double* __restrict__ dist,
@@ -169,36 +171,37 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
                double* __restrict__ Xmean, double* __restrict__ mring, double* __restrict__ latched,
                int* __restrict__ latch) {
   __shared__ double sp[CPB][NPAR];      // the candidate's parameters: q16 | k4 | T12 | palm6
-  __shared__ double sr[CPB][NRED];      // reduced per-copy results
+  __shared__ double sr[CPB][NRED];      // results reduced over the copies
   __shared__ double sg[CPB][NPAR];      // gradient
-  CDX_PG_TICK(7);
-  const int l = threadIdx.x & 3, cl = threadIdx.x >> 2;
-  const int64_t b = (int64_t)blockIdx.x * CPB + cl;
-  if (b >= B) return;                   // whole 4-lane groups leave together
-  const unsigned gmask = 0xFu << ((threadIdx.x & 31) & ~3);
-  const int nd = S.n_dofs;
   __shared__ double sq[CPB][NGP];       // GPIS outputs of this candidate
   __shared__ double sm1[CPB][NPAR], sm2[CPB][NPAR];
   __shared__ __align__(8) float sJ[CPB][4][3 * CDX_MAX_CHAIN_DOF];
+  CDX_PG_TICK(7);
+  const int sub = threadIdx.x & 15, p = sub >> 2, l = sub & 3, cl = threadIdx.x >> 4;
+  const int64_t b = (int64_t)blockIdx.x * CPB + cl;
+  if (b >= B) return;                   // whole 16-lane groups leave together
+  const unsigned gmask = 0xFFFFu << ((threadIdx.x & 31) & 16);
+  const unsigned fmask = 0xFu << ((threadIdx.x & 31) & ~3);
+  const int nd = S.n_dofs;
   {
     double* g = sq[cl];
-    for (int i = l; i < U * 4; i += 4) { pg_cp8(g + i, dist + b * U * 4 + i); pg_cp8(g + 16 + i, sd + b * U * 4 + i); }
-    for (int i = l; i < U * 12; i += 4) { pg_cp8(g + 32 + i, gmu + b * U * 12 + i); pg_cp8(g + 80 + i, gsd + b * U * 12 + i); }
-    for (int i = l; i < 9; i += 4) pg_cp8(g + 128 + i, mean9 + b * 9 + i);
-    for (int i = l; i < 27; i += 4) pg_cp8(g + 137 + i, gmean9 + b * 27 + i);
-    if (V != 2) {
+    for (int i = sub; i < U * 4; i += 16) { pg_cp8(g + i, dist + b * U * 4 + i); pg_cp8(g + 16 + i, sd + b * U * 4 + i); }
+    for (int i = sub; i < U * 12; i += 16) { pg_cp8(g + 32 + i, gmu + b * U * 12 + i); pg_cp8(g + 80 + i, gsd + b * U * 12 + i); }
+    if (sub < 9) pg_cp8(g + 128 + sub, mean9 + b * 9 + sub);
+    for (int i = sub; i < 27; i += 16) pg_cp8(g + 137 + i, gmean9 + b * 27 + i);
+    if (V != 2 && p == 1) {
       const float* Jf = J + (b * 4 + l) * 3 * CDX_MAX_CHAIN_DOF;
       for (int i = 0; i < 3 * CDX_MAX_CHAIN_DOF / 2; i++) pg_cp8(&sJ[cl][l][2 * i], Jf + 2 * i);
     }
     if (do_step)
-      for (int i = l; i < NPAR; i += 4) { pg_cp8(&sm1[cl][i], m1 + b * NPAR + i); pg_cp8(&sm2[cl][i], m2 + b * NPAR + i); }
+      for (int i = sub; i < NPAR; i += 16) { pg_cp8(&sm1[cl][i], m1 + b * NPAR + i); pg_cp8(&sm2[cl][i], m2 + b * NPAR + i); }
   }
   double oval = 0.0, bc1 = 0.0, bc2s = 0.0;
   if (do_step) { oval = ovalue[b]; bc1 = adam_tab[2 * it]; bc2s = adam_tab[2 * it + 1]; }
   double* par = sp[cl];
-  for (int i = l; i < NPAR; i += 4)
+  for (int i = sub; i < NPAR; i += 16)
     par[i] = i < 16 ? (i < nd ? q[b * nd + i] : 0.0) : (i < 20 ? k[b * 4 + i - 16] : (i < 32 ? T[b * 12 + i - 20] : palm[b * 6 + i - 32]));
-  for (int i = l; i < 16; i += 4) sg[cl][i] = 0.0;
+  sg[cl][sub] = 0.0;
   __syncwarp(gmask);
   const double (*Tp)[3] = reinterpret_cast<const double (*)[3]>(par + 20);
   const double (*tlp)[3] = reinterpret_cast<const double (*)[3]>(tl + b * 12);
@@ -213,65 +216,76 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   }
   double refn = 0.0;
   if (S.w_ref != 0.0) {
-    for (int i = l; i < nd; i += 4) refn += (par[i] - S.ref_q[i]) * (par[i] - S.ref_q[i]);
+    if (sub < nd) refn = (par[sub] - S.ref_q[sub]) * (par[sub] - S.ref_q[sub]);
+    refn += __shfl_xor_sync(gmask, refn, 4);
+    refn += __shfl_xor_sync(gmask, refn, 8);
     refn += __shfl_xor_sync(gmask, refn, 1);
     refn += __shfl_xor_sync(gmask, refn, 2);
     refn = sqrt(refn);
   }
   // Kin / GPIS variants: the margin of the previous iteration becomes the latched opt_margin if anything improved then
-  if (V != 0 && do_step && it > 0 && latch[(it - 1) & 1] == it - 1) {
+  if (V != 0 && do_step && it > 0 && latch[(it - 1) & 1] == it - 1 && p == 0) {
     latched[b * 4 + l] = mring[((it - 1) & 1) * B * 4 + b * 4 + l];
     if (b == 0 && l == 0) latch[2] = it - 1;
   }
   const double* m9 = sq[cl] + 128;
   const double* g9 = sq[cl] + 137;
-  // ---- copy p = l
-  double red[NRED];
-#pragma unroll
-  for (int i = 0; i < NRED; i++) red[i] = 0.0;
   double wsum = 0.0;
-  for (int p = 0; p < S.P; p++) wsum += S.weight[p];
+  for (int c = 0; c < S.P; c++) wsum += S.weight[c];
+  // noise[9] of copy p (replaces torch.rand_like(H), :61): lane f draws elements f, f+4, f+8 and the four lanes exchange
+  double noise[9];
+  {
+    const int64_t gb = prm.env_offset + b;
+    double mine[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) mine[j] = (l + 4 * j < 9) ? cdx_kabsch_noise(prm.noise_seed, it, p, gb, l + 4 * j) : 0.0;
+#pragma unroll
+    for (int e = 0; e < 9; e++) noise[e] = __shfl_sync(fmask, mine[e >> 2], e & 3, 4);
+  }
   pg_cp_wait();
-  __syncwarp(gmask);                    // the group's staged GPIS outputs are visible to its four lanes
-  if (l < S.P) {
-    const int p = l, u = S.uniq[p];
-    double a[4][3], noise[9], lossp, mg[4], ga[4][3], gTr[4][3], gkr[4];
+  __syncwarp(gmask);                    // the group's staged GPIS outputs are visible to its sixteen lanes
+  // ---- copy p, finger l
+  double red[9];                        // total | margin_f | gk_f | gtips_f 3 | gT_f 3
+#pragma unroll
+  for (int i = 0; i < 9; i++) red[i] = 0.0;
+  if (p < S.P) {
+    const int u = S.uniq[p];
+    double a[4][3], lossp, mg, ga[3], gTr[3], gkr;
 #pragma unroll
     for (int f = 0; f < 4; f++)
       for (int r = 0; r < 3; r++) a[f][r] = V ? tips[f][r] : Tp[f][r] + S.coeff[p][f] * (tips[f][r] - Tp[f][r]);
-    const int64_t gb = prm.env_offset + b;
-#pragma unroll
-    for (int e = 0; e < 9; e++) noise[e] = cdx_kabsch_noise(prm.noise_seed, it, p, gb, e);
     const double* gq = sq[cl];
     CDX_PG_TICK(8);
-    cdx_pg_row(a, Tp, par + 16, gq + u * 4, gq + 16 + u * 4, reinterpret_cast<const double (*)[3]>(gq + 32 + u * 12),
-               reinterpret_cast<const double (*)[3]>(gq + 80 + u * 12), m9, reinterpret_cast<const double (*)[3]>(g9), noise,
-               S.C, lossp, mg, ga, gTr, gkr);
+    cdx_pg_row_coop(l, fmask, a, Tp, par + 16, gq + u * 4, gq + 16 + u * 4, reinterpret_cast<const double (*)[3]>(gq + 32 + u * 12),
+                    reinterpret_cast<const double (*)[3]>(gq + 80 + u * 12), m9, reinterpret_cast<const double (*)[3]>(g9), noise,
+                    S.C, lossp, mg, ga, gTr, gkr);
+    CDX_PG_TICK(6);
     const double wp = S.weight[p];
+    const double c = S.coeff[p][l];
     red[0] = wp * (lossp + S.w_ref * refn);
-#pragma unroll
-    for (int f = 0; f < 4; f++) {
-      red[1 + f] = wp * mg[f];
-      red[5 + f] = wp * gkr[f];
-      const double c = S.coeff[p][f];
-      for (int r = 0; r < 3; r++) {
-        red[9 + f * 3 + r] = wp * c * ga[f][r];
-        red[21 + f * 3 + r] = wp * ((1.0 - c) * ga[f][r] + gTr[f][r]);
-      }
+    red[1] = wp * mg;
+    red[2] = wp * gkr;
+    for (int r = 0; r < 3; r++) {
+      red[3 + r] = wp * c * ga[r];
+      red[6 + r] = wp * ((1.0 - c) * ga[r] + gTr[r]);
     }
   }
 #pragma unroll
-  for (int i = 0; i < NRED; i++) {
+  for (int i = 0; i < 9; i++) {         // over the copies: (p0 + p1) + (p2 + p3)
     double v = red[i];
-    v += __shfl_xor_sync(gmask, v, 1);
-    v += __shfl_xor_sync(gmask, v, 2);
+    v += __shfl_xor_sync(gmask, v, 4);
+    v += __shfl_xor_sync(gmask, v, 8);
     red[i] = v;
   }
-  if (l == 0)
-    for (int i = 0; i < NRED; i++) sr[cl][i] = red[i];
+  if (p == 0) {
+    if (l == 0) sr[cl][0] = red[0];
+    sr[cl][1 + l] = red[1];
+    sr[cl][5 + l] = red[2];
+    for (int r = 0; r < 3; r++) { sr[cl][9 + l * 3 + r] = red[3 + r]; sr[cl][21 + l * 3 + r] = red[6 + r]; }
+  }
   __syncwarp(gmask);
   CDX_PG_TICK(9);
-  // ---- :757-763 and the chain rule of finger f = l
+  // ---- :757-763 and the chain rule of finger f = l (lanes of p == 0)
   double total = red[0];
   for (int f = 0; f < 4; f++) total -= S.w_pre * m9[4 + f];
   double gpalm_pm[3] = {0.0, 0.0, 0.0};
@@ -281,71 +295,68 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     for (int r = 0; r < 3; r++) gpalm_pm[r] = -g9[24 + r] / (pm * pm);
   }
   const int f = l;
-  double gt[3], gl[3], acc[12];
-  for (int r = 0; r < 3; r++) gt[r] = sr[cl][9 + f * 3 + r] - S.w_pre * g9[(4 + f) * 3 + r];
-  cdx_mtv(Rw, gt, gl);
-  for (int r = 0; r < 3; r++) {
-    acc[r] = gt[r];
-    for (int c = 0; c < 3; c++) acc[3 + r * 3 + c] = gt[r] * tlp[f][c];
-  }
-#pragma unroll
-  for (int i = 0; i < 12; i++) {
-    acc[i] += __shfl_xor_sync(gmask, acc[i], 1);
-    acc[i] += __shfl_xor_sync(gmask, acc[i], 2);
-  }
-  // back through .double() (:666) into the float32 FK graph; fingers take turns so shared joints would accumulate
-  const float g32[3] = {(float)gl[0], (float)gl[1], (float)gl[2]};
-  if (V == 2) {
-    for (int r = 0; r < 3; r++) sg[cl][f * 3 + r] = gt[r];       // tip_pose is the leaf
-    __syncwarp(gmask);
-  } else {
-    const cdx_chain& ch = hand->finger[f];
-    const float* Jf = sJ[cl][f];
-    for (int turn = 0; turn < 4; turn++) {
-      if (turn == f)
-        for (int c = 0; c < ch.ndof; c++) {
-          const float gj = Jf[c] * g32[0] + Jf[CDX_MAX_CHAIN_DOF + c] * g32[1] + Jf[2 * CDX_MAX_CHAIN_DOF + c] * g32[2];
-          sg[cl][ch.dofs[c]] += (double)gj;
-        }
-      __syncwarp(gmask);
-    }
-  }
   double* g = sg[cl];
-  if (S.w_ref != 0.0)
-    for (int i = l; i < nd; i += 4) g[i] += refn > 0.0 ? wsum * S.w_ref * (par[i] - S.ref_q[i]) / refn : 0.0;
-  g[16 + f] = sr[cl][5 + f];
-  for (int r = 0; r < 3; r++) g[20 + f * 3 + r] = sr[cl][21 + f * 3 + r];
-  for (int i = l; i < 6; i += 4) {
-    double v;
-    if (i < 3) v = acc[i] + gpalm_pm[i];
-    else {
-      const double* dR = i == 3 ? dR0 : (i == 4 ? dR1 : dR2);
-      v = 0.0;
-      for (int e = 0; e < 9; e++) v += acc[3 + e] * dR[e];
+  if (p == 0) {
+    double gt[3], gl[3], acc[12];
+    for (int r = 0; r < 3; r++) gt[r] = red[3 + r] - S.w_pre * g9[(4 + f) * 3 + r];
+    cdx_mtv(Rw, gt, gl);
+    for (int r = 0; r < 3; r++) {
+      acc[r] = gt[r];
+      for (int c = 0; c < 3; c++) acc[3 + r * 3 + c] = gt[r] * tlp[f][c];
     }
-    g[32 + i] = v;
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+      acc[i] += __shfl_xor_sync(fmask, acc[i], 1);
+      acc[i] += __shfl_xor_sync(fmask, acc[i], 2);
+    }
+    // back through .double() (:666) into the float32 FK graph; fingers take turns so shared joints would accumulate
+    const float g32[3] = {(float)gl[0], (float)gl[1], (float)gl[2]};
+    if (V == 2) {
+      for (int r = 0; r < 3; r++) g[f * 3 + r] = gt[r];       // tip_pose is the leaf
+      __syncwarp(fmask);
+    } else {
+      const cdx_chain& ch = hand->finger[f];
+      const float* Jf = sJ[cl][f];
+      for (int turn = 0; turn < 4; turn++) {
+        if (turn == f)
+          for (int c = 0; c < ch.ndof; c++) {
+            const float gj = Jf[c] * g32[0] + Jf[CDX_MAX_CHAIN_DOF + c] * g32[1] + Jf[2 * CDX_MAX_CHAIN_DOF + c] * g32[2];
+            g[ch.dofs[c]] += (double)gj;
+          }
+        __syncwarp(fmask);
+      }
+    }
+    g[16 + f] = red[2];
+    for (int r = 0; r < 3; r++) g[20 + f * 3 + r] = red[6 + r];
+    for (int i = l; i < 6; i += 4) {
+      double v;
+      if (i < 3) v = acc[i] + gpalm_pm[i];
+      else {
+        const double* dR = i == 3 ? dR0 : (i == 4 ? dR1 : dR2);
+        v = 0.0;
+        for (int e = 0; e < 9; e++) v += acc[3 + e] * dR[e];
+      }
+      g[32 + i] = v;
+    }
   }
   __syncwarp(gmask);
-  if (l == 0) {
-    if (loss) loss[b] = total;
-    if (margin) for (int i = 0; i < 4; i++) margin[b * 4 + i] = sr[cl][1 + i];
-  }
-  if (grad) for (int i = l; i < NPAR; i += 4) grad[b * NPAR + i] = g[i];
+  if (S.w_ref != 0.0 && sub < nd) g[sub] += refn > 0.0 ? wsum * S.w_ref * (par[sub] - S.ref_q[sub]) / refn : 0.0;
+  __syncwarp(gmask);
+  if (sub == 0 && loss) loss[b] = total;
+  if (sub < 4 && margin) margin[b * 4 + sub] = sr[cl][1 + sub];
+  if (grad) for (int i = sub; i < NPAR; i += 16) grad[b * NPAR + i] = g[i];
   CDX_PG_TICK(10);
   if (!do_step) return;
   // ---- best-iterate tracking (:822-829): BEFORE the optimiser step, only for s > track_after; NaN never updates
   const bool better = it > prm.track_after && total < oval;
-  __syncwarp(gmask);                                    // every lane has read ovalue[b] before lane 0 overwrites it
-  if (V != 0) {
+  if (V != 0 && p == 0) {
     mring[(it & 1) * B * 4 + b * 4 + l] = sr[cl][1 + l];
     if (better && l == 0) latch[it & 1] = it;          // benign race: every writer stores the same value
   }
   if (better) {
-    if (l == 0) {
-      ovalue[b] = total;
-      for (int i = 0; i < 4; i++) omargin[b * 4 + i] = sr[cl][1 + i];
-    }
-    for (int i = l; i < NPAR; i += 4) {
+    if (sub == 0) ovalue[b] = total;
+    if (sub < 4) omargin[b * 4 + sub] = sr[cl][1 + sub];
+    for (int i = sub; i < NPAR; i += 16) {
       const double v = par[i];
       if (i < 16) { if (i < nd) oq[b * nd + i] = v; }
       else if (i < 20) ok[b * 4 + i - 16] = v;
@@ -356,14 +367,16 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   // ---- torch.optim.Adam (:796,:831): exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2 v + (1-b2) g^2;
   //      p -= (lr / (1-b1^t)) * m / (sqrt(v)/sqrt(1-b2^t) + eps);  then the clamps (:833-834)
   const double omb1 = 1.0 - prm.beta1, omb2 = 1.0 - prm.beta2;
-  // lane l owns parameters i = l + 4 j; unrolled over j the group of a parameter (q | k | T | palm xyz | palm rpy) is known
-  // at compile time except in the palm block, and the ten independent sqrt / divide chains overlap
 #pragma unroll
-  for (int j = 0; j < (NPAR + 3) / 4; j++) {
-    const int i = l + 4 * j;
+  for (int j = 0; j < (NPAR + 15) / 16; j++) {
+    const int i = sub + 16 * j;
     if (i >= NPAR) break;
-    const int grp = j < 4 ? 0 : (j == 4 ? 1 : (j < 8 ? 2 : (i < 35 ? 3 : 4)));
-    const bool upd = j < 4 ? i < nd : (j == 4 ? true : (j < 8 ? prm.optimize_target != 0 : prm.optimize_palm != 0));
+    int grp;
+    bool upd = true;
+    if (i < 16) { upd = i < nd; grp = 0; }
+    else if (i < 20) grp = 1;
+    else if (i < 32) { upd = prm.optimize_target != 0; grp = 2; }
+    else { upd = prm.optimize_palm != 0; grp = i < 35 ? 3 : 4; }
     double pv = par[i];
     if (upd && V == 0) {
       const double gi = g[i];
@@ -384,23 +397,23 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
       m2[b * NPAR + i] = v;
       pv = pv + (-prm.lr[grp] * gi) / (sqrt(v) + prm.eps);   // addcdiv_(g, avg, value=-lr): (value * g) / avg
     }
-    if (V == 2 && j < 3)    // tip_pose.clamp_(box) (:402)
+    if (V == 2 && i < 12)   // tip_pose.clamp_(box) (:402)
       pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[i / 3][i % 3]), (double)prm.box_hi[i / 3][i % 3]);
-    if (j == 4) pv = clamp_lo(pv, prm.compliance_min);
-    if (j >= 5 && j < 8 && V != 2) {   // target clamp: prob (:834) and Kin (:505); commented out at :404
+    if (i >= 16 && i < 20) pv = clamp_lo(pv, prm.compliance_min);
+    if (i >= 20 && i < 32 && V != 2) {   // target clamp: prob (:834) and Kin (:505); commented out at :404
       const int e = i - 20;
       pv = clamp_hi(clamp_lo(pv, (double)prm.box_lo[e / 3][e % 3]), (double)prm.box_hi[e / 3][e % 3]);
     }
     par[i] = pv;
-    if (j < 4) { if (i < nd) q[b * nd + i] = pv; }
-    else if (j == 4) k[b * 4 + i - 16] = pv;
-    else if (j < 8) T[b * 12 + i - 20] = pv;
+    if (i < 16) { if (i < nd) q[b * nd + i] = pv; }
+    else if (i < 20) k[b * 4 + i - 16] = pv;
+    else if (i < 32) T[b * 12 + i - 20] = pv;
     else palm[b * 6 + i - 32] = pv;
   }
   __syncwarp(gmask);
   CDX_PG_TICK(11);
   // ---- FK + GPIS query points of the NEW iterate (what pg_points_kernel does for the first iteration)
-  pg_emit_points<V>(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
+  if (p == 0) pg_emit_points<V>(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
   CDX_PG_TICK(12);
 }
 
@@ -721,7 +734,7 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   mark(1, st);
   CDX_CUDA(cudaStreamWaitEvent(st, s->ev_join, 0));
   mark(4, st);
-#define PG_STEP(V) pg_step_kernel<V><<<(unsigned)((B + CPB - 1) / CPB), CPB * 4, 0, st>>>(                                      \
+#define PG_STEP(V) pg_step_kernel<V><<<(unsigned)((B + CPB - 1) / CPB), CPB * 16, 0, st>>>(                                      \
       s->hand_dev, B, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd, s->mean9,   \
       s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,            \
       s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch)

@@ -17,8 +17,6 @@ raw = ctypes.CDLL(_lib.LIB_PATH)
 buf = (ctypes.c_longlong * 16)()
 assert raw.cdx_debug_pg_ticks(buf) == 0
 t = list(buf)
-names = [("start->row", 7, 8), ("row: normals+H", 0, 1), ("row: svd", 1, 2), ("row: R,t + forward costs", 2, 3),
-         ("row: per-finger reverse", 3, 4), ("row: t/Kabsch backward", 4, 5), ("row: H adjoint", 5, 6),
-         ("row end -> reduced", 6, 9), ("chain rule + grad", 9, 10), ("tracking + Adam", 10, 11), ("FK new iterate", 11, 12),
-         ("whole kernel", 7, 12)]
+names = [("start->row (loads, Euler, noise)", 7, 8), ("row (4 lanes per copy)", 8, 6), ("row end -> reduced over copies", 6, 9),
+         ("chain rule + grad", 9, 10), ("tracking + Adam", 10, 11), ("FK new iterate", 11, 12), ("whole kernel", 7, 12)]
 print(json.dumps({"B": B, "cycles": {n: t[b] - t[a] for n, a, b in names}}))
