@@ -148,6 +148,9 @@ constexpr int NGP = 16 + 16 + 48 + 48 + 9 + 27;   // dist | sd | gmu | gsd (up t
 __device__ __forceinline__ void pg_cp8(void* smem, const void* g) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g) : "memory");
 }
+__device__ __forceinline__ void pg_cp4(void* smem, const void* g) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g) : "memory");
+}
 __device__ __forceinline__ void pg_cp_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // One closure (+ optional optimiser step) per candidate, spread over a group of 16 lanes (p, f) = (lane >> 2, lane & 3):
@@ -176,6 +179,8 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   __shared__ double sq[CPB][NGP];       // GPIS outputs of this candidate
   __shared__ double sm1[CPB][NPAR], sm2[CPB][NPAR];
   __shared__ __align__(8) float sJ[CPB][4][3 * CDX_MAX_CHAIN_DOF];
+  constexpr int HW = (int)((sizeof(cdx_hand_dev) + 3) / 4);
+  __shared__ __align__(16) unsigned shand[CPB][HW];   // the group's own copy of the finger chains (FK walks them body by body)
   CDX_PG_TICK(7);
   const int sub = threadIdx.x & 15, p = sub >> 2, l = sub & 3, cl = threadIdx.x >> 4;
   const int64_t b = (int64_t)blockIdx.x * CPB + cl;
@@ -195,7 +200,10 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
     }
     if (do_step)
       for (int i = sub; i < NPAR; i += 16) { pg_cp8(&sm1[cl][i], m1 + b * NPAR + i); pg_cp8(&sm2[cl][i], m2 + b * NPAR + i); }
+    if (V != 2)
+      for (int i = sub; i < HW; i += 16) pg_cp4(&shand[cl][i], reinterpret_cast<const unsigned*>(hand) + i);
   }
+  const cdx_hand_dev* hs = V != 2 ? reinterpret_cast<const cdx_hand_dev*>(shand[cl]) : hand;
   double oval = 0.0, bc1 = 0.0, bc2s = 0.0;
   if (do_step) { oval = ovalue[b]; bc1 = adam_tab[2 * it]; bc2s = adam_tab[2 * it + 1]; }
   double* par = sp[cl];
@@ -315,7 +323,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
       for (int r = 0; r < 3; r++) g[f * 3 + r] = gt[r];       // tip_pose is the leaf
       __syncwarp(fmask);
     } else {
-      const cdx_chain& ch = hand->finger[f];
+      const cdx_chain& ch = hs->finger[f];
       const float* Jf = sJ[cl][f];
       for (int turn = 0; turn < 4; turn++) {
         if (turn == f)
@@ -413,7 +421,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int U, cdx_pg_s
   __syncwarp(gmask);
   CDX_PG_TICK(11);
   // ---- FK + GPIS query points of the NEW iterate (what pg_points_kernel does for the first iteration)
-  if (p == 0) pg_emit_points<V>(hand, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
+  if (p == 0) pg_emit_points<V>(hs, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
   CDX_PG_TICK(12);
 }
 
@@ -672,7 +680,10 @@ extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int
     s->U = U;
   }
   if (!s->side) {
-    CDX_CUDA(cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking));
+    // highest priority: the short mean-only query's CTAs are placed ahead of the extended query's whenever SMs free up
+    int prio_lo = 0, prio_hi = 0;
+    CDX_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CDX_CUDA(cudaStreamCreateWithPriority(&s->side, cudaStreamNonBlocking, prio_hi));
     CDX_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
     CDX_CUDA(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
   }
