@@ -125,10 +125,11 @@ def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks
                                     "FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0)),
                      "flop_per_query": flop_ext, "queries_per_launch": ext_queries,
                      "traffic": ncu_traffic("r01_ncu_pregrasp_v4_summary.json", "gpis_var_kernel") if B == 1024 and N == 196 else None,
-                     "dominant_by_time": "pg_step_kernel (latency-bound scalar FP64: Kabsch SVD, costs, analytic reverse pass, Adam, "
-                                         "float32 FK of the new iterate; ~2e4 flop per candidate) - see kernel_share",
+                     "dominant_by_time": "%s - see kernel_share; pg_step_kernel is latency-bound scalar FP64 (16 lanes per "
+                                         "candidate: Kabsch SVD, costs, analytic reverse pass, Adam, float32 FK of the new iterate; "
+                                         "~2e4 flop per candidate)" % max(share, key=share.get),
                      "kernel_ms_per_iteration": kernel_ms, "kernel_share": share,
-                     "note": "per-kernel times from one extra step with CUDA events around each launch (cdx_pregrasp_profile); the mean-only query runs on a forked stream, overlapped with the extended query; kernel_share is over the main-stream critical path",
+                     "note": "per-kernel times from one extra step with CUDA events around each launch (cdx_pregrasp_profile); the mean-only query runs on a forked stream, overlapped with the extended query; kernel_share is over the main-stream critical path. The profiled step runs the candidates as ONE group; the timed steps pipeline them in two groups on separate streams (cdx_pregrasp_run, CDX_PG_GROUPS), which is why ms_per_iteration is below the sum of these",
                      "fp64_pipes": pipes},
     }
 

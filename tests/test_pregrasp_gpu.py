@@ -107,6 +107,34 @@ def test_sharding_invariance(golden_dir):
     assert 4 <= idx < 8
 
 
+@pytest.mark.parametrize("groups", [2, 3, 4])
+def test_candidate_groups_are_bit_identical(groups, monkeypatch):
+    """cdx_pregrasp_run pipelines the candidates in groups on separate streams (default 2 from 768 candidates): whatever the
+    group count, every candidate's trajectory is the one it has in a single group."""
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path("mug_state"))
+    doc = load_hand("leap")
+    d = np.load(state_path("mug_state"))
+    B = 100   # not a multiple of the group size or of the 8 candidates a CTA holds
+    q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=7)
+
+    def run(G):
+        monkeypatch.setenv("CDX_PG_GROUPS", str(G))
+        opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                          palm_offset=palm, num_iters=30, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
+                                          com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True,
+                                          noise_seed=11)
+        res = [t.clone() for t in opt.optimize(q0.cuda(), T0.cuda(), k0.cuda(), 1.0, gp, verbose=False)]
+        return res + [opt.opt_value.clone()]
+
+    one = run(1)
+    many = run(groups)
+    for a, b in zip(one, many):
+        assert torch.equal(a, b)
+
+
 def test_distinct_pregrasp_coefficients_against_oracle(golden_dir):
     """coefficient rows that differ (U = 3 GPIS query blocks) + optimize_palm/target off, vs the oracle."""
     from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path, hand_path
