@@ -9,9 +9,13 @@
 #pragma once
 #include "cdx_pg_math.cuh"
 
-__device__ __forceinline__ void pg_gather4(unsigned fmask, double v, double* out) {
+// Every shuffle of the step kernel names the FULL warp: the kernel keeps all 32 lanes on one path up to its last shuffle
+// (idle copy quads and out-of-range candidate groups evaluate a duplicate row whose results are dropped).  With a run-time
+// partial mask each double shuffle compiled into a WARPSYNC collective region (~13 instructions, 30 % of the kernel's SASS).
+constexpr unsigned PG_FULL = 0xffffffffu;
+__device__ __forceinline__ void pg_gather4(unsigned /*fmask*/, double v, double* out) {
 #pragma unroll
-  for (int j = 0; j < 4; j++) out[j] = __shfl_sync(fmask, v, j, 4);
+  for (int j = 0; j < 4; j++) out[j] = __shfl_sync(PG_FULL, v, j, 4);
 }
 __device__ __forceinline__ double pg_sum4(unsigned fmask, double v) {   // ((v0 + v1) + v2) + v3, identical on the four lanes
   double g[4];

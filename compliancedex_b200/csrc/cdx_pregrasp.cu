@@ -167,8 +167,11 @@ __device__ __forceinline__ void pg_cp_wait() { asm volatile("cp.async.wait_all;"
 //   lane (0, f) then owns finger f: chain rule through the palm transform and the float32 FK Jacobian, and - when stepping -
 //   the FK and query points of the NEW iterate, so the next iteration needs no separate points launch;
 //   the 38 parameters are spread over the 16 lanes for best-iterate tracking (:822-829), Adam (:831) and the clamps (:833-834).
-template <int V>
-__global__ void __launch_bounds__(CPB * 16)
+// OCC = resident CTAs per SM the register allocation is sized for: 2 (255 registers) for launches of at most one wave, where
+// only a warp's own latency counts; 3 (168 registers) for larger launches, where the kernel is paced by how many of its
+// latency-bound warps an SM can hold.  Same source, same arithmetic (tests compare the two bit for bit).
+template <int V, int OCC>
+__global__ void __launch_bounds__(CPB * 16, OCC)
 pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int64_t b1, int U, cdx_pg_setup S,
                cdx_pregrasp_params prm,
                double* __restrict__ q, double* __restrict__ k, double* __restrict__ T, double* __restrict__ palm,
@@ -191,8 +194,12 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   __shared__ __align__(16) unsigned shand[CPB][HW];   // the group's own copy of the finger chains (FK walks them body by body)
   CDX_PG_TICK(7);
   const int sub = threadIdx.x & 15, p = sub >> 2, l = sub & 3, cl = threadIdx.x >> 4;
-  const int64_t b = b0 + (int64_t)blockIdx.x * CPB + cl;   // this launch covers candidates [b0, b1) of the B
-  if (b >= b1) return;                  // whole 16-lane groups leave together
+  const int64_t braw = b0 + (int64_t)blockIdx.x * CPB + cl;   // this launch covers candidates [b0, b1) of the B
+  if (braw - (cl & 1) >= b1) return;    // whole WARPS (two candidates) leave together
+  // a warp's second 16-lane group may lie past the end: it stays on the warp's path until the last shuffle (all shuffles
+  // name the full warp, see PG_FULL) evaluating a duplicate of the last candidate, writes nothing and leaves after that
+  const bool live = braw < b1;
+  const int64_t b = live ? braw : b1 - 1;
   const unsigned gmask = 0xFFFFu << ((threadIdx.x & 31) & 16);
   const unsigned fmask = 0xFu << ((threadIdx.x & 31) & ~3);
   const int nd = S.n_dofs;
@@ -233,14 +240,14 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   double refn = 0.0;
   if (S.w_ref != 0.0) {
     if (sub < nd) refn = (par[sub] - S.ref_q[sub]) * (par[sub] - S.ref_q[sub]);
-    refn += __shfl_xor_sync(gmask, refn, 4);
-    refn += __shfl_xor_sync(gmask, refn, 8);
-    refn += __shfl_xor_sync(gmask, refn, 1);
-    refn += __shfl_xor_sync(gmask, refn, 2);
+    refn += __shfl_xor_sync(PG_FULL, refn, 4);
+    refn += __shfl_xor_sync(PG_FULL, refn, 8);
+    refn += __shfl_xor_sync(PG_FULL, refn, 1);
+    refn += __shfl_xor_sync(PG_FULL, refn, 2);
     refn = sqrt(refn);
   }
   // Kin / GPIS variants: the margin of the previous iteration becomes the latched opt_margin if anything improved then
-  if (V != 0 && do_step && it > 0 && latch[(it - 1) & 1] == it - 1 && p == 0) {
+  if (V != 0 && live && do_step && it > 0 && latch[(it - 1) & 1] == it - 1 && p == 0) {
     latched[b * 4 + l] = mring[((it - 1) & 1) * B * 4 + b * 4 + l];
     if (b == 0 && l == 0) latch[2] = it - 1;
   }
@@ -249,14 +256,16 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   double wsum = 0.0;
   for (int c = 0; c < S.P; c++) wsum += S.weight[c];
   // noise[9] of copy p (replaces torch.rand_like(H), :61): lane f draws elements f, f+4, f+8 and the four lanes exchange
+  // lane quads p >= P have no copy of their own: they evaluate copy P-1 again (results dropped) so that the warp stays converged
+  const int pc = p < S.P ? p : S.P - 1;
   double noise[9];
   {
     const int64_t gb = prm.env_offset + b;
     double mine[3];
 #pragma unroll
-    for (int j = 0; j < 3; j++) mine[j] = (l + 4 * j < 9) ? cdx_kabsch_noise(prm.noise_seed, it, p, gb, l + 4 * j) : 0.0;
+    for (int j = 0; j < 3; j++) mine[j] = (l + 4 * j < 9) ? cdx_kabsch_noise(prm.noise_seed, it, pc, gb, l + 4 * j) : 0.0;
 #pragma unroll
-    for (int e = 0; e < 9; e++) noise[e] = __shfl_sync(fmask, mine[e >> 2], e & 3, 4);
+    for (int e = 0; e < 9; e++) noise[e] = __shfl_sync(PG_FULL, mine[e >> 2], e & 3, 4);
   }
   pg_cp_wait();
   __syncwarp(gmask);                    // the group's staged GPIS outputs are visible to its sixteen lanes
@@ -264,20 +273,20 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   double red[9];                        // total | margin_f | gk_f | gtips_f 3 | gT_f 3
 #pragma unroll
   for (int i = 0; i < 9; i++) red[i] = 0.0;
-  if (p < S.P) {
-    const int u = S.uniq[p];
+  {
+    const int u = S.uniq[pc];
     double a[4][3], lossp, mg, ga[3], gTr[3], gkr;
 #pragma unroll
     for (int f = 0; f < 4; f++)
-      for (int r = 0; r < 3; r++) a[f][r] = V ? tips[f][r] : Tp[f][r] + S.coeff[p][f] * (tips[f][r] - Tp[f][r]);
+      for (int r = 0; r < 3; r++) a[f][r] = V ? tips[f][r] : Tp[f][r] + S.coeff[pc][f] * (tips[f][r] - Tp[f][r]);
     const double* gq = sq[cl];
     CDX_PG_TICK(8);
     cdx_pg_row_coop(l, fmask, a, Tp, par + 16, gq + u * 4, gq + 16 + u * 4, reinterpret_cast<const double (*)[3]>(gq + 32 + u * 12),
                     reinterpret_cast<const double (*)[3]>(gq + 80 + u * 12), m9, reinterpret_cast<const double (*)[3]>(g9), noise,
                     S.C, lossp, mg, ga, gTr, gkr);
     CDX_PG_TICK(6);
-    const double wp = S.weight[p];
-    const double c = S.coeff[p][l];
+    const double wp = S.weight[pc];
+    const double c = S.coeff[pc][l];
     red[0] = wp * (lossp + S.w_ref * refn);
     red[1] = wp * mg;
     red[2] = wp * gkr;
@@ -285,12 +294,14 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
       red[3 + r] = wp * c * ga[r];
       red[6 + r] = wp * ((1.0 - c) * ga[r] + gTr[r]);
     }
+    if (p >= S.P)
+      for (int i = 0; i < 9; i++) red[i] = 0.0;
   }
 #pragma unroll
   for (int i = 0; i < 9; i++) {         // over the copies: (p0 + p1) + (p2 + p3)
     double v = red[i];
-    v += __shfl_xor_sync(gmask, v, 4);
-    v += __shfl_xor_sync(gmask, v, 8);
+    v += __shfl_xor_sync(PG_FULL, v, 4);
+    v += __shfl_xor_sync(PG_FULL, v, 8);
     red[i] = v;
   }
   if (p == 0) {
@@ -312,19 +323,22 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   }
   const int f = l;
   double* g = sg[cl];
-  if (p == 0) {
-    double gt[3], gl[3], acc[12];
-    for (int r = 0; r < 3; r++) gt[r] = red[3 + r] - S.w_pre * g9[(4 + f) * 3 + r];
-    cdx_mtv(Rw, gt, gl);
-    for (int r = 0; r < 3; r++) {
-      acc[r] = gt[r];
-      for (int c = 0; c < 3; c++) acc[3 + r * 3 + c] = gt[r] * tlp[f][c];
-    }
+  // the reduced values are identical on the four copy quads, so every lane forms the palm sums (the last shuffles of the
+  // kernel: all 32 lanes take part); only the lanes of p == 0 go on
+  double gt[3], gl[3], acc[12];
+  for (int r = 0; r < 3; r++) gt[r] = red[3 + r] - S.w_pre * g9[(4 + f) * 3 + r];
+  cdx_mtv(Rw, gt, gl);
+  for (int r = 0; r < 3; r++) {
+    acc[r] = gt[r];
+    for (int c = 0; c < 3; c++) acc[3 + r * 3 + c] = gt[r] * tlp[f][c];
+  }
 #pragma unroll
-    for (int i = 0; i < 12; i++) {
-      acc[i] += __shfl_xor_sync(fmask, acc[i], 1);
-      acc[i] += __shfl_xor_sync(fmask, acc[i], 2);
-    }
+  for (int i = 0; i < 12; i++) {
+    acc[i] += __shfl_xor_sync(PG_FULL, acc[i], 1);
+    acc[i] += __shfl_xor_sync(PG_FULL, acc[i], 2);
+  }
+  if (!live) return;                    // a group past the end has served the warp's shuffles and writes nothing
+  if (p == 0) {
     // back through .double() (:666) into the float32 FK graph; fingers take turns so shared joints would accumulate
     const float g32[3] = {(float)gl[0], (float)gl[1], (float)gl[2]};
     if (V == 2) {
@@ -771,12 +785,16 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   mark(1, st);
   CDX_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
   mark(4, st);
-#define PG_STEP(V) pg_step_kernel<V><<<(unsigned)((nb + CPB - 1) / CPB), CPB * 16, 0, st>>>(                                    \
+  int occ = (nb + CPB - 1) / CPB > 2 * (int64_t)ctx->sms ? 3 : 2;
+  if (const char* e = getenv("CDX_PG_OCC")) occ = atoi(e) == 3 ? 3 : 2;
+#define PG_STEP(V) PG_STEP_O(V, 2); else PG_STEP_O(V, 3)
+#define PG_STEP_O(V, O) if (occ == O) pg_step_kernel<V, O><<<(unsigned)((nb + CPB - 1) / CPB), CPB * 16, 0, st>>>(                                  \
       s->hand_dev, B, b0, b1, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd,      \
       s->mean9, s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,   \
       s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch)
-  if (s->setup.variant == 0) PG_STEP(0); else if (s->setup.variant == 1) PG_STEP(1); else PG_STEP(2);
+  if (s->setup.variant == 0) { PG_STEP(0); } else if (s->setup.variant == 1) { PG_STEP(1); } else { PG_STEP(2); }
 #undef PG_STEP
+#undef PG_STEP_O
   CDX_CHECK_LAUNCH(ctx);
   mark(5, st);
   if (prof)

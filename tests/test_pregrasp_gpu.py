@@ -135,6 +135,34 @@ def test_candidate_groups_are_bit_identical(groups, monkeypatch):
         assert torch.equal(a, b)
 
 
+@pytest.mark.parametrize("B", [101, 2500])
+def test_step_kernel_occupancy_variants_are_bit_identical(B, monkeypatch):
+    """pg_step_kernel is compiled twice (2 resident CTAs per SM / 255 registers for launches of one wave, 3 / 168 registers
+    for larger ones; CDX_PG_OCC forces one): same arithmetic, so the choice - which depends on the launch size, i.e. on the
+    shard - never shows in the results.  B = 101 also has a warp whose second candidate lies past the end of the batch."""
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path("mug_state"))
+    doc = load_hand("leap")
+    d = np.load(state_path("mug_state"))
+    q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=9)
+
+    def run(occ):
+        monkeypatch.setenv("CDX_PG_OCC", str(occ))
+        opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                          palm_offset=palm, num_iters=25, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
+                                          com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True,
+                                          noise_seed=5)
+        res = [t.clone() for t in opt.optimize(q0.cuda(), T0.cuda(), k0.cuda(), 1.0, gp, verbose=False)]
+        return res + [opt.opt_value.clone()]
+
+    two = run(2)
+    three = run(3)
+    for a, b in zip(two, three):
+        assert torch.equal(a, b)
+
+
 def test_distinct_pregrasp_coefficients_against_oracle(golden_dir):
     """coefficient rows that differ (U = 3 GPIS query blocks) + optimize_palm/target off, vs the oracle."""
     from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path, hand_path
