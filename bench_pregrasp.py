@@ -1,173 +1,192 @@
-"""bench.py's pregrasp workload (BASELINE.json configs[1]): ProbabilisticGraspOptimizer, Leap hand on the mug GPIS,
-1,024 candidates x 200 iterations per GPU.  One "step" = one whole optimisation (init + 200 iterations + arg-min).
-Weak scaling: every rank optimises its own 1,024 candidates (global candidate index = rank * 1024 + local), the only
-cross-rank traffic is the final 16-byte all-gather for the arg-min."""
+"""bench.py's pregrasp workloads: ProbabilisticGraspOptimizer.optimize through the drop-in class.
+  pregrasp_c2 (BASELINE.json configs[1]): Leap hand on the mug GPIS, 1,024 candidates x 200 iterations per GPU (weak scaling).
+  pregrasp_c5 (configs[4]): Allegro hand on the hammer (or lego / coffeebottle) GPIS, 65,536 candidates x 500 iterations in
+                            TOTAL, split over the ranks by contiguous ranges (strong scaling), NCCL arg-min at the end.
+One "step" = one whole optimisation (init + all iterations + arg-min).  The only cross-rank traffic is the final 16-byte
+all-gather for the arg-min; candidate b of the global batch is the same candidate for every rank count."""
 import ctypes
-import json
 import os
 import time
 
 import numpy as np
 import torch
 
+from bench_common import measured_peaks, ncu_traffic, pipe_peaks, reference_kind, timed
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 METRIC = "pregrasp candidate-iters/sec"
 
 
-def _workload_name(B, iters, world, hand="leap", obj="mug", N=196):
-    tag = "pregrasp_c2" if (hand, obj) == ("leap", "mug") else "pregrasp_c5_shape"
-    return ("%s: ProbabilisticGraspOptimizer (optimize_target, optimize_palm), %s hand on the %s GPIS state "
-            "(N=%d), %d candidates x %d iterations per GPU, %d GPU(s)" % (tag, hand.capitalize(), obj, N, B, iters, world))
+def workload_name(tag, hand, obj, N, total, iters, world, weak):
+    split = "%d candidates per GPU" % total if weak else "%d candidates in total split over the GPUs" % total
+    return ("%s: ProbabilisticGraspOptimizer (optimize_target, optimize_palm), %s hand on the %s GPIS state (N=%d), %s x %d "
+            "iterations" % (tag, hand.capitalize(), obj, N, split, iters))
 
 
-def _make(rank, B, iters, device, hand="leap", obj="mug"):
-    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+def _candidates(hand, obj, total):
+    from compliancedex_b200 import load_hand, state_path
     from compliancedex_b200.synthetic import surface_center, synthetic_candidates
-    gp = GPIS(0.08, 1.0)
-    gp.load_state_data(state_path(f"{obj}_state"), device=device)
     doc = load_hand(hand)
     d = np.load(state_path(f"{obj}_state"))
-    center = surface_center(d["X1"], d["y1"])
-    q0, T0, k0, palm = synthetic_candidates(doc, B, center, seed=100 + rank)
-    opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
-                                      palm_offset=palm, num_iters=iters, optimize_target=True, ref_q=doc["ref_q"],
-                                      mass=0.1, com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True,
-                                      device=device, noise_seed=2024, env_offset=rank * B)
-    return gp, opt, q0, T0, k0, palm, int(d["X1"].shape[0])
+    q0, T0, k0, palm = synthetic_candidates(doc, total, surface_center(d["X1"], d["y1"]), seed=100)
+    return doc, q0, T0, k0, palm, int(d["X1"].shape[0])
 
 
-def run_bench_c2(args, rank, world, local, ClockSampler, barrier, max_over_ranks, fp64_pipe_peaks, measured_peaks,
-                 ncu_traffic=lambda *a: None):
-    from compliancedex_b200 import _lib
-    from compliancedex_b200.distributed import global_argmin
+def run_pregrasp(args, rank, world, local, tag):
+    """tag 'pregrasp_c2': every rank optimises `--candidates` candidates of its own (global index rank * B + local);
+    tag 'pregrasp_c5': `--c5-candidates` candidates in total, rank r takes the r-th contiguous range."""
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, _lib, state_path
+    from compliancedex_b200.distributed import global_argmin, shard_range
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    B, iters = args.candidates, args.iters
-    gp, opt, q0, T0, k0, palm, N = _make(rank, B, iters, dev, args.hand, args.object)
+    weak = tag == "pregrasp_c2"
+    if weak:
+        hand, obj, iters, total = args.hand, args.object, args.iters, args.candidates * world
+        lo, hi = rank * args.candidates, (rank + 1) * args.candidates
+    else:
+        hand, obj, iters, total = "allegro", args.c5_object, args.c5_iters, args.c5_candidates
+        lo, hi = shard_range(total, rank, world)
+    doc, q0, T0, k0, palm, N = _candidates(hand, obj, total)
+    q0, T0, k0, palm = q0[lo:hi].contiguous(), T0[lo:hi].contiguous(), k0[lo:hi].contiguous(), palm[lo:hi].copy()
+    B = hi - lo
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path(f"{obj}_state"), device=dev)
+    opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                      palm_offset=palm, num_iters=iters, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
+                                      com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True, device=dev,
+                                      noise_seed=2024, env_offset=lo)
     lib = _lib.load()
     q0d, T0d, k0d = q0.to(dev), T0.to(dev), k0.to(dev)
+    best = [None]
 
     def step():
         opt._init(q0d, T0d, k0d, 1, gp)
         opt.step(iters)
-        return global_argmin(opt, world)
+        best[0] = global_argmin(opt, world)
 
     for _ in range(args.warmup):
-        best = step()
-    sampler = ClockSampler(local)
+        step()
     l0 = lib.cdx_launch_count(gp._ctx)
-    barrier(world)
-    if rank == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        best = step()
-    e1.record()
-    barrier(world)
-    ms = max_over_ranks(e0.elapsed_time(e1), world)
-    clocks = sampler.stop() if rank == 0 else None
+    ms_step, clocks = timed(step, args.steps, world, rank, local)
     launches = lib.cdx_launch_count(gp._ctx) - l0
+    nan_ci, nan_first = opt.nan_count()
 
     # e2e: the public call with HOST tensors (pinned): H2D of the candidates, D2H of the 5-tuple + arg-min
     hq, hT, hk = q0.pin_memory(), T0.pin_memory(), k0.pin_memory()
-    outs = None
 
     def step_e2e():
         res = opt.optimize(hq, hT, hk, 1, gp, verbose=False)
-        b = global_argmin(opt, world)
-        return [t.cpu() for t in res], b
+        best[0] = global_argmin(opt, world)
+        return [t.cpu() for t in res]
 
     step_e2e()
-    barrier(world)
-    e0.record()
-    for _ in range(args.steps):
-        outs, best = step_e2e()
-    e1.record()
-    barrier(world)
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world)
+    ms_e2e, _ = timed(step_e2e, args.steps, world, rank, local, sample_clocks=False)
 
-    # one more step with per-kernel CUDA events (cdx_pregrasp_profile) for the roofline of the dominant kernel
+    # one more optimisation with CUDA events around every launch (cdx_pregrasp_profile): direct launches in the SAME candidate
+    # groups and launch shapes as the timed loop (the timed loop replays them from a CUDA graph)
     _lib.check(lib.cdx_pregrasp_profile(gp._ctx, 1))
-    step()
+    piters = min(iters, 100)
+    opt._init(q0d, T0d, k0d, 1, gp)
+    opt.step(piters)
     kms = (ctypes.c_double * 4)()
-    nit = ctypes.c_int()
-    _lib.check(lib.cdx_pregrasp_profile_read(gp._ctx, kms, ctypes.byref(nit), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    nl = ctypes.c_int()
+    _lib.check(lib.cdx_pregrasp_profile_read(gp._ctx, kms, ctypes.byref(nl), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
     _lib.check(lib.cdx_pregrasp_profile(gp._ctx, 0))
     if rank != 0:
         return None
-    kernel_ms = {k: kms[i] / max(1, nit.value) for i, k in enumerate(["wait_for_mean_query", "gpis_var_ext", "gpis_mean_overlapped", "pg_step"])}
-    ms_step = ms / args.steps
-    total_units = B * world * iters
-    pipes = fp64_pipe_peaks()
+    groups = max(1, nl.value // piters)
+    per_launch = {k: kms[i] / max(1, nl.value) for i, k in enumerate(["wait_for_mean_query", "gpis_var_ext", "gpis_mean_overlapped", "pg_step"])}
+    total_units = total * iters
+    pipes = pipe_peaks()
     peaks, src = measured_peaks()
-    U = 1                                                          # identical coefficient rows share one query block
-    ext_queries = B * U * 4
+    ext_queries = (B + groups - 1) // groups * 4                  # per launch: one group's candidates x 4 contact points (U = 1)
     flop_ext = 2 * N * N + 34 * N                                  # extended query {mean, grad, std, grad std}
-    achieved = flop_ext * ext_queries / (kernel_ms["gpis_var_ext"] * 1e-3) / 1e12
+    achieved = flop_ext * ext_queries / (per_launch["gpis_var_ext"] * 1e-3) / 1e12
     peak = pipes.get("dmma_m8n8k4_tflops")
-    crit = kernel_ms["gpis_var_ext"] + kernel_ms["wait_for_mean_query"] + kernel_ms["pg_step"]   # main-stream critical path
-    share = {k: kernel_ms[k] / crit for k in ("gpis_var_ext", "wait_for_mean_query", "pg_step")}
+    crit = per_launch["gpis_var_ext"] + per_launch["wait_for_mean_query"] + per_launch["pg_step"]   # one group's critical path
+    share = {k: per_launch[k] / crit for k in ("gpis_var_ext", "wait_for_mean_query", "pg_step")}
+    ms_iter = ms_step / iters
     return {
         "metric": METRIC, "value": total_units / (ms_step * 1e-3), "unit": "candidate-iters/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": _workload_name(B, iters, world, args.hand, args.object, N), "ms_per_iteration": ms_step / iters,
-                   "l2_policy": "latency-bound loop: the 0.6 MB state (L, E11^-1) and the per-candidate buffers are re-used "
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(tag, hand, obj, N, args.candidates if weak else total, iters, world, weak),
+                   "candidates_per_gpu": B, "ms_per_iteration": ms_iter,
+                   "l2_policy": "latency-bound loop: the < 1.3 MB state (L^-1, E11^-1) and the per-candidate buffers are re-used "
                                 "every iteration by design (resident working set), no flush applies",
-                   "argmin": {"value": best[0], "global_index": best[1]}},
-        "e2e": {"value": total_units / (ms_e2e / args.steps * 1e-3), "unit": "candidate-iters/s",
+                   "argmin": {"value": best[0][0], "global_index": best[0][1]},
+                   "nan_candidate_iterations": nan_ci, "nan_first_iteration": nan_first,
+                   "loop": "CUDA graph of 50-iteration chunks, %d candidate group(s) on separate stream pairs" % groups},
+        "e2e": {"value": total_units / (ms_e2e * 1e-3), "unit": "candidate-iters/s",
                 "h2d_bytes_per_step": int(B * (16 + 12 + 4 + 6) * 8), "d2h_bytes_per_step": int(B * (16 + 4 + 12 + 6 + 4) * 8 + 16)},
         "gpu_launches": int(launches), "clocks": clocks,
-        "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,64,ext,32> (FP64 DMMA) inside the pregrasp iteration",
+        "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,ext> (FP64 DMMA) inside the pregrasp iteration",
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if peak else None,
                      "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json has no "
                                     "FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0)),
-                     "flop_per_query": flop_ext, "queries_per_launch": ext_queries,
-                     "traffic": ncu_traffic("r01_ncu_pregrasp_v4_summary.json", "gpis_var_kernel") if B == 1024 and N == 196 else None,
-                     "dominant_by_time": "%s - see kernel_share; pg_step_kernel is latency-bound scalar FP64 (16 lanes per "
-                                         "candidate: Kabsch SVD, costs, analytic reverse pass, Adam, float32 FK of the new iterate; "
-                                         "~2e4 flop per candidate)" % max(share, key=share.get),
-                     "kernel_ms_per_iteration": kernel_ms, "kernel_share": share,
-                     "note": "per-kernel times from one extra step with CUDA events around each launch (cdx_pregrasp_profile); the mean-only query runs on a forked stream, overlapped with the extended query; kernel_share is over the main-stream critical path. The profiled step runs the candidates as ONE group; the timed steps pipeline them in two groups on separate streams (cdx_pregrasp_run, CDX_PG_GROUPS), which is why ms_per_iteration is below the sum of these",
-                     "fp64_pipes": pipes},
+                     "flop_per_query": flop_ext, "queries_per_launch": ext_queries, "launch_groups": groups,
+                     "traffic": ncu_traffic(args.ncu_summary_pg, "gpis_var_kernel"),
+                     "kernel_ms_per_launch": per_launch, "kernel_share_of_group_critical_path": share,
+                     "iteration_ms_vs_sum_of_group_critical_paths": {"timed_loop": ms_iter, "sum": crit * groups},
+                     "note": "per-launch times from %d extra iterations with CUDA events around each launch, in the timed loop's own "
+                             "launch shape (%d group(s) of %d candidates, each walking its iterations on its own stream pair, so a "
+                             "group's launches overlap the other's); pg_step_kernel is latency-bound scalar FP64 (16 lanes per "
+                             "candidate)" % (piters, groups, (B + groups - 1) // groups)},
     }
 
 
-# ------------------------------------------------------------------------------------------ CPU side (oracle port)
-def cpu_pregrasp(B, iters, threads, seed=100):
-    """The reference's algorithm (oracle/pregrasp_oracle.py, a torch restatement of optimize_pregrasp.py:614-839 with the
-    reference's own per-call LU / inverse GPIS, kind "port": /root/reference cannot travel to the GPU box) on the host
-    cores: B candidates x iters iterations of the same workload.  -> candidate-iters/s, seconds"""
-    from compliancedex_b200 import hand_path, load_hand, state_path
-    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
-    from oracle.gpis_oracle import GPISOracle
-    from oracle.pregrasp_oracle import PregraspOracle
+# ------------------------------------------------------------------------------------------ CPU side (reference arm)
+def cpu_pregrasp(hand, obj, total, B, iters, threads, kind):
+    """The reference's own ProbabilisticGraspOptimizer.optimize (kind "reference", through oracle/ref_harness.py) or the oracle
+    port on the host cores: the first B candidates of the workload's batch for `iters` iterations.
+    -> candidate-iters/s, seconds"""
+    from compliancedex_b200 import hand_path, state_path
     torch.set_num_threads(threads)
-    go = GPISOracle(0.08, 1.0).load_npz(state_path("mug_state"))
-    doc = load_hand("leap")
-    d = np.load(state_path("mug_state"))
-    q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=seed)
-    o = PregraspOracle(hand_path("leap"), palm, iters, mass=0.1, noise_seed=2024)
-    t0 = time.perf_counter()
-    o.optimize(q0, T0, k0, 1, go)
-    dt = time.perf_counter() - t0
-    return B * iters / dt, dt
+    doc, q0, T0, k0, palm, N = _candidates(hand, obj, total)
+    q0, T0, k0, palm = q0[:B].clone(), T0[:B].clone(), k0[:B].clone(), palm[:B].copy()
+    if kind == "reference":
+        import contextlib
+        import io
+        from oracle import ref_harness as rh
+        g = rh.load_gpis(f"{obj}_state")
+        ropt, _ = rh.make_prob_optimizer(hand, palm, iters, mass=0.1, com=[0.0, 0.0, 0.0])
+        t0 = time.perf_counter()
+        with contextlib.redirect_stdout(io.StringIO()), rh.pinned_kabsch_noise(2024):
+            ropt.optimize(q0, T0, k0, 1, g)
+        dt = time.perf_counter() - t0
+    else:
+        from oracle.gpis_oracle import GPISOracle
+        from oracle.pregrasp_oracle import PregraspOracle
+        go = GPISOracle(0.08, 1.0).load_npz(state_path(f"{obj}_state"))
+        o = PregraspOracle(hand_path(hand), palm, iters, mass=0.1, noise_seed=2024)
+        t0 = time.perf_counter()
+        o.optimize(q0, T0, k0, 1, go)
+        dt = time.perf_counter() - t0
+    return B * iters / dt, dt, N
 
 
-def run_reference_c2(args, threads, world):
-    Bs, its = 64, 10
+def ref_pregrasp(args, threads, world, tag):
+    import warnings
+    warnings.filterwarnings("ignore")
+    kind = reference_kind()
+    weak = tag == "pregrasp_c2"
+    if weak:
+        hand, obj, iters, total, Bs, its = args.hand, args.object, args.iters, args.candidates, 64, 10
+    else:
+        hand, obj, iters, total, Bs, its = "allegro", args.c5_object, args.c5_iters, args.c5_candidates, 64, 6
     vals = []
     for i in range(args.warmup + args.steps):
-        v, dt = cpu_pregrasp(Bs, its, threads)
+        v, dt, N = cpu_pregrasp(hand, obj, total, Bs, its, threads, kind)
         if i >= args.warmup:
             vals.append((v, dt))
     v = float(np.mean([a for a, _ in vals]))
     ms = float(np.mean([b for _, b in vals])) * 1e3
-    sample = "each step = %d candidates x %d iterations of the same workload (oracle port of the reference, torch CPU)" % (Bs, its)
+    sample = ("each step = the first %d candidates x %d iterations of the same batch through %s on the host cores (%.1f s)"
+              % (Bs, its, "the reference's own optimize_pregrasp.py / gpis.py / FK package" if kind == "reference"
+                 else "the oracle port of the reference (torch CPU)", ms * 1e-3))
     return {"impl": "reference", "metric": METRIC, "value": v, "unit": "candidate-iters/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": _workload_name(args.candidates, args.iters, world), "sample": sample},
-            "cpu_baseline": {"value": v, "unit": "candidate-iters/s", "cores": threads, "kind": "port", "sample": sample},
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(tag, hand, obj, N, total, iters, world, weak), "sample": sample},
+            "cpu_baseline": {"value": v, "unit": "candidate-iters/s", "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "candidate-iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}

@@ -2,9 +2,10 @@
 missing or fails to load, importing the compute classes raises."""
 import ctypes
 import os
+import weakref
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("CDX_LIB") or os.path.join(_HERE, "libcdx.so")   # CDX_LIB: developer override (kernel experiments)
+LIB_PATH = os.path.join(_HERE, "libcdx.so")
 
 c_void_p, c_int, c_i64, c_double, c_u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double, ctypes.c_uint64
 
@@ -46,6 +47,8 @@ SIGNATURES = {
     "cdx_create": (c_int, [c_int, ctypes.POINTER(c_void_p)]),
     "cdx_destroy": (c_int, [c_void_p]),
     "cdx_gpis_fit": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_i64, c_double, c_int, c_double, c_void_p]),
+    "cdx_gpis_fit_profile": (c_int, [c_void_p, c_int]),
+    "cdx_gpis_fit_profile_read": (c_int, [c_void_p, c_void_p, c_void_p]),
     "cdx_gpis_set_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_double, c_i64, c_int, c_double, c_void_p]),
     "cdx_gpis_get": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "cdx_gpis_info": (c_int, [c_void_p, ctypes.POINTER(c_i64), ctypes.POINTER(c_double), ctypes.POINTER(c_double),
@@ -64,10 +67,13 @@ SIGNATURES = {
     "cdx_collision_cost": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_init": (c_int, [c_void_p, ctypes.POINTER(PregraspParams), c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_run": (c_int, [c_void_p, c_int, c_void_p]),
-    "cdx_pregrasp_eval": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "cdx_pregrasp_results": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "cdx_pregrasp_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "cdx_pregrasp_latched_margin": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cdx_pregrasp_set_tuning": (c_int, [c_void_p, c_int, c_int, c_int]),
+    "cdx_pregrasp_nan_count": (c_int, [c_void_p, ctypes.POINTER(c_i64), ctypes.POINTER(c_int), c_void_p]),
+    "cdx_pregrasp_generation": (c_i64, [c_void_p, ctypes.POINTER(c_i64)]),
+    "cdx_pregrasp_eval": (c_int, [c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cdx_pregrasp_results": (c_int, [c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cdx_pregrasp_state": (c_int, [c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cdx_pregrasp_latched_margin": (c_int, [c_void_p, c_i64, c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_argmin": (c_int, [c_void_p, c_void_p, c_void_p]),
     "cdx_pregrasp_profile": (c_int, [c_void_p, c_int]),
     "cdx_pregrasp_profile_read": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_int), c_void_p]),
@@ -128,8 +134,21 @@ def context(device_index):
     return _contexts[device_index]
 
 
+class Context(ctypes.c_void_p):
+    """A cdx_ctx handle that is released with its last Python reference (cdx_destroy frees the factorised state -
+    4 Np^2 doubles, 0.5 GB at N = 4096 - the INT8 slices and the pregrasp buffers).  Passed wherever the C ABI takes
+    a cdx_ctx*."""
+
+    def close(self):
+        fin = getattr(self, "_finalizer", None)
+        if fin is not None:
+            fin()
+
+
 def new_context(device_index):
     lib = load()
-    h = c_void_p()
+    h = Context()
     check(lib.cdx_create(int(device_index), ctypes.byref(h)))
+    h._finalizer = weakref.finalize(h, lib.cdx_destroy, c_void_p(h.value))
+    h._finalizer.atexit = False          # at interpreter exit the driver reclaims everything; do not race its teardown
     return h

@@ -195,9 +195,14 @@ int gpis_reserve(cdx_ctx* ctx, int64_t N) {
   return CDX_OK;
 }
 
+static inline void fit_mark(cdx_gpis_state& g, int i, cudaStream_t st) {
+  if (g.fit_prof && g.fit_ev[i]) cudaEventRecord(g.fit_ev[i], st);
+}
+
 // factorise g.E11 (padded) -> L, U, P, alpha, Xa.  X1 is [N,3] device.
 int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
+  fit_mark(g, 1, st);
   const int Np = (int)g.Np, N = (int)g.N;
   const int64_t ld = Np;
   const size_t mat = sizeof(double) * (size_t)Np * (size_t)Np;
@@ -227,6 +232,7 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   dim3 g2((Np + 255) / 256, Np);
   zero_upper_kernel<<<g2, 256, 0, st>>>(g.L, Np);
   CDX_CHECK_LAUNCH(ctx);
+  fit_mark(g, 2, st);
   // U = L^-1 by doubling: inv([L11 0; L21 L22]) = [U11 0; -U22 L21 U11, U22]; P is scratch for T = L21 U11
   for (int s = 64; s < Np; s *= 2) {
     int npairs = (Np + 2 * s - 1) / (2 * s);
@@ -249,11 +255,13 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
       if (r > 0) { int rc = level(nfull, 1, r); if (rc) return rc; }
     }
   }
+  fit_mark(g, 3, st);
   // P = U^T U (lower tiles, k >= m0), mirrored
   int rc = cdx_dgemm(ctx, true, true, Np, Np, Np, 1.0, g.U, ld, g.U, ld, 0.0, g.P, ld, true, 3, 1, 0, 0, 0, st);
   if (rc) return rc;
   mirror_lower_kernel<<<g2, 256, 0, st>>>(g.P, Np);
   CDX_CHECK_LAUNCH(ctx);
+  fit_mark(g, 4, st);
   // alpha = U^T (U y1)
   trmv_lower_kernel<<<(Np + 7) / 8, 256, 0, st>>>(g.U, Np, g.y1, g.tmp);
   CDX_CHECK_LAUNCH(ctx);
@@ -264,10 +272,34 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   cdx_kparams kp = cdx_make_kparams(g);
   g.prior = g.kernel == CDX_KERNEL_TPS ? kp.R3 : (g.kernel == CDX_KERNEL_RBF ? 1.0 : 0.3 + 0.7 * kp.R3);
   g.ready = true;
+  fit_mark(g, 5, st);
   return CDX_OK;
 }
 
 }  // namespace
+
+extern "C" int cdx_gpis_fit_profile(cdx_ctx* ctx, int enable) {
+  if (!ctx) { cdx_set_error("cdx_gpis_fit_profile: NULL context"); return CDX_ERR_ARG; }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  cdx_gpis_state& g = ctx->g;
+  if (enable)
+    for (int i = 0; i < 6; i++)
+      if (!g.fit_ev[i]) CDX_CUDA(cudaEventCreate(&g.fit_ev[i]));
+  g.fit_prof = enable != 0;
+  return CDX_OK;
+}
+
+extern "C" int cdx_gpis_fit_profile_read(cdx_ctx* ctx, double* ms_out5, void* stream) {
+  if (!ctx || !ms_out5 || !ctx->g.fit_ev[0]) { cdx_set_error("cdx_gpis_fit_profile_read: enable profiling and fit first"); return CDX_ERR_STATE; }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  CDX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  for (int i = 0; i < 5; i++) {
+    float ms = 0.f;
+    CDX_CUDA(cudaEventElapsedTime(&ms, ctx->g.fit_ev[i], ctx->g.fit_ev[i + 1]));
+    ms_out5[i] = (double)ms;
+  }
+  return CDX_OK;
+}
 
 extern "C" int cdx_create(int device, cdx_ctx** out) {
   if (!out) { cdx_set_error("cdx_create: null out"); return CDX_ERR_ARG; }
@@ -300,6 +332,7 @@ extern "C" int cdx_destroy(cdx_ctx* ctx) {
   cudaFree(g.Xa); cudaFree(g.y1); cudaFree(g.E11); cudaFree(g.L); cudaFree(g.U); cudaFree(g.P);
   cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.dR2); cudaFree(g.flag);
   cudaFree(ctx->hx); cudaFree(ctx->hout);
+  for (int i = 0; i < 6; i++) if (g.fit_ev[i]) cudaEventDestroy(g.fit_ev[i]);
   cdx_i8_free(ctx);
   cdx_pregrasp_free(ctx);
   cdx_sdf_free(ctx);
@@ -311,6 +344,7 @@ extern "C" int64_t cdx_launch_count(cdx_ctx* ctx) { return ctx ? ctx->launches :
 
 extern "C" int cdx_gpis_fit(cdx_ctx* ctx, const double* X1, const double* y1, const double* noise, double noise_scalar,
                             int64_t N, double bias, int kernel, double sigma, void* stream) {
+  CDX_NVTX("cdx_gpis_fit");
   if (!ctx || !X1 || !y1 || N <= 0 || kernel < 0 || kernel > 2) { cdx_set_error("cdx_gpis_fit: bad argument"); return CDX_ERR_ARG; }
   cudaStream_t st = (cudaStream_t)stream;
   CDX_CUDA(cudaSetDevice(ctx->device));
@@ -319,6 +353,7 @@ extern "C" int cdx_gpis_fit(cdx_ctx* ctx, const double* X1, const double* y1, co
   cdx_gpis_state& g = ctx->g;
   g.kernel = kernel; g.sigma = sigma; g.bias = bias; g.R = 0.0;
   const int Np = (int)g.Np;
+  fit_mark(g, 0, st);
   if (kernel != CDX_KERNEL_RBF) {  // gpis.py:35-36
     CDX_CUDA(cudaMemsetAsync(g.dR2, 0, sizeof(double), st));
     pairmax_kernel<<<((int)N + 127) / 128, 128, 0, st>>>(X1, (int)N, (unsigned long long*)g.dR2);
@@ -341,6 +376,7 @@ extern "C" int cdx_gpis_fit(cdx_ctx* ctx, const double* X1, const double* y1, co
 
 extern "C" int cdx_gpis_set_state(cdx_ctx* ctx, const double* X1, const double* y1, const double* E11, double R,
                                   double bias, int64_t N, int kernel, double sigma, void* stream) {
+  CDX_NVTX("cdx_gpis_set_state");
   if (!ctx || !X1 || !y1 || !E11 || N <= 0 || kernel < 0 || kernel > 2) { cdx_set_error("cdx_gpis_set_state: bad argument"); return CDX_ERR_ARG; }
   cudaStream_t st = (cudaStream_t)stream;
   CDX_CUDA(cudaSetDevice(ctx->device));
@@ -349,6 +385,7 @@ extern "C" int cdx_gpis_set_state(cdx_ctx* ctx, const double* X1, const double* 
   cdx_gpis_state& g = ctx->g;
   g.kernel = kernel; g.sigma = sigma; g.bias = bias; g.R = R;
   const int Np = (int)g.Np;
+  fit_mark(g, 0, st);
   sub_bias_kernel<<<(Np + 255) / 256, 256, 0, st>>>(y1, (int)N, Np, 0.0, g.y1);
   CDX_CHECK_LAUNCH(ctx);
   dim3 g2((Np + 255) / 256, Np);
@@ -373,6 +410,7 @@ extern "C" int cdx_gpis_info(cdx_ctx* ctx, int64_t* N, double* R, double* bias, 
 }
 
 extern "C" int cdx_gpis_get(cdx_ctx* ctx, int which, double* out, void* stream) {
+  CDX_NVTX("cdx_gpis_get");
   if (!ctx || !ctx->g.ready || !out) { cdx_set_error("cdx_gpis_get: no fitted state / null out"); return CDX_ERR_STATE; }
   cudaStream_t st = (cudaStream_t)stream;
   CDX_CUDA(cudaSetDevice(ctx->device));

@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(256) grid_scatter_kernel(const float* __restri
 }  // namespace
 
 extern "C" int cdx_grid_surface(cdx_ctx* ctx, const float* mean, int steps, long long* idx, long long* count, void* stream) {
+  CDX_NVTX("cdx_grid_surface");
   if (!ctx || !mean || !idx || !count || steps < 1 || steps > 1290) {
     cdx_set_error("cdx_grid_surface: bad argument (1 <= steps <= 1290)");
     return CDX_ERR_ARG;

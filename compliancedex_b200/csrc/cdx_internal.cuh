@@ -4,7 +4,17 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <vector>
 #include "../../include/cdx.h"
+
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: a no-op unless a profiler injects its library
+
+// NVTX range covering a C-ABI entry point (tracing hooks at the boundary)
+struct cdx_nvtx_range {
+  explicit cdx_nvtx_range(const char* name) { nvtxRangePushA(name); }
+  ~cdx_nvtx_range() { nvtxRangePop(); }
+};
+#define CDX_NVTX(name) cdx_nvtx_range cdx_nvtx_range_##__LINE__(name)
 
 #define CDX_MAX_BODIES 32
 #define CDX_NPAD 64  // matrices are padded to a multiple of this (identity on the padded diagonal)
@@ -65,6 +75,10 @@ struct cdx_gpis_state {
   int i8_S = 0;             // slices the copy was built with (0 = not built for the current state)
   size_t i8_cap = 0;        // bytes allocated for i8_B
   int64_t i8_np = 0;        // Np the small arrays were allocated for
+  // optional phase timing of the fit (cdx_gpis_fit_profile): events at the phase boundaries
+  bool fit_prof = false;
+  cudaEvent_t fit_ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t i8_ready = nullptr;  // recorded after the slices were built: queries on any other stream wait for it
   int var_mode = 0;         // cdx_gpis_set_var_mode: 0 auto, -1 always FP64 DMMA, 4/5/6 = INT8 slices whenever eligible
 };
 
@@ -82,7 +96,19 @@ struct cdx_ctx {
   cdx_sdf_state* sdf = nullptr;
   // scratch for host-pointer entry points
   double* hx = nullptr; double* hout = nullptr; int64_t hcap = 0;
+  // kernels whose dynamic shared-memory limit has been raised ON THIS DEVICE (the attribute is per device, one ctx per device)
+  std::vector<const void*> smem_attr_done;
 };
+
+template <class F>
+static inline int cdx_smem_attr(cdx_ctx* ctx, F* func, size_t bytes) {
+  const void* key = reinterpret_cast<const void*>(func);
+  for (const void* k : ctx->smem_attr_done)
+    if (k == key) return CDX_OK;
+  CDX_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  ctx->smem_attr_done.push_back(key);
+  return CDX_OK;
+}
 
 // covariance function and radial derivative factor:  k(d), c(d) with grad_x k = c * (x - xi)
 struct cdx_kparams {

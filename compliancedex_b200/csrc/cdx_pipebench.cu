@@ -1,6 +1,7 @@
 // Pipe-rate microbenchmarks for the FP64 units this path runs on (MEASURED_PEAKS.json has only HBM and bf16).
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/cdx_pipebench cdx_pipebench.cu
-// Prints one JSON object: DFMA TF/s, DMMA(m8n8k4) TF/s, both interleaved, FP32 FFMA TF/s, MUFU.RSQ rate.
+// Prints one JSON object: DFMA TF/s, DMMA(m8n8k4) TF/s, both interleaved, FP32 FFMA TF/s, MUFU.RSQ rate, and the
+// tcgen05.mma kind::i8 issue rate (TOP/s) for the operand shapes of gpis_std_i8_kernel.
 #include <cstdio>
 #include <cuda_runtime.h>
 
@@ -90,6 +91,83 @@ __global__ void __launch_bounds__(CAP) gen_kernel(const double* __restrict__ pts
   out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 
+// ---- tcgen05 kind::i8 issue rate (the roof of gpis_std_i8_kernel): one CTA per SM, one thread issues `count` MMAs of
+// M=128 x N x K=32 onto two alternating TMEM accumulators, operands constant in shared memory (SS) or A in tensor memory (TS)
+__device__ __forceinline__ unsigned pb_s32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned long long pb_desc(unsigned saddr, unsigned lbo, unsigned sbo) {
+  return (unsigned long long)((saddr >> 4) & 0x3FFFu) | ((unsigned long long)((lbo >> 4) & 0x3FFFu) << 16) |
+         ((unsigned long long)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
+}
+template <int N, bool TS>
+__global__ void __launch_bounds__(128, 1) i8_peak_kernel(int count, unsigned* out) {
+  extern __shared__ __align__(128) unsigned char pb_smem[];
+  __shared__ unsigned long long bar;
+  __shared__ unsigned tmem_slot;
+  const int t = threadIdx.x, warp = t >> 5;
+  for (int i = t; i < (128 * 32 + N * 32) / 4; i += 128) reinterpret_cast<unsigned*>(pb_smem)[i] = 0x01010101u * (i & 3);
+  if (t == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(pb_s32(&bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;\n" ::"r"(pb_s32(&tmem_slot)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
+  }
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+  const unsigned tmem = tmem_slot;
+  if (t == 0) {
+    const unsigned idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((unsigned)(N >> 3) << 17) | (8u << 24);
+    const unsigned long long da = pb_desc(pb_s32(pb_smem), 128 * 16, 128);
+    const unsigned long long db = pb_desc(pb_s32(pb_smem) + 128 * 32, N * 16, 128);
+    const int nacc = 512 / N >= 2 ? 2 : 1;
+    for (int i = 0; i < count; i++) {
+      const unsigned d = tmem + (unsigned)((i % nacc) * N);
+      if (TS)
+        asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %3, 0;\ntcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %4, {%5,%5,%5,%5}, p;\n}\n" ::"r"(d),
+                     "r"(tmem + 2u * N), "l"(db), "r"((unsigned)(i >= nacc)), "r"(idesc), "r"(0u) : "memory");
+      else
+        asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %3, 0;\ntcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %4, {%5,%5,%5,%5}, p;\n}\n" ::"r"(d),
+                     "l"(da), "l"(db), "r"((unsigned)(i >= nacc)), "r"(idesc), "r"(0u) : "memory");
+    }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(pb_s32(&bar)) : "memory");
+    asm volatile("{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n@p bra D_%=;\nbra W_%=;\nD_%=:\n}\n" ::"r"(pb_s32(&bar)) : "memory");
+    out[blockIdx.x] = count;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;\n" ::"r"(tmem));
+}
+
+template <int N, bool TS>
+static double run_i8(int count) {   // -> TOP/s (2 x multiply-adds) of the whole chip
+  int dev, sms;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  unsigned* out;
+  cudaMalloc(&out, sizeof(unsigned) * sms);
+  const size_t smem = 128 * 32 + N * 32;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  i8_peak_kernel<N, TS><<<sms, 128, smem>>>(count / 10, out);
+  if (cudaDeviceSynchronize() != cudaSuccess) { cudaGetLastError(); cudaFree(out); return 0.0; }
+  float best = 1e30f;
+  for (int r = 0; r < 5; r++) {
+    cudaEventRecord(e0);
+    i8_peak_kernel<N, TS><<<sms, 128, smem>>>(count, out);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (ms < best) best = ms;
+  }
+  cudaFree(out);
+  return 2.0 * 128.0 * N * 32.0 * (double)count * sms / ((double)best * 1e-3) * 1e-12;
+}
+
 template <int CAP>
 static double run_gen(int stages, int blocks_per_sm) {   // -> cycles-equivalent: seconds per (SM, stage of 128x64 pairs)
   int dev, sms;
@@ -155,14 +233,18 @@ int main() {
   double t_dfma = run<0>(iters, 4), t_dmma = run<1>(iters, 4), t_both = run<2>(iters, 4), t_ffma = run<3>(iters, 4),
          t_rsq = run<4>(iters, 4);
   const double g1 = run_gen<512>(20000, 1), g2 = run_gen<512>(20000, 2), g3 = run_gen<704>(20000, 1);
+  const double i8_ss256 = run_i8<256, false>(40000), i8_ss128 = run_i8<128, false>(40000), i8_ss96 = run_i8<96, false>(40000),
+               i8_ss64 = run_i8<64, false>(40000), i8_ts64 = run_i8<64, true>(40000);
   int khz = 0;
   cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, 0);
   // per thread-iteration: DFMA 16 fma = 32 flop; DMMA 8 x (512/32) = 128 flop; FFMA 32 flop
   printf("{\"dfma_tflops\": %.2f, \"dmma_m8n8k4_tflops\": %.2f, \"dfma_plus_dmma_tflops\": %.2f, "
          "\"dfma_plus_dmma_time_vs_sum\": %.3f, \"ffma_tflops\": %.2f, \"rsqrtf_cvt_dfma_gops\": %.1f, "
          "\"kstar_gen_us_per_128x64_stage_1cta\": %.4f, \"kstar_gen_us_per_128x64_stage_2cta\": %.4f, "
-         "\"kstar_gen_us_per_128x64_stage_1cta_88regs\": %.4f, \"max_sm_khz\": %d}\n",
+         "\"kstar_gen_us_per_128x64_stage_1cta_88regs\": %.4f, \"i8_mma_ss_m128n256k32_tops\": %.1f, "
+         "\"i8_mma_ss_m128n128k32_tops\": %.1f, \"i8_mma_ss_m128n96k32_tops\": %.1f, \"i8_mma_ss_m128n64k32_tops\": %.1f, "
+         "\"i8_mma_ts_m128n64k32_tops\": %.1f, \"max_sm_khz\": %d}\n",
          32.0 / t_dfma * 1e-12, 128.0 / t_dmma * 1e-12, 160.0 / t_both * 1e-12, t_both / (t_dfma + t_dmma),
-         32.0 / t_ffma * 1e-12, 16.0 / t_rsq * 1e-9, g1 * 1e6, g2 * 1e6, g3 * 1e6, khz);
+         32.0 / t_ffma * 1e-12, 16.0 / t_rsq * 1e-9, g1 * 1e6, g2 * 1e6, g3 * 1e6, i8_ss256, i8_ss128, i8_ss96, i8_ss64, i8_ts64, khz);
   return 0;
 }

@@ -62,7 +62,18 @@ struct cdx_pg_state {
   cdx_hand_dev* hand_dev = nullptr;
   int hand_n_dofs = 0;
   bool prof = false;
-  std::vector<cudaEvent_t> prof_ev;   // 5 events per profiled iteration
+  std::vector<cudaEvent_t> prof_ev;   // 6 events per profiled (iteration, group)
+  uint64_t hand_id = 0;               // hash of the loaded kinematic chains
+  uint64_t generation = 0;            // bumped by every cdx_pregrasp_init: lets a caller detect that another optimizer took the state over
+  int* it_dev = nullptr;              // device copy of it_host: the base iteration the nodes of a captured graph add their offset to
+  long long* nan_dev = nullptr;       // [0] candidate-iterations whose total_loss was NaN, [1] first such iteration (INT_MAX: none)
+  int tune_groups = 0, tune_occ = 0;  // cdx_pregrasp_set_tuning: 0 = automatic
+  bool use_graph = true;
+  // the iteration loop captured once as a CUDA graph of g_K iterations (all groups, all streams) and re-launched
+  cudaGraphExec_t gexec = nullptr;
+  cudaStream_t cap_stream = nullptr;
+  int g_K = 0;
+  uint64_t g_key = 0;
 };
 
 namespace {
@@ -178,8 +189,8 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
                double* __restrict__ tl, float* __restrict__ J, const double* __restrict__ dist,
                const double* __restrict__ sd, const double* __restrict__ gmu, const double* __restrict__ gsd,
                const double* __restrict__ mean9, const double* __restrict__ gmean9, double* __restrict__ loss,
-               double* __restrict__ margin, double* __restrict__ grad, int do_step, int it,
-               const double* __restrict__ adam_tab, double* __restrict__ m1, double* __restrict__ m2,
+               double* __restrict__ margin, double* __restrict__ grad, int do_step, const int* __restrict__ it_base, int it_off,
+               long long* __restrict__ nan_rec, const double* __restrict__ adam_tab, double* __restrict__ m1, double* __restrict__ m2,
                double* __restrict__ oq, double* __restrict__ ok, double* __restrict__ oT, double* __restrict__ opalm,
                double* __restrict__ omargin, double* __restrict__ ovalue, double* __restrict__ Xext,
                double* __restrict__ Xmean, double* __restrict__ mring, double* __restrict__ latched,
@@ -194,6 +205,8 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   __shared__ __align__(16) unsigned shand[CPB][HW];   // the group's own copy of the finger chains (FK walks them body by body)
   CDX_PG_TICK(7);
   const int sub = threadIdx.x & 15, p = sub >> 2, l = sub & 3, cl = threadIdx.x >> 4;
+  // absolute iteration index: inside a captured graph the base lives in device memory, so one graph serves every chunk
+  const int it = (it_base ? *it_base : 0) + it_off;
   const int64_t braw = b0 + (int64_t)blockIdx.x * CPB + cl;   // this launch covers candidates [b0, b1) of the B
   if (braw - (cl & 1) >= b1) return;    // whole WARPS (two candidates) leave together
   // a warp's second 16-lane group may lie past the end: it stays on the warp's path until the last shuffle (all shuffles
@@ -373,6 +386,11 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   if (S.w_ref != 0.0 && sub < nd) g[sub] += refn > 0.0 ? wsum * S.w_ref * (par[sub] - S.ref_q[sub]) / refn : 0.0;
   __syncwarp(gmask);
   if (sub == 0 && loss) loss[b] = total;
+  // the reference prints "NaN detected" and carries on (optimize_pregrasp.py:819): counted on the device, read after the run
+  if (sub == 0 && do_step && total != total) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(nan_rec), 1ull);
+    atomicMin(nan_rec + 1, (long long)it);
+  }
   if (sub < 4 && margin) margin[b * 4 + sub] = sr[cl][1 + sub];
   if (grad) for (int i = sub; i < NPAR; i += 16) grad[b * NPAR + i] = g[i];
   CDX_PG_TICK(10);
@@ -549,10 +567,20 @@ void cdx_pregrasp_free(cdx_ctx* ctx) {
     }
   if (ctx->pg->ev_begin) cudaEventDestroy(ctx->pg->ev_begin);
   for (cudaEvent_t e : ctx->pg->prof_ev) cudaEventDestroy(e);
+  if (ctx->pg->gexec) cudaGraphExecDestroy(ctx->pg->gexec);
+  if (ctx->pg->cap_stream) cudaStreamDestroy(ctx->pg->cap_stream);
+  cudaFree(ctx->pg->it_dev);
+  cudaFree(ctx->pg->nan_dev);
   cudaFree(ctx->pg->adam_tab);
   cudaFree(ctx->pg->hand_dev);
   delete ctx->pg;
   ctx->pg = nullptr;
+}
+
+static uint64_t pg_hash(uint64_t h, const void* p, size_t n) {   // FNV-1a
+  const unsigned char* c = (const unsigned char*)p;
+  for (size_t i = 0; i < n; i++) { h ^= c[i]; h *= 1099511628211ull; }
+  return h;
 }
 
 static cdx_pg_state* pg_get(cdx_ctx* ctx) {
@@ -563,6 +591,7 @@ static cdx_pg_state* pg_get(cdx_ctx* ctx) {
 extern "C" int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, const int* dof, const int* axis,
                              const float* axis_sign, const float* fixed_rot, const float* xyz, int n_dofs,
                              const int* tip_body, const float* tip_offset) {
+  CDX_NVTX("cdx_hand_load");
   if (!ctx || !parent || !dof || !axis || !axis_sign || !fixed_rot || !xyz || !tip_body || !tip_offset || n_bodies < 1 ||
       n_dofs < 1 || n_dofs > 16) {
     cdx_set_error("cdx_hand_load: bad argument (n_dofs must be 1..16)");
@@ -578,14 +607,21 @@ extern "C" int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, cons
   }
   CDX_CUDA(cudaSetDevice(ctx->device));
   cdx_pg_state* s = pg_get(ctx);
+  // the loaded hand's identity lives on the context: callers (one optimizer object per hand, several sharing one GPIS
+  // context) load unconditionally and an identical hand costs nothing
+  const uint64_t id = pg_hash(1469598103934665603ull, &h, sizeof(h));
+  if (s->hand_dev && ctx->hand_ready && s->hand_id == id && s->hand_n_dofs == n_dofs) return CDX_OK;
   if (!s->hand_dev) CDX_CUDA(cudaMalloc((void**)&s->hand_dev, sizeof(cdx_hand_dev)));
+  CDX_CUDA(cudaDeviceSynchronize());   // non-blocking side / group streams may still be reading the previous hand
   CDX_CUDA(cudaMemcpy(s->hand_dev, &h, sizeof(h), cudaMemcpyHostToDevice));
+  s->hand_id = id;
   s->setup.n_dofs = s->hand_n_dofs = n_dofs;
   ctx->hand_ready = true;
   return CDX_OK;
 }
 
 extern "C" int cdx_hand_fk(cdx_ctx* ctx, const double* q, const double* palm, int64_t B, double* tips, void* stream) {
+  CDX_NVTX("cdx_hand_fk");
   if (!ctx || !ctx->hand_ready) { cdx_set_error("cdx_hand_fk: no hand loaded"); return CDX_ERR_STATE; }
   if (B < 0 || (B > 0 && (!q || !palm || !tips))) { cdx_set_error("cdx_hand_fk: bad argument"); return CDX_ERR_ARG; }
   if (B == 0) return CDX_OK;
@@ -604,6 +640,7 @@ extern "C" int cdx_hand_fk(cdx_ctx* ctx, const double* q, const double* palm, in
 // the constant palm offset (xyz, zero Euler angles) repeated per candidate
 extern "C" int cdx_hand_fk_recursive(cdx_ctx* ctx, const double* q, const double* palm_offset3, int64_t B, double* tips,
                                      void* stream) {
+  CDX_NVTX("cdx_hand_fk_recursive");
   if (!ctx || !ctx->hand_ready) { cdx_set_error("cdx_hand_fk_recursive: no hand loaded"); return CDX_ERR_STATE; }
   if (B < 0 || (B > 0 && (!q || !palm_offset3 || !tips))) { cdx_set_error("cdx_hand_fk_recursive: bad argument"); return CDX_ERR_ARG; }
   if (B == 0) return CDX_OK;
@@ -621,6 +658,7 @@ extern "C" int cdx_hand_fk_recursive(cdx_ctx* ctx, const double* q, const double
 
 extern "C" int cdx_collision_cost(cdx_ctx* ctx, const double* anchor, int64_t B, int A, const int* left, const int* right,
                                   int npairs, double threshold, const double* palm, double* cost, void* stream) {
+  CDX_NVTX("cdx_collision_cost");
   if (!ctx || B < 0 || A < 1 || npairs < 0 || (B > 0 && (!anchor || !cost)) || (npairs > 0 && (!left || !right))) {
     cdx_set_error("cdx_collision_cost: bad argument");
     return CDX_ERR_ARG;
@@ -637,6 +675,7 @@ extern "C" int cdx_collision_cost(cdx_ctx* ctx, const double* anchor, int64_t B,
 
 extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int64_t B, const double* q0,
                                  const double* k0, const double* T0, const double* palm0, void* stream) {
+  CDX_NVTX("cdx_pregrasp_init");
   if (!ctx || !p) { cdx_set_error("cdx_pregrasp_init: NULL argument"); return CDX_ERR_ARG; }
   if (p->variant < 0 || p->variant > 2) { cdx_set_error("cdx_pregrasp_init: variant must be 0, 1 or 2"); return CDX_ERR_ARG; }
   if (p->variant != 2 && !ctx->hand_ready) { cdx_set_error("cdx_pregrasp_init: cdx_hand_load first"); return CDX_ERR_STATE; }
@@ -715,7 +754,17 @@ extern "C" int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int
     CDX_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
     CDX_CUDA(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
   }
+  if (!s->it_dev) {
+    CDX_CUDA(cudaMalloc((void**)&s->it_dev, sizeof(int)));
+    CDX_CUDA(cudaMalloc((void**)&s->nan_dev, sizeof(long long) * 2));
+  }
+  {
+    const long long nan0[2] = {0, 0x7fffffffll};
+    CDX_CUDA(cudaMemcpyAsync(s->nan_dev, nan0, sizeof(nan0), cudaMemcpyHostToDevice, st));
+    CDX_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), st));
+  }
   s->B = B;
+  s->generation++;
   CDX_CUDA(cudaMemcpyAsync(s->q, q0, sizeof(double) * B * nd, cudaMemcpyDeviceToDevice, st));
   CDX_CUDA(cudaMemcpyAsync(s->k, k0, sizeof(double) * B * 4, cudaMemcpyDeviceToDevice, st));
   CDX_CUDA(cudaMemcpyAsync(s->T, T0, sizeof(double) * B * 12, cudaMemcpyDeviceToDevice, st));
@@ -751,9 +800,10 @@ static int pg_points(cdx_ctx* ctx, cdx_pg_state* s, cudaStream_t st) {
 }
 
 // one closure evaluation of candidates [b0, b1): (points of the initial iterate) -> GPIS queries (extended on `st`, mean-only
-// overlapped on the side stream) -> step kernel (objective + gradient, optionally Adam + points of the new iterate)
+// overlapped on the side stream) -> step kernel (objective + gradient, optionally Adam + points of the new iterate).
+// The iteration index the step kernel sees is *it_base + it_off (it_base == nullptr: it_off alone).
 static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss, double* margin, double* grad,
-                        cudaStream_t st, int64_t b0 = 0, int64_t b1 = -1, int group = 0) {
+                        cudaStream_t st, const int* it_base, int it_off, int64_t b0 = 0, int64_t b1 = -1, int group = 0) {
   const int64_t B = s->B;
   if (b1 < 0) b1 = B;
   const int64_t nb = b1 - b0;
@@ -786,12 +836,12 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   CDX_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
   mark(4, st);
   int occ = (nb + CPB - 1) / CPB > 2 * (int64_t)ctx->sms ? 3 : 2;
-  if (const char* e = getenv("CDX_PG_OCC")) occ = atoi(e) == 3 ? 3 : 2;
+  if (s->tune_occ == 2 || s->tune_occ == 3) occ = s->tune_occ;
 #define PG_STEP(V) PG_STEP_O(V, 2); else PG_STEP_O(V, 3)
 #define PG_STEP_O(V, O) if (occ == O) pg_step_kernel<V, O><<<(unsigned)((nb + CPB - 1) / CPB), CPB * 16, 0, st>>>(                                  \
       s->hand_dev, B, b0, b1, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd,      \
-      s->mean9, s->gmean9, loss, margin, grad, do_step, s->it_host, s->adam_tab, s->m1, s->m2, s->oq, s->ok, s->oT, s->opalm,   \
-      s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch)
+      s->mean9, s->gmean9, loss, margin, grad, do_step, it_base, it_off, s->nan_dev, s->adam_tab, s->m1, s->m2, s->oq, s->ok,   \
+      s->oT, s->opalm, s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch)
   if (s->setup.variant == 0) { PG_STEP(0); } else if (s->setup.variant == 1) { PG_STEP(1); } else { PG_STEP(2); }
 #undef PG_STEP
 #undef PG_STEP_O
@@ -810,10 +860,9 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
 // slows down beside another group's FP64 tensor work, so the gain stays well under what the gaps suggest).
 // The Kin / GPIS variants latch the WHOLE batch's margin when any candidate improves (:491-494): one group.
 static int pg_groups(const cdx_pg_state* s) {
-  if (s->setup.variant != 0 || s->prof) return 1;
+  if (s->setup.variant != 0) return 1;
   int G = s->B >= 768 ? 2 : 1;
-  if (const char* e = getenv("CDX_PG_GROUPS")) G = atoi(e);
-  if (G < 1) G = 1;
+  if (s->tune_groups > 0) G = s->tune_groups;
   if (G > cdx_pg_state::MAX_GROUPS) G = cdx_pg_state::MAX_GROUPS;
   while (G > 1 && s->B / G < CPB) G--;
   return G;
@@ -833,17 +882,64 @@ static int pg_adam_table(cdx_pg_state* s, int upto, cudaStream_t st) {
     tab[2 * i] = 1.0 - pow(s->prm.beta1, (double)(i + 1));
     tab[2 * i + 1] = sqrt(1.0 - pow(s->prm.beta2, (double)(i + 1)));
   }
-  CDX_CUDA(cudaStreamSynchronize(st));
+  CDX_CUDA(cudaDeviceSynchronize());   // group / side streams may still read the old table
   cudaFree(s->adam_tab);
   s->adam_tab = nullptr;
   s->tab_cap = 0;
+  s->g_key = 0;                        // a captured graph holds the old pointer
   CDX_CUDA(cudaMalloc((void**)&s->adam_tab, sizeof(double) * tab.size()));
   CDX_CUDA(cudaMemcpy(s->adam_tab, tab.data(), sizeof(double) * tab.size(), cudaMemcpyHostToDevice));
   s->tab_cap = cap;
   return CDX_OK;
 }
 
+__global__ void pg_set_int_kernel(int* p, int v) { *p = v; }
+
+// iterations [0, n) of all G candidate groups on their stream pairs, forked from and joined back into `st`; the step
+// kernels see iteration *it_base + it0 + i
+static int pg_enqueue(cdx_ctx* ctx, cdx_pg_state* s, int G, int n, cudaStream_t st, const int* it_base, int it0) {
+  if (G == 1) {
+    for (int i = 0; i < n; i++) {
+      int rc = pg_iteration(ctx, s, 1, s->loss, s->margin, nullptr, st, it_base, it0 + i);
+      if (rc) return rc;
+    }
+    return CDX_OK;
+  }
+  // group boundaries on whole CTAs
+  const int64_t per = ((s->B + G - 1) / G + CPB - 1) / CPB * CPB;
+  CDX_CUDA(cudaEventRecord(s->ev_begin, st));
+  for (int g = 1; g < G; g++) CDX_CUDA(cudaStreamWaitEvent(s->gmain[g], s->ev_begin, 0));
+  for (int i = 0; i < n; i++)
+    for (int g = 0; g < G; g++) {
+      const int64_t b0 = g * per, b1 = b0 + per < s->B ? b0 + per : s->B;
+      if (b0 >= b1) continue;
+      int rc = pg_iteration(ctx, s, 1, s->loss, s->margin, nullptr, g ? s->gmain[g] : st, it_base, it0 + i, b0, b1, g);
+      if (rc) return rc;
+    }
+  for (int g = 1; g < G; g++) {
+    CDX_CUDA(cudaEventRecord(s->gend[g], s->gmain[g]));
+    CDX_CUDA(cudaStreamWaitEvent(st, s->gend[g], 0));
+  }
+  return CDX_OK;
+}
+
+// everything a captured iteration bakes into its kernel nodes
+static uint64_t pg_graph_key(const cdx_ctx* ctx, const cdx_pg_state* s, int G, int K) {
+  uint64_t h = 1469598103934665603ull;
+  const void* ptrs[] = {s->q, s->m1, s->ovalue, s->Xext, s->adam_tab, s->hand_dev, ctx->g.Xa, ctx->g.P, ctx->g.U, s->gmain[1]};
+  h = pg_hash(h, ptrs, sizeof(ptrs));
+  h = pg_hash(h, &s->B, sizeof(s->B));
+  h = pg_hash(h, &s->prm, sizeof(s->prm));
+  h = pg_hash(h, &s->setup, sizeof(s->setup));
+  const int64_t misc[] = {G, K, s->U, s->tune_occ, ctx->g.N, ctx->g.Np, ctx->g.kernel, ctx->g.var_mode};
+  h = pg_hash(h, misc, sizeof(misc));
+  const double dm[] = {ctx->g.R, ctx->g.bias, ctx->g.sigma, ctx->g.prior};
+  h = pg_hash(h, dm, sizeof(dm));
+  return h ? h : 1;
+}
+
 extern "C" int cdx_pregrasp_run(cdx_ctx* ctx, int n_iters, void* stream) {
+  CDX_NVTX("cdx_pregrasp_run");
   int rc = pg_ready(ctx, "cdx_pregrasp_run");
   if (rc) return rc;
   if (n_iters < 0) { cdx_set_error("cdx_pregrasp_run: n_iters < 0"); return CDX_ERR_ARG; }
@@ -852,58 +948,132 @@ extern "C" int cdx_pregrasp_run(cdx_ctx* ctx, int n_iters, void* stream) {
   cdx_pg_state* s = ctx->pg;
   rc = pg_adam_table(s, s->it_host + n_iters, st);
   if (rc) return rc;
-  const int G = n_iters > 0 ? pg_groups(s) : 1;
-  if (G == 1) {
-    for (int i = 0; i < n_iters; i++) {
-      rc = pg_iteration(ctx, s, 1, s->loss, s->margin, nullptr, st);
-      if (rc) return rc;
-      s->it_host++;
-    }
-    return CDX_OK;
+  if (n_iters == 0) return CDX_OK;
+  const int G = pg_groups(s);
+  if (G > 1) {
+    int prio_lo = 0, prio_hi = 0;
+    CDX_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    if (!s->ev_begin) CDX_CUDA(cudaEventCreateWithFlags(&s->ev_begin, cudaEventDisableTiming));
+    for (int g = 1; g < G; g++)
+      if (!s->gmain[g]) {
+        CDX_CUDA(cudaStreamCreateWithFlags(&s->gmain[g], cudaStreamNonBlocking));
+        CDX_CUDA(cudaStreamCreateWithPriority(&s->gside[g], cudaStreamNonBlocking, prio_hi));
+        CDX_CUDA(cudaEventCreateWithFlags(&s->gfork[g], cudaEventDisableTiming));
+        CDX_CUDA(cudaEventCreateWithFlags(&s->gjoin[g], cudaEventDisableTiming));
+        CDX_CUDA(cudaEventCreateWithFlags(&s->gend[g], cudaEventDisableTiming));
+      }
   }
-  int prio_lo = 0, prio_hi = 0;
-  CDX_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-  if (!s->ev_begin) CDX_CUDA(cudaEventCreateWithFlags(&s->ev_begin, cudaEventDisableTiming));
-  for (int g = 1; g < G; g++)
-    if (!s->gmain[g]) {
-      CDX_CUDA(cudaStreamCreateWithFlags(&s->gmain[g], cudaStreamNonBlocking));
-      CDX_CUDA(cudaStreamCreateWithPriority(&s->gside[g], cudaStreamNonBlocking, prio_hi));
-      CDX_CUDA(cudaEventCreateWithFlags(&s->gfork[g], cudaEventDisableTiming));
-      CDX_CUDA(cudaEventCreateWithFlags(&s->gjoin[g], cudaEventDisableTiming));
-      CDX_CUDA(cudaEventCreateWithFlags(&s->gend[g], cudaEventDisableTiming));
-    }
   rc = pg_points(ctx, s, st);
   if (rc) return rc;
-  // group boundaries on whole CTAs
-  const int64_t per = ((s->B + G - 1) / G + CPB - 1) / CPB * CPB;
-  CDX_CUDA(cudaEventRecord(s->ev_begin, st));
-  for (int g = 1; g < G; g++) CDX_CUDA(cudaStreamWaitEvent(s->gmain[g], s->ev_begin, 0));
-  for (int i = 0; i < n_iters; i++) {
-    for (int g = 0; g < G; g++) {
-      const int64_t b0 = g * per, b1 = b0 + per < s->B ? b0 + per : s->B;
-      if (b0 >= b1) continue;
-      rc = pg_iteration(ctx, s, 1, s->loss, s->margin, nullptr, g ? s->gmain[g] : st, b0, b1, g);
-      if (rc) return rc;
+  // The loop as a CUDA graph: K iterations - every group's three launches, forks and joins - are captured
+  // once and re-launched n_iters / K times; the nodes read the chunk's base iteration from device memory, so the same
+  // executable graph serves every chunk and every later run with the same batch.  Without it the host issues ~14 driver
+  // calls per iteration.  Profiling (per-kernel events) and the remainder iterations use direct launches.
+  int done = 0;
+  if (s->use_graph && !s->prof) {
+    int K = n_iters < 50 ? n_iters : 50;
+    if (K >= 4) {
+      const uint64_t key = pg_graph_key(ctx, s, G, K);
+      if (s->gexec == nullptr || s->g_key != key) {
+        if (s->gexec) { cudaGraphExecDestroy(s->gexec); s->gexec = nullptr; }
+        // one direct iteration first: every kernel's attributes (dynamic shared memory) are set outside the capture
+        rc = pg_enqueue(ctx, s, G, 1, st, nullptr, s->it_host);
+        if (rc) return rc;
+        s->it_host++;
+        done = 1;
+        cudaGraph_t graph = nullptr;
+        const int64_t launches0 = ctx->launches;
+        // captured on a stream of our own (the caller's may be the legacy default stream, which cannot capture); the
+        // executable graph is then launched into the caller's stream
+        if (!s->cap_stream) CDX_CUDA(cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking));
+        CDX_CUDA(cudaStreamBeginCapture(s->cap_stream, cudaStreamCaptureModeRelaxed));
+        rc = pg_enqueue(ctx, s, G, K, s->cap_stream, s->it_dev, 0);
+        cudaError_t ce = cudaStreamEndCapture(s->cap_stream, &graph);
+        ctx->launches = launches0;                                   // captured, not launched
+        if (rc || ce != cudaSuccess || !graph) {
+          if (graph) cudaGraphDestroy(graph);
+          if (!rc) { cdx_set_error("cdx_pregrasp_run: graph capture failed: %s", cudaGetErrorString(ce)); rc = CDX_ERR_CUDA; }
+          cudaGetLastError();
+          return rc;
+        }
+        ce = cudaGraphInstantiate(&s->gexec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ce != cudaSuccess) {
+          s->gexec = nullptr;
+          cdx_set_error("cdx_pregrasp_run: cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+          return CDX_ERR_CUDA;
+        }
+        s->g_key = key;
+        s->g_K = K;
+      }
+      const int per_iter = 3 * G;   // kernel nodes per captured iteration (mean query, extended query, step) per group
+      while (n_iters - done >= s->g_K) {
+        pg_set_int_kernel<<<1, 1, 0, st>>>(s->it_dev, s->it_host);
+        CDX_CHECK_LAUNCH(ctx);
+        CDX_CUDA(cudaGraphLaunch(s->gexec, st));
+        ctx->launches += (int64_t)per_iter * s->g_K;
+        s->it_host += s->g_K;
+        done += s->g_K;
+      }
     }
-    s->it_host++;
   }
-  for (int g = 1; g < G; g++) {
-    CDX_CUDA(cudaEventRecord(s->gend[g], s->gmain[g]));
-    CDX_CUDA(cudaStreamWaitEvent(st, s->gend[g], 0));
+  if (done < n_iters) {
+    rc = pg_enqueue(ctx, s, G, n_iters - done, st, nullptr, s->it_host);
+    if (rc) return rc;
+    s->it_host += n_iters - done;
   }
   return CDX_OK;
 }
 
-extern "C" int cdx_pregrasp_eval(cdx_ctx* ctx, double* total_loss, double* margin, double* gq, double* gc, double* gt,
-                                 double* gp, void* stream) {
+extern "C" int cdx_pregrasp_set_tuning(cdx_ctx* ctx, int groups, int occupancy, int use_graph) {
+  if (!ctx || groups < 0 || groups > cdx_pg_state::MAX_GROUPS || !(occupancy == 0 || occupancy == 2 || occupancy == 3)) {
+    cdx_set_error("cdx_pregrasp_set_tuning: groups in 0..%d (0 = auto), occupancy 0 (auto), 2 or 3", cdx_pg_state::MAX_GROUPS);
+    return CDX_ERR_ARG;
+  }
+  cdx_pg_state* s = pg_get(ctx);
+  s->tune_groups = groups;
+  s->tune_occ = occupancy;
+  s->use_graph = use_graph != 0;
+  return CDX_OK;
+}
+
+extern "C" int cdx_pregrasp_nan_count(cdx_ctx* ctx, int64_t* count_host, int* first_iter_host, void* stream) {
+  if (!ctx || !ctx->pg || ctx->pg->B == 0 || !count_host) { cdx_set_error("cdx_pregrasp_nan_count: cdx_pregrasp_init first"); return CDX_ERR_STATE; }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  long long h[2] = {0, 0};
+  CDX_CUDA(cudaMemcpyAsync(h, ctx->pg->nan_dev, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CDX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  *count_host = (int64_t)h[0];
+  if (first_iter_host) *first_iter_host = h[0] > 0 ? (int)h[1] : -1;
+  return CDX_OK;
+}
+
+extern "C" int64_t cdx_pregrasp_generation(cdx_ctx* ctx, int64_t* B_out) {
+  if (!ctx || !ctx->pg) return 0;
+  if (B_out) *B_out = ctx->pg->B;
+  return (int64_t)ctx->pg->generation;
+}
+
+// the caller sized its buffers for B candidates: they must be the batch of the last cdx_pregrasp_init on this context
+static int pg_batch_check(const cdx_pg_state* s, int64_t B, const char* who) {
+  if (B == s->B) return CDX_OK;
+  cdx_set_error("%s: buffers for %lld candidates, but the context holds a batch of %lld (another optimizer re-initialised it?)",
+                who, (long long)B, (long long)s->B);
+  return CDX_ERR_ARG;
+}
+
+extern "C" int cdx_pregrasp_eval(cdx_ctx* ctx, int64_t Bcap, double* total_loss, double* margin, double* gq, double* gc,
+                                 double* gt, double* gp, void* stream) {
+  CDX_NVTX("cdx_pregrasp_eval");
   int rc = pg_ready(ctx, "cdx_pregrasp_eval");
   if (rc) return rc;
+  if ((rc = pg_batch_check(ctx->pg, Bcap, "cdx_pregrasp_eval"))) return rc;
   CDX_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = (cudaStream_t)stream;
   cdx_pg_state* s = ctx->pg;
   rc = pg_adam_table(s, s->it_host + 1, st);
   if (rc) return rc;
-  rc = pg_iteration(ctx, s, 0, s->loss, s->margin, s->grad, st);
+  rc = pg_iteration(ctx, s, 0, s->loss, s->margin, s->grad, st, nullptr, s->it_host);
   if (rc) return rc;
   const int64_t B = s->B;
   const int nd = s->setup.n_dofs;
@@ -919,9 +1089,11 @@ extern "C" int cdx_pregrasp_eval(cdx_ctx* ctx, double* total_loss, double* margi
 
 #define PG_COPY(dst, src, n) if (dst) CDX_CUDA(cudaMemcpyAsync(dst, src, sizeof(double) * (size_t)(n), cudaMemcpyDeviceToDevice, st))
 
-extern "C" int cdx_pregrasp_results(cdx_ctx* ctx, double* oq, double* ok, double* oT, double* opalm, double* omargin,
-                                    double* ovalue, void* stream) {
+extern "C" int cdx_pregrasp_results(cdx_ctx* ctx, int64_t Bcap, double* oq, double* ok, double* oT, double* opalm,
+                                    double* omargin, double* ovalue, void* stream) {
+  CDX_NVTX("cdx_pregrasp_results");
   if (!ctx || !ctx->pg || ctx->pg->B == 0) { cdx_set_error("cdx_pregrasp_results: cdx_pregrasp_init first"); return CDX_ERR_STATE; }
+  if (int rcb = pg_batch_check(ctx->pg, Bcap, "cdx_pregrasp_results")) return rcb;
   CDX_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = (cudaStream_t)stream;
   cdx_pg_state* s = ctx->pg;
@@ -931,8 +1103,9 @@ extern "C" int cdx_pregrasp_results(cdx_ctx* ctx, double* oq, double* ok, double
   return CDX_OK;
 }
 
-extern "C" int cdx_pregrasp_state(cdx_ctx* ctx, double* q, double* k, double* T, double* palm, void* stream) {
+extern "C" int cdx_pregrasp_state(cdx_ctx* ctx, int64_t Bcap, double* q, double* k, double* T, double* palm, void* stream) {
   if (!ctx || !ctx->pg || ctx->pg->B == 0) { cdx_set_error("cdx_pregrasp_state: cdx_pregrasp_init first"); return CDX_ERR_STATE; }
+  if (int rcb = pg_batch_check(ctx->pg, Bcap, "cdx_pregrasp_state")) return rcb;
   CDX_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = (cudaStream_t)stream;
   cdx_pg_state* s = ctx->pg;
@@ -941,7 +1114,9 @@ extern "C" int cdx_pregrasp_state(cdx_ctx* ctx, double* q, double* k, double* T,
   return CDX_OK;
 }
 
-extern "C" int cdx_pregrasp_latched_margin(cdx_ctx* ctx, double* margin, int* iter, void* stream) {
+extern "C" int cdx_pregrasp_latched_margin(cdx_ctx* ctx, int64_t Bcap, double* margin, int* iter, void* stream) {
+  if (ctx && ctx->pg && ctx->pg->B)
+    if (int rcb = pg_batch_check(ctx->pg, Bcap, "cdx_pregrasp_latched_margin")) return rcb;
   if (!ctx || !ctx->pg || ctx->pg->B == 0) { cdx_set_error("cdx_pregrasp_latched_margin: cdx_pregrasp_init first"); return CDX_ERR_STATE; }
   cdx_pg_state* s = ctx->pg;
   if (s->setup.variant == 0) {
@@ -957,6 +1132,7 @@ extern "C" int cdx_pregrasp_latched_margin(cdx_ctx* ctx, double* margin, int* it
 }
 
 extern "C" int cdx_pregrasp_argmin(cdx_ctx* ctx, double* out, void* stream) {
+  CDX_NVTX("cdx_pregrasp_argmin");
   if (!ctx || !ctx->pg || ctx->pg->B == 0) { cdx_set_error("cdx_pregrasp_argmin: cdx_pregrasp_init first"); return CDX_ERR_STATE; }
   if (!out) { cdx_set_error("cdx_pregrasp_argmin: out is NULL"); return CDX_ERR_ARG; }
   CDX_CUDA(cudaSetDevice(ctx->device));

@@ -332,11 +332,7 @@ int launch_mean(cdx_ctx* ctx, const double* Xa, const double* X, int64_t M, doub
   cdx_gpis_state& g = ctx->g;
   int tile = (int)min((int64_t)4096, g.Np);
   size_t smem = (size_t)tile * 32 + 16;
-  static bool attr_set[3] = {false, false, false};
-  if (!attr_set[KERNEL]) {
-    CDX_CUDA(cudaFuncSetAttribute(gpis_mean_kernel<KERNEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 32 + 16));
-    attr_set[KERNEL] = true;
-  }
+  if (int rc = cdx_smem_attr(ctx, gpis_mean_kernel<KERNEL>, 4096 * 32 + 16)) return rc;
   int per_sm = (int)max((size_t)1, min((size_t)8, (size_t)(200 * 1024) / smem));
   int64_t nqt = (M + MQ - 1) / MQ;
   int grid = (int)min(nqt, (int64_t)ctx->sms * per_sm);
@@ -350,11 +346,7 @@ int launch_var(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* g
                cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
   size_t smem = sizeof(double) * (size_t)(NA * TQ * LDS + (TQ == 32 ? 3 : NB) * TN * LDS + TQ * 3 + 4 * TQ * 4 + TQ * 4);
-  static bool attr_set = false;
-  if (!attr_set) {
-    CDX_CUDA(cudaFuncSetAttribute(gpis_var_kernel<KERNEL, TN, EXT, TQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (int rc = cdx_smem_attr(ctx, gpis_var_kernel<KERNEL, TN, EXT, TQ>, smem)) return rc;
   const int64_t grid = (M + TQ - 1) / TQ;
   const int NT = (int)((g.Np + TN - 1) / TN);
   // small batch and few column tiles: one CTA per (query tile, column tile), the column tiles of a query tile forming a
@@ -418,6 +410,7 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
 
 extern "C" int cdx_gpis_query(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv,
                               double* gstd, void* stream) {
+  CDX_NVTX("cdx_gpis_query");
   if (!ctx || !ctx->g.ready) { cdx_set_error("cdx_gpis_query: no fitted state"); return CDX_ERR_STATE; }
   if (M < 0 || (M > 0 && !X)) { cdx_set_error("cdx_gpis_query: bad argument"); return CDX_ERR_ARG; }
   if (M == 0 || (!mean && !gmean && !stdv && !gstd)) return CDX_OK;
@@ -433,6 +426,7 @@ extern "C" int cdx_gpis_query(cdx_ctx* ctx, const double* X, int64_t M, double* 
 
 extern "C" int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha, const double* X, int64_t M, double* mean,
                                       double* gmean, void* stream) {
+  CDX_NVTX("cdx_gpis_query_weights");
   if (!ctx || !ctx->g.ready) { cdx_set_error("cdx_gpis_query_weights: no fitted state"); return CDX_ERR_STATE; }
   if (!alpha || M < 0 || (M > 0 && !X)) { cdx_set_error("cdx_gpis_query_weights: bad argument"); return CDX_ERR_ARG; }
   if (M == 0) return CDX_OK;
@@ -455,6 +449,7 @@ extern "C" int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha, const d
 
 extern "C" int cdx_gpis_query_host(cdx_ctx* ctx, const double* Xh, int64_t M, double* mean_h, double* gmean_h,
                                    double* std_h, double* gstd_h, void* stream) {
+  CDX_NVTX("cdx_gpis_query_host");
   if (!ctx || !ctx->g.ready) { cdx_set_error("cdx_gpis_query_host: no fitted state"); return CDX_ERR_STATE; }
   if (M < 0 || (M > 0 && !Xh)) { cdx_set_error("cdx_gpis_query_host: bad argument"); return CDX_ERR_ARG; }
   if (M == 0) return CDX_OK;

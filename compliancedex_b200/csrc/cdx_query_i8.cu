@@ -498,6 +498,8 @@ int i8_prepare(cdx_ctx* ctx, cudaStream_t st) {
   i8_points_kernel<<<1, 256, 0, st>>>(g.Xa, N, Np, g.i8_pts, g.i8_bb);
   CDX_CHECK_LAUNCH(ctx);
   g.i8_S = S;
+  if (!g.i8_ready) CDX_CUDA(cudaEventCreateWithFlags(&g.i8_ready, cudaEventDisableTiming));
+  CDX_CUDA(cudaEventRecord(g.i8_ready, st));
   return CDX_OK;
 }
 
@@ -506,11 +508,8 @@ int i8_launch(cdx_ctx* ctx, const double* X, int64_t M, double* stdv, cudaStream
   int rc = i8_prepare<S>(ctx, st);
   if (rc) return rc;
   cdx_gpis_state& g = ctx->g;
-  static bool attr_set = false;
-  if (!attr_set) {
-    CDX_CUDA(cudaFuncSetAttribute(gpis_std_i8_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)i8cfg<S>::SMEM));
-    attr_set = true;
-  }
+  if (int rca = cdx_smem_attr(ctx, gpis_std_i8_kernel<S>, i8cfg<S>::SMEM)) return rca;
+  CDX_CUDA(cudaStreamWaitEvent(st, g.i8_ready, 0));   // the slices may have been built on another stream
   const int64_t grid = (M + I8_TQ - 1) / I8_TQ;
   gpis_std_i8_kernel<S><<<(unsigned)grid, I8_THREADS, i8cfg<S>::SMEM, st>>>(X, M, g.i8_pts, g.i8_B, g.i8_sb, g.i8_bb, (int)g.Np,
                                                                              g.R, g.R * g.R * g.R, g.prior, stdv);
@@ -540,6 +539,7 @@ void cdx_i8_free(cdx_ctx* ctx) {
   cudaFree(g.i8_B); cudaFree(g.i8_sb); cudaFree(g.i8_eb); cudaFree(g.i8_pts); cudaFree(g.i8_bb);
   g.i8_B = nullptr; g.i8_sb = nullptr; g.i8_eb = nullptr; g.i8_pts = nullptr; g.i8_bb = nullptr;
   g.i8_S = 0; g.i8_cap = 0; g.i8_np = 0;
+  if (g.i8_ready) { cudaEventDestroy(g.i8_ready); g.i8_ready = nullptr; }
 }
 
 extern "C" int cdx_gpis_set_var_mode(cdx_ctx* ctx, int mode) {

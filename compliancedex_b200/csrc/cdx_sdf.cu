@@ -502,6 +502,7 @@ static int sdf_forward_t(cdx_ctx* ctx, cdx_sdf_state* s, const T* points, int64_
 
 extern "C" int cdx_sdf_forward(cdx_ctx* ctx, const void* points, int64_t P, const void* face_vertices, int64_t F, int dtype,
                                void* dist, int32_t* sign, void* normals, void* closest, void* stream) {
+  CDX_NVTX("cdx_sdf_forward");
   if (!ctx || P < 0 || F < 0 || (dtype != 0 && dtype != 1) || (P > 0 && !points) || (F > 0 && !face_vertices)) {
     cdx_set_error("cdx_sdf_forward: bad argument (dtype 0 = float32, 1 = float64)");
     return CDX_ERR_ARG;
@@ -534,6 +535,7 @@ extern "C" int cdx_sdf_set_mode(cdx_ctx* ctx, int mode) {
 
 extern "C" int cdx_sdf_backward(cdx_ctx* ctx, const void* grad_dist, const void* points, const void* closest, int64_t P,
                                 int dtype, void* grad_points, void* stream) {
+  CDX_NVTX("cdx_sdf_backward");
   if (!ctx || P < 0 || (dtype != 0 && dtype != 1) || (P > 0 && (!grad_dist || !points || !closest || !grad_points))) {
     cdx_set_error("cdx_sdf_backward: bad argument");
     return CDX_ERR_ARG;

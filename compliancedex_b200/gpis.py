@@ -89,6 +89,8 @@ class GPIS:
             raise RuntimeError("compliancedex_b200.GPIS runs on CUDA tensors only (no CPU fallback)")
         idx = device.index if device.index is not None else torch.cuda.current_device()
         if self._ctx is None or self._device != idx:
+            if self._ctx is not None:
+                self._ctx.close()                     # moving to another device: release the old device's state now
             self._ctx = _lib.new_context(idx)
             self._device = idx
             _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, getattr(self, "_var_mode", 0)))
@@ -203,24 +205,25 @@ class GPIS:
             return n.view(shape)
         return n.view(shape), weight_sum
 
-    def compute_multinormals(self, X2, num_normal_samples):
-        # gpis.py:89-111
+    def _nested_row_subsets(self, S):
+        """The training-row subsets of gpis.py:96-104, cached on first use like the reference (`self.fraction`,
+        `self.indices`): S // 2 prefixes [0, int(f N)), f = linspace(0.8, 1, S // 2); all rows; S // 2 ranges
+        [int(1 - f), N) - which start at 0 for every f in (0, 1], i.e. all rows again (the reference's arithmetic, kept)."""
         if self.fraction is None:
-            self.fraction = torch.linspace(0.8, 1, num_normal_samples // 2)
-            self.indices = []
-            n = len(self.X1)
-            for i in range(num_normal_samples // 2):
-                self.indices.append(list(range(int(self.fraction[i] * n))))
-            self.indices.append(list(range(n)))
-            for i in range(num_normal_samples // 2):
-                self.indices.append(list(range(int(1 - self.fraction[-i - 1]), n)))
-        normals, weights = [], []
-        for i in range(num_normal_samples):
-            nrm, w = self.compute_normal(X2, self.indices[i])
-            normals.append(nrm)
-            weights.append(w)
-        weights = torch.hstack(weights)
-        return torch.stack(normals, dim=1), weights / weights.sum()
+            N, h = len(self.X1), S // 2
+            self.fraction = torch.linspace(0.8, 1, h)
+            stops = [int(self.fraction[i] * N) for i in range(h)]
+            starts = [int(1 - self.fraction[h - 1 - i]) for i in range(h)]
+            self.indices = [list(range(e)) for e in stops] + [list(range(N))] + [list(range(b, N)) for b in starts]
+        return self.indices
+
+    def compute_multinormals(self, X2, num_normal_samples):
+        """gpis.py:89-111: X2 [M,3] -> (normals [M,S,3], weights [S]); sample i is compute_normal on the i-th nested
+        row subset, the weights are the subsets' alpha sums normalised to 1."""
+        subsets = self._nested_row_subsets(num_normal_samples)
+        per_subset = [self.compute_normal(X2, subsets[i]) for i in range(num_normal_samples)]
+        w = torch.hstack([w_i for _, w_i in per_subset])
+        return torch.stack([n_i for n_i, _ in per_subset], dim=1), w / w.sum()
 
     def get_visualization_data(self, lb, ub, steps=100):
         """gpis.py:113-125: the grid driver; one fused query over all steps^3 points instead of `steps` slabs."""

@@ -69,7 +69,8 @@ class ProbabilisticGraspOptimizer:
         self.noise_seed, self.env_offset = int(noise_seed), int(env_offset)
         self.opt_value = None
         self._ctx = None
-        self._hand_loaded_for = None
+        self._generation = None          # cdx_pregrasp_generation of the _init that made this object the owner of the ctx state
+        self._tuning = None
 
     # ---- plumbing --------------------------------------------------------------------------------------
     def _dev_index(self):
@@ -81,14 +82,35 @@ class ProbabilisticGraspOptimizer:
         return ctypes.c_void_p(torch.cuda.current_stream(self._dev_index()).cuda_stream)
 
     def _bind(self, ctx):
-        """use `ctx` (the GPIS object's context, which owns the fitted state) and load the hand into it once"""
+        """use `ctx` (the GPIS object's context, which owns the fitted state) and make this optimizer's hand the one loaded
+        in it.  Unconditional: the context keeps the loaded hand's identity, so re-loading the same hand is free and two
+        optimizers with different hands sharing one GPIS can alternate."""
         self._ctx = ctx
-        if self._hand_loaded_for != ctx.value:
-            t = self.tree
-            _lib.check(_lib.load().cdx_hand_load(ctx, t.n_bodies, _np_ptr(t.parent), _np_ptr(t.dof), _np_ptr(t.axis),
-                                                 _np_ptr(t.sign), _np_ptr(t.rot), _np_ptr(t.xyz), t.n_dofs,
-                                                 _np_ptr(t.tip_body), _np_ptr(t.tip_offset)))
-            self._hand_loaded_for = ctx.value
+        t = self.tree
+        _lib.check(_lib.load().cdx_hand_load(ctx, t.n_bodies, _np_ptr(t.parent), _np_ptr(t.dof), _np_ptr(t.axis),
+                                             _np_ptr(t.sign), _np_ptr(t.rot), _np_ptr(t.xyz), t.n_dofs,
+                                             _np_ptr(t.tip_body), _np_ptr(t.tip_offset)))
+
+    def _owned(self):
+        """the pregrasp state is one per context: refuse to read or advance it after another optimizer re-initialised it"""
+        if self._ctx is None or self._generation is None:
+            raise RuntimeError("optimize() / _init() first")
+        if _lib.load().cdx_pregrasp_generation(self._ctx, None) != self._generation:
+            raise RuntimeError("another optimizer has re-initialised this GPIS context's pregrasp state; call optimize() again")
+
+    def set_tuning(self, groups=0, occupancy=0, use_graph=True):
+        """launch tuning of the device loop (cdx_pregrasp_set_tuning); results are bit-identical under every setting"""
+        self._tuning = (int(groups), int(occupancy), int(bool(use_graph)))
+        if self._ctx is not None:
+            _lib.check(_lib.load().cdx_pregrasp_set_tuning(self._ctx, *self._tuning))
+
+    def nan_count(self):
+        """(candidate-iterations whose total_loss was NaN since optimize() started, first such iteration or -1): the
+        reference's `print("NaN detected")` (:819) as a device-side record"""
+        self._owned()
+        n, first = ctypes.c_int64(0), ctypes.c_int(0)
+        _lib.check(_lib.load().cdx_pregrasp_nan_count(self._ctx, ctypes.byref(n), ctypes.byref(first), self._stream()))
+        return int(n.value), int(first.value)
 
     def _own_ctx(self):
         if self._ctx is None:
@@ -163,32 +185,38 @@ class ProbabilisticGraspOptimizer:
         if palm0.shape[0] != B or k0.shape != (B, 4) or T0.shape != (B, 4, 3) or q0.shape[1] != self.tree.n_dofs:
             raise ValueError("shapes: joint_angles [B,n_dofs], target_pose [B,4,3], compliance [B,4], palm_offset [B,6]")
         p = self._params(friction_mu)
-        _lib.check(_lib.load().cdx_pregrasp_init(self._ctx, ctypes.byref(p), B, _ptr(q0), _ptr(k0), _ptr(T0), _ptr(palm0),
-                                                 self._stream()))
+        lib = _lib.load()
+        _lib.check(lib.cdx_pregrasp_set_tuning(self._ctx, *(self._tuning or (0, 0, 1))))
+        _lib.check(lib.cdx_pregrasp_init(self._ctx, ctypes.byref(p), B, _ptr(q0), _ptr(k0), _ptr(T0), _ptr(palm0), self._stream()))
+        self._generation = lib.cdx_pregrasp_generation(self._ctx, None)
         self._B = B
         return B
 
     def evaluate(self):
         """closure() at the current iterate without stepping: total_loss [B], margin [B,4] and the gradients
         autograd leaves in q / compliance / target / palm (.grad after total_loss.sum().backward(), :767-768)."""
+        self._owned()
         B, dev, nd = self._B, self.device, self.tree.n_dofs
         out = [torch.empty(s, dtype=torch.float64, device=dev) for s in ((B,), (B, 4), (B, nd), (B, 4), (B, 4, 3), (B, 6))]
-        _lib.check(_lib.load().cdx_pregrasp_eval(self._ctx, *[_ptr(t) for t in out], self._stream()))
+        _lib.check(_lib.load().cdx_pregrasp_eval(self._ctx, B, *[_ptr(t) for t in out], self._stream()))
         return out
 
     def step(self, n_iters):
+        self._owned()
         _lib.check(_lib.load().cdx_pregrasp_run(self._ctx, int(n_iters), self._stream()))
 
     def current(self):
+        self._owned()
         B, dev, nd = self._B, self.device, self.tree.n_dofs
         out = [torch.empty(s, dtype=torch.float64, device=dev) for s in ((B, nd), (B, 4), (B, 4, 3), (B, 6))]
-        _lib.check(_lib.load().cdx_pregrasp_state(self._ctx, *[_ptr(t) for t in out], self._stream()))
+        _lib.check(_lib.load().cdx_pregrasp_state(self._ctx, B, *[_ptr(t) for t in out], self._stream()))
         return out
 
     def results(self):
+        self._owned()
         B, dev, nd = self._B, self.device, self.tree.n_dofs
         out = [torch.empty(s, dtype=torch.float64, device=dev) for s in ((B, nd), (B, 4), (B, 4, 3), (B, 6), (B, 4), (B,))]
-        _lib.check(_lib.load().cdx_pregrasp_results(self._ctx, *[_ptr(t) for t in out], self._stream()))
+        _lib.check(_lib.load().cdx_pregrasp_results(self._ctx, B, *[_ptr(t) for t in out], self._stream()))
         return out
 
     def optimize(self, init_joint_angles, target_pose, compliance, friction_mu, gpis, verbose=True):
@@ -205,6 +233,7 @@ class ProbabilisticGraspOptimizer:
     def argmin(self):
         """(best opt_value, GLOBAL candidate index = env_offset + local index), lowest index on ties; the cross-rank
         reduction of these pairs is compliancedex_b200.distributed.global_argmin."""
+        self._owned()
         out = torch.empty(2, dtype=torch.float64, device=self.device)
         self.argmin_into(out)
         v, i = out.tolist()
@@ -306,7 +335,8 @@ class KinGPISGraspOptimizer(ProbabilisticGraspOptimizer):
         """(opt_margin [B,4], iteration at which it was taken; -1 = never)"""
         m = torch.empty(self._B, 4, dtype=torch.float64, device=self.device)
         it = torch.empty(1, dtype=torch.int32, device=self.device)
-        _lib.check(_lib.load().cdx_pregrasp_latched_margin(self._ctx, _ptr(m), _ptr(it), self._stream()))
+        self._owned()
+        _lib.check(_lib.load().cdx_pregrasp_latched_margin(self._ctx, self._B, _ptr(m), _ptr(it), self._stream()))
         return m, it
 
     def optimize(self, joint_angles, target_pose, compliance, friction_mu, gpis, verbose=True):
@@ -347,7 +377,8 @@ class GPISGraspOptimizer(KinGPISGraspOptimizer):
         self.noise_seed, self.env_offset = int(noise_seed), int(env_offset)
         self.opt_value = self.opt_margin = None
         self._ctx = None
-        self._hand_loaded_for = None
+        self._generation = None
+        self._tuning = None
 
     def _bind(self, ctx):
         self._ctx = ctx                                                          # no hand to load

@@ -42,6 +42,12 @@ int cdx_destroy(cdx_ctx* ctx);
 int cdx_gpis_fit(cdx_ctx* ctx, const double* X1_dev, const double* y1_dev, const double* noise_dev,
                  double noise_scalar, int64_t N, double bias, int kernel, double sigma, void* stream);
 
+/* optional phase timing of cdx_gpis_fit / cdx_gpis_set_state (bench.py's fit workload): after cdx_gpis_fit_profile(ctx, 1)
+ * a fit records CUDA events at its phase boundaries; cdx_gpis_fit_profile_read synchronises `stream` and returns the
+ * milliseconds of {assembly (R, labels, E11), Cholesky, L^-1, E11^-1 = L^-T L^-1, alpha + packing} of the LAST fit. */
+int cdx_gpis_fit_profile(cdx_ctx* ctx, int enable);
+int cdx_gpis_fit_profile_read(cdx_ctx* ctx, double* ms_out5, void* stream);
+
 /* GPIS.load_state_data (gpis.py:162-168): adopt a stored state (y1 already bias-subtracted, E11 as stored) and
  * factorise it. */
 int cdx_gpis_set_state(cdx_ctx* ctx, const double* X1_dev, const double* y1_dev, const double* E11_dev, double R,
@@ -102,7 +108,8 @@ int cdx_sdf_backward(cdx_ctx* ctx, const void* grad_dist_dev, const void* points
  * (-1 for the root), dof[i] = column of q driving it or -1 (fixed), axis[i] in {0,1,2} with axis_sign[i] = +-1
  * (rigid_body.py:149-154), fixed_rot[i] = (Rz(yaw) Ry(pitch)) Rx(roll) of the joint origin as the float32 3x3 the
  * reference builds (rigid_body.py:142), xyz[i] float32.  tips: 4 link ids + offsets (robot_model.py:255-263).
- * All HOST pointers. */
+ * All HOST pointers.  The loaded hand's identity is kept on the context: loading the hand that is already there is free,
+ * loading a different one first waits for all work of the device (the kernels of a running optimisation read it). */
 int cdx_hand_load(cdx_ctx* ctx, int n_bodies, const int* parent, const int* dof, const int* axis,
                   const float* axis_sign, const float* fixed_rot, const float* xyz, int n_dofs, const int* tip_body,
                   const float* tip_offset);
@@ -158,28 +165,46 @@ typedef struct cdx_pregrasp_params {
  * Adam moments and the best-iterate buffers. q0 [B,16], compliance0 [B,4], target0 [B,4,3], palm0 [B,6]. */
 int cdx_pregrasp_init(cdx_ctx* ctx, const cdx_pregrasp_params* p, int64_t B, const double* q0_dev,
                       const double* compliance0_dev, const double* target0_dev, const double* palm0_dev, void* stream);
-/* n_iters iterations of closure + best-tracking + Adam + clamps (optimize_pregrasp.py:805-834), no host sync */
+/* n_iters iterations of closure + best-tracking + Adam + clamps (optimize_pregrasp.py:805-834), no host sync.  The loop is
+ * captured once per batch as a CUDA graph of up to 50 iterations and re-launched; iterations that do not
+ * fill a chunk are launched directly. */
 int cdx_pregrasp_run(cdx_ctx* ctx, int n_iters, void* stream);
-/* objective and its gradient at the CURRENT iterate without stepping (closure, :741-769) - for parity tests.
+/* launch tuning of cdx_pregrasp_run; results are bit-identical under every setting (tests/test_pregrasp_gpu.py).
+ * groups: candidate groups pipelined on separate stream pairs, 0 = auto (2 from 768 candidates), 1..4.
+ * occupancy: register allocation of the step kernel, 0 = auto by launch size, 2 = 255 registers, 3 = 168 registers.
+ * use_graph: 0 = launch every iteration from the host. */
+int cdx_pregrasp_set_tuning(cdx_ctx* ctx, int groups, int occupancy, int use_graph);
+/* NaN policy of the reference (print and continue, optimize_pregrasp.py:819) without the per-iteration host sync: the step
+ * kernel counts candidate-iterations whose total_loss was NaN since cdx_pregrasp_init.  Synchronises `stream`.
+ * count_host[0] = that count, first_iter_host[0] = first iteration that saw one (-1: none; may be NULL). */
+int cdx_pregrasp_nan_count(cdx_ctx* ctx, int64_t* count_host, int* first_iter_host, void* stream);
+/* number of cdx_pregrasp_init calls this context has seen (0: none) and the current batch size: the pregrasp state is one
+ * per context, so an optimizer object that shares a context checks that it still owns the state before reading it. */
+int64_t cdx_pregrasp_generation(cdx_ctx* ctx, int64_t* B_out);
+/* The read-back calls below take B = the number of candidates the caller's buffers were sized for; it must equal the
+ * batch of the last cdx_pregrasp_init on this context (CDX_ERR_ARG otherwise: no overrun if another optimizer took the
+ * context over with a different batch).
+ * objective and its gradient at the CURRENT iterate without stepping (closure, :741-769) - for parity tests.
  * total_loss [B], margin [B,4], grads: q [B,16], compliance [B,4], target [B,4,3], palm [B,6]; any may be NULL */
-int cdx_pregrasp_eval(cdx_ctx* ctx, double* total_loss_dev, double* margin_dev, double* gq_dev, double* gc_dev,
+int cdx_pregrasp_eval(cdx_ctx* ctx, int64_t B, double* total_loss_dev, double* margin_dev, double* gq_dev, double* gc_dev,
                       double* gt_dev, double* gp_dev, void* stream);
 /* the reference's 5-tuple (:839) + opt_value (:802); any may be NULL */
-int cdx_pregrasp_results(cdx_ctx* ctx, double* opt_q_dev, double* opt_compliance_dev, double* opt_target_dev,
+int cdx_pregrasp_results(cdx_ctx* ctx, int64_t B, double* opt_q_dev, double* opt_compliance_dev, double* opt_target_dev,
                          double* opt_palm_dev, double* opt_margin_dev, double* opt_value_dev, void* stream);
 /* current iterate (for tests) */
-int cdx_pregrasp_state(cdx_ctx* ctx, double* q_dev, double* compliance_dev, double* target_dev, double* palm_dev,
+int cdx_pregrasp_state(cdx_ctx* ctx, int64_t B, double* q_dev, double* compliance_dev, double* target_dev, double* palm_dev,
                        void* stream);
 /* KinGPISGraspOptimizer's `opt_margin` (:493): the WHOLE batch's margin [B,4] at the last iteration in which any candidate
  * improved, and that iteration's index (-1: never) in iter_dev[0] (int32).  flag = (opt_margin > 0).all() is the caller's. */
-int cdx_pregrasp_latched_margin(cdx_ctx* ctx, double* margin_dev, int* iter_dev, void* stream);
+int cdx_pregrasp_latched_margin(cdx_ctx* ctx, int64_t B, double* margin_dev, int* iter_dev, void* stream);
 /* local arg-min over opt_value with lowest-index tie-break: out_dev[0] = value, out_dev[1] = (double) GLOBAL index
  * (env_offset + local).  The cross-rank step is an all-gather of these 16 bytes. */
 int cdx_pregrasp_argmin(cdx_ctx* ctx, double* out_dev, void* stream);
 
-/* optional per-kernel timing (bench.py's roofline): after cdx_pregrasp_profile(ctx, 1) every cdx_pregrasp_run records
- * CUDA events around the four kernels of each iteration; cdx_pregrasp_profile_read synchronises `stream` and returns the
- * summed milliseconds {points, gpis extended query, gpis mean query, objective+Adam} and the iterations covered, then
+/* optional per-kernel timing (bench.py's roofline): after cdx_pregrasp_profile(ctx, 1) every cdx_pregrasp_run launches
+ * directly (no graph) in the SAME candidate groups as the timed loop and records CUDA events around each group's launches;
+ * cdx_pregrasp_profile_read synchronises `stream` and returns the summed milliseconds {wait for the overlapped mean query,
+ * gpis extended query, gpis mean query, objective+Adam step} and the number of (iteration, group) launches covered, then
  * clears the record. */
 int cdx_pregrasp_profile(cdx_ctx* ctx, int enable);
 int cdx_pregrasp_profile_read(cdx_ctx* ctx, double* ms_out4, int* n_iters, void* stream);

@@ -2,8 +2,9 @@
 
 Imports the *unmodified* reference (Ericcsr/ComplianceDex, mounted read-only at /root/reference) on
 CPU so that golden vectors can be generated from the reference's own code (see make_golden.py).
-This module only works in the build container: /root/reference does not exist on the GPU box, and
-nothing under tests/ -m gpu, bench.py or __graft_entry__.smoke() may call it.
+In the build container the reference is /root/reference; on the GPU box it is the git-ignored unmodified copy
+oracle/_ref/reference_py (oracle/build_ref_py.py).  Only goldens generation and bench.py's reference arm /
+cpu_baseline leg use this module - always on the HOST cores (CUDA is hidden from the process first).
 
 What is stubbed (none of it is arithmetic on the hot path):
   * open3d, matplotlib, torchsdf, cvxpy, cvxpylayers, pybullet_robot: imported at module top of
@@ -27,7 +28,17 @@ import xml.etree.ElementTree as ET
 import numpy as np
 import torch
 
-REF = os.environ.get("CDX_REFERENCE_ROOT", "/root/reference")
+def _reference_root():
+    """/root/reference in the build container; on the GPU box the git-ignored unmodified copy of the path's files that
+    oracle/build_ref_py.py made (oracle/_ref/reference_py travels with the snapshot like oracle/_ref/torchsdf_ref.so)"""
+    for cand in (os.environ.get("CDX_REFERENCE_ROOT"), "/root/reference",
+                 os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "reference_py")):
+        if cand and os.path.isfile(os.path.join(cand, "gpis.py")):
+            return cand
+    return "/root/reference"
+
+
+REF = _reference_root()
 LEAP_URDF = f"{REF}/pybullet_robot/src/pybullet_robot/robots/leap_hand/assets/leap_hand/robot.urdf"
 ALLEGRO_URDF = f"{REF}/pybullet_robot/src/pybullet_robot/robots/allegro_hand/models/allegro_hand_description_left.urdf"
 

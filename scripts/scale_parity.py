@@ -1,0 +1,110 @@
+"""Config-scale parity statistics (runs on the GPU box): the CUDA pregrasp path at the full C2 / C5 batch against
+ (a) tests/golden/pregrasp_scale_{c2,c5}.npz - the REAL reference's trajectories for the first rows of that batch, and
+ (b) the oracle port on the host cores for the full C2 batch (optional, --oracle).
+Writes gpurun_out/scale_parity_<case>.json: arg-min identity, fraction of candidates whose opt_value agrees to 1e-4,
+the iteration at which each candidate's total_loss first leaves 1e-4, what the disagreeing candidates look like."""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def run_cuda(hand, state, B, iters, per_iteration=True):
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path(f"{state}_state"))
+    doc = load_hand(hand)
+    d = np.load(state_path(f"{state}_state"))
+    q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=100)
+    opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                      palm_offset=palm, num_iters=iters, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
+                                      com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True, noise_seed=2024)
+    losses = None
+    if per_iteration:
+        opt._init(q0.cuda(), T0.cuda(), k0.cuda(), 1, gp)
+        rows = []
+        for _ in range(iters):
+            rows.append(opt.evaluate()[0].cpu().numpy())
+            opt.step(1)
+        losses = np.stack(rows)
+    res = opt.optimize(q0.cuda(), T0.cuda(), k0.cuda(), 1, gp, verbose=False)
+    return losses, opt.opt_value.cpu().numpy(), [t.cpu().numpy() for t in res], opt.argmin(), opt.nan_count(), (q0, T0, k0, palm, doc)
+
+
+def compare(tag, losses, ov, ref_losses, ref_ov):
+    n = ref_ov.shape[0]
+    ov = ov[:n]
+    fin = np.isfinite(ref_ov) & np.isfinite(ov)
+    rel = np.abs(ov - ref_ov) / np.maximum(np.abs(ref_ov), 1.0)
+    out = {"against": tag, "candidates": int(n), "both_finite": int(fin.sum()),
+           "nan_or_inf_pattern_identical": bool(np.array_equal(np.isfinite(ov), np.isfinite(ref_ov))),
+           "opt_value_within_1e-4": float((rel[fin] <= 1e-4).mean()), "opt_value_within_1e-3": float((rel[fin] <= 1e-3).mean()),
+           "opt_value_within_1e-2": float((rel[fin] <= 1e-2).mean()), "opt_value_rel_median": float(np.median(rel[fin])),
+           "opt_value_rel_max": float(rel[fin].max()),
+           "argmin_ref": int(np.nanargmin(np.where(np.isfinite(ref_ov), ref_ov, np.inf))),
+           "argmin_cuda_same_rows": int(np.nanargmin(np.where(np.isfinite(ov), ov, np.inf)))}
+    out["argmin_identical"] = out["argmin_ref"] == out["argmin_cuda_same_rows"]
+    order_ref, order_cu = np.argsort(np.where(np.isfinite(ref_ov), ref_ov, np.inf)), np.argsort(np.where(np.isfinite(ov), ov, np.inf))
+    out["best5_ref"] = [(int(i), float(ref_ov[i])) for i in order_ref[:5]]
+    out["best5_cuda"] = [(int(i), float(ov[i])) for i in order_cu[:5]]
+    if losses is not None and ref_losses is not None:
+        L = losses[:, :n]
+        r = np.abs(L - ref_losses) / np.maximum(np.abs(ref_losses), 1.0)
+        r = np.where(np.isnan(r), 0.0, r)
+        bad = r > 1e-4
+        first = np.where(bad.any(axis=0), bad.argmax(axis=0), L.shape[0])
+        out["iteration_first_leaving_1e-4"] = {"min": int(first.min()), "p10": float(np.percentile(first, 10)),
+                                                 "median": float(np.median(first)), "never": float((first == L.shape[0]).mean())}
+        out["max_rel_by_iteration"] = {str(s): float(r[s].max()) for s in (0, 5, 10, 20, 50, 100, 150, L.shape[0] - 1) if s < L.shape[0]}
+        out["median_rel_by_iteration"] = {str(s): float(np.median(r[s])) for s in (0, 5, 10, 20, 50, 100, 150, L.shape[0] - 1) if s < L.shape[0]}
+        out["nan_pattern_identical_every_iteration"] = bool(np.array_equal(np.isnan(L), np.isnan(ref_losses)))
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("case", choices=["c2", "c5"])
+    ap.add_argument("--oracle", type=int, default=0, help="also run the oracle port on this many leading candidates (C2: 1024)")
+    a = ap.parse_args()
+    cfg = {"c2": ("leap", "mug", 1024, 200), "c5": ("allegro", "hammer", 8192, 500)}[a.case]
+    hand, state, B, iters = cfg
+    g = np.load(os.path.join(ROOT, "tests", "golden", f"pregrasp_scale_{a.case}.npz"))
+    t0 = time.time()
+    losses, ov, res, best, nans, inputs = run_cuda(hand, state, B, iters)
+    out = {"case": a.case, "hand": hand, "state": state, "B": B, "iters": iters, "cuda_seconds": time.time() - t0,
+           "cuda_argmin_full_batch": {"value": best[0], "index": best[1]}, "nan_candidate_iterations": nans[0],
+           "vs_reference": compare("reference fixture (first %d rows)" % g["opt_value"].shape[0], losses, ov, g["losses"], g["opt_value"])}
+    if a.oracle:
+        from compliancedex_b200 import hand_path, state_path
+        from oracle.gpis_oracle import GPISOracle
+        from oracle.pregrasp_oracle import PregraspOracle
+        n = a.oracle
+        q0, T0, k0, palm, doc = inputs
+        go = GPISOracle(0.08, 1.0).load_npz(state_path(f"{state}_state"))
+        torch.set_num_threads(os.cpu_count())
+        o = PregraspOracle(hand_path(hand), palm[:n], iters, mass=0.1, noise_seed=2024)
+        rows = []
+        t0 = time.time()
+        o.optimize(q0[:n], T0[:n], k0[:n], 1, go, record=lambda s, t, gr: rows.append(t.numpy().copy()))
+        out["oracle_seconds"] = time.time() - t0
+        ref_losses = np.stack(rows)
+        ref_ov = np.full(n, np.inf)
+        for s in range(21, iters):
+            ref_ov = np.where(ref_losses[s] < ref_ov, ref_losses[s], ref_ov)
+        out["vs_oracle_port"] = compare("oracle port (first %d rows, host cores of this box)" % n, losses, ov, ref_losses, ref_ov)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    path = os.path.join(ROOT, "gpurun_out", f"scale_parity_{a.case}.json")
+    json.dump(out, open(path, "w"), indent=1)
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()

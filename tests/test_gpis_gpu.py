@@ -174,3 +174,29 @@ def test_full_size_properties():
     assert torch.isfinite(m).all() and (s ** 2 <= float(g.R) ** 3 * (1 + 1e-9)).all()
     n = g.compute_normal(X[:4096])
     assert (n.norm(dim=1) - 1).abs().max() < 1e-6
+
+
+@pytest.mark.parametrize("name", ["lego", "hammer"])
+def test_normal_index_and_multinormals_against_reference_golden(name, golden_dir):
+    """GPIS.compute_normal(X2, index) (gpis.py:63-87, index branch) and GPIS.compute_multinormals (gpis.py:89-111) through
+    cdx_gpis_query_weights, vs goldens produced by the reference's own gpis.py (oracle/make_golden_normals.py)."""
+    ref = np.load(os.path.join(golden_dir, "gpis_normals_index.npz"))
+    g = _gpis(name)
+    X = torch.from_numpy(ref[f"{name}_X"]).cuda()
+    for tag in ["prefix", "suffix", "scattered", "single"]:
+        n, w = g.compute_normal(X, ref[f"{name}_{tag}_index"].tolist())
+        assert tuple(n.shape) == (48, 3) and n.dtype == torch.float64
+        assert np.abs(n.cpu().numpy() - ref[f"{name}_{tag}_normal"]).max() <= 1e-5, tag
+        wr = float(ref[f"{name}_{tag}_weight"])
+        assert abs(float(w) - wr) <= 1e-5 * abs(wr), tag
+    nb, _ = g.compute_normal(X[:40].reshape(10, 4, 3), ref[f"{name}_prefix_index"].tolist())
+    assert tuple(nb.shape) == (10, 4, 3)
+    assert np.abs(nb.cpu().numpy() - ref[f"{name}_prefix_normal_batched"]).max() <= 1e-5
+    for S in (3, 5):
+        g.fraction = None                                   # the row subsets are cached by the first call (gpis.py:96)
+        nm, wm = g.compute_multinormals(X, S)
+        assert [len(i) for i in g.indices] == ref[f"{name}_multi{S}_sizes"].tolist()
+        assert [i[0] for i in g.indices] == ref[f"{name}_multi{S}_first"].tolist()
+        assert tuple(nm.shape) == (48, S, 3) and tuple(wm.shape) == (S,)
+        assert np.abs(nm.cpu().numpy() - ref[f"{name}_multi{S}_normals"]).max() <= 1e-5
+        assert np.abs(wm.cpu().numpy() - ref[f"{name}_multi{S}_weights"]).max() <= 1e-5 * np.abs(ref[f"{name}_multi{S}_weights"]).max()

@@ -122,3 +122,40 @@ def test_refit_invalidates_slices():
             outs.append(g.pred(X)[1].clone())
     assert torch.equal(outs[0], outs[2])
     assert not torch.equal(outs[0], outs[1])
+
+
+def test_c3_size_against_oracle_sample():
+    """The size bench.py's gpis_c3 workload runs (N = 4,096 synthetic, auto mode -> INT8 slices on tcgen05): 1,536 of 2^17
+    queries (uniform ones, ones next to training points, ones ON training points) re-evaluated by the oracle - one
+    4,096^2 LU on the host - and the whole batch against the FP64 tensor-MMA path.  Gates: BASELINE.json."""
+    from compliancedex_b200 import GPIS, _lib
+    from compliancedex_b200.synthetic import synthetic_queries, synthetic_training_set
+    from oracle.gpis_oracle import GPISOracle
+    N, M = 4096, 1 << 17
+    X1, y1, noise = synthetic_training_set(N, seed=0)
+    g = GPIS(0.08, 1.0)
+    g.fit(X1.cuda(), y1.cuda(), noise.cuda())
+    X = synthetic_queries(M, 0, M)
+    pick = torch.randint(0, N, (1024,), generator=torch.Generator().manual_seed(1))
+    X[:512] = X1[pick[:512]] + 1e-4 * torch.randn(512, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(2))
+    X[512:1024] = X1[pick[512:]]
+    Xd = X.cuda()
+    lib = _lib.load()
+    before = lib.cdx_launch_count(g._ctx)
+    with torch.no_grad():
+        m1, s1 = g.pred(Xd)
+    assert lib.cdx_launch_count(g._ctx) - before == 5        # rowscale + slice + points + gpis_std_i8_kernel + mean: the INT8 path ran
+    n1 = g.compute_normal(Xd)
+    with torch.no_grad():
+        g.set_var_mode(-1)
+        m0, s0 = g.pred(Xd)
+    prior = float(g.R) ** 3
+    assert ((s1 ** 2 - s0 ** 2).abs().max() / prior).item() <= 5e-8
+    idx = torch.cat([torch.arange(0, 1024), torch.arange(1024, M, (M - 1024) // 512)[:512]])
+    o = GPISOracle(0.08, 1.0).fit(X1, y1, noise)
+    mo, so = o.pred_diag(X[idx])
+    no = o.compute_normal(X[idx])
+    assert ((s1[idx].cpu() ** 2 - so ** 2).abs().max() / prior).item() <= 1e-6
+    assert ((m1[idx].cpu() - mo).abs().max() / mo.abs().max()).item() <= 1e-5
+    assert ((m1[idx].cpu() - mo).abs() / mo.abs().clamp(min=1e-3)).max().item() <= 1e-5
+    assert (n1[idx].cpu() - no).abs().max().item() <= 1e-5

@@ -57,6 +57,28 @@ def test_gpis_oracle_fit(kern, golden_dir):
     assert np.abs(s.numpy() - g[f"{kern}_std"]).max() < 1e-9
 
 
+@pytest.mark.parametrize("name", ["lego", "hammer"])
+def test_gpis_oracle_normal_index_and_multinormals(name, golden_dir):
+    """compute_normal(X2, index) (gpis.py:66-69,78-80,84-87) and compute_multinormals (gpis.py:89-111) vs the reference"""
+    g = np.load(os.path.join(golden_dir, "gpis_normals_index.npz"))
+    o = GPISOracle(0.08, 1.0).load_npz(os.path.join(STATES, f"{name}_state.npz"))
+    X = torch.from_numpy(g[f"{name}_X"])
+    for tag in ["prefix", "suffix", "scattered", "single"]:
+        n, w = o.compute_normal(X, g[f"{name}_{tag}_index"].tolist())
+        assert np.abs(n.numpy() - g[f"{name}_{tag}_normal"]).max() < 1e-9
+        assert abs(float(w) - float(g[f"{name}_{tag}_weight"])) <= 1e-9 * abs(float(g[f"{name}_{tag}_weight"]))
+    nb, _ = o.compute_normal(X[:40].reshape(10, 4, 3), g[f"{name}_prefix_index"].tolist())
+    assert tuple(nb.shape) == (10, 4, 3) and np.abs(nb.numpy() - g[f"{name}_prefix_normal_batched"]).max() < 1e-9
+    for S in (3, 5):
+        subsets = o.nested_row_subsets(S)
+        assert [len(i) for i in subsets] == g[f"{name}_multi{S}_sizes"].tolist()
+        assert [i[0] for i in subsets] == g[f"{name}_multi{S}_first"].tolist()
+        nm, wm = o.compute_multinormals(X, S)
+        assert tuple(nm.shape) == (48, S, 3)
+        assert np.abs(nm.numpy() - g[f"{name}_multi{S}_normals"]).max() < 1e-9
+        assert np.abs(wm.numpy() - g[f"{name}_multi{S}_weights"]).max() < 1e-9
+
+
 def test_gpis_oracle_viz_grid(golden_dir):
     g = np.load(os.path.join(golden_dir, "gpis_viz_banana6.npz"))
     o = GPISOracle(0.08, 1.0).load_npz(os.path.join(STATES, "banana_state.npz"))

@@ -108,7 +108,7 @@ def test_sharding_invariance(golden_dir):
 
 
 @pytest.mark.parametrize("groups", [2, 3, 4])
-def test_candidate_groups_are_bit_identical(groups, monkeypatch):
+def test_candidate_groups_are_bit_identical(groups):
     """cdx_pregrasp_run pipelines the candidates in groups on separate streams (default 2 from 768 candidates): whatever the
     group count, every candidate's trajectory is the one it has in a single group."""
     from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
@@ -121,11 +121,11 @@ def test_candidate_groups_are_bit_identical(groups, monkeypatch):
     q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=7)
 
     def run(G):
-        monkeypatch.setenv("CDX_PG_GROUPS", str(G))
         opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
                                           palm_offset=palm, num_iters=30, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
                                           com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True,
                                           noise_seed=11)
+        opt.set_tuning(groups=G)
         res = [t.clone() for t in opt.optimize(q0.cuda(), T0.cuda(), k0.cuda(), 1.0, gp, verbose=False)]
         return res + [opt.opt_value.clone()]
 
@@ -136,9 +136,9 @@ def test_candidate_groups_are_bit_identical(groups, monkeypatch):
 
 
 @pytest.mark.parametrize("B", [101, 2500])
-def test_step_kernel_occupancy_variants_are_bit_identical(B, monkeypatch):
+def test_step_kernel_occupancy_variants_are_bit_identical(B):
     """pg_step_kernel is compiled twice (2 resident CTAs per SM / 255 registers for launches of one wave, 3 / 168 registers
-    for larger ones; CDX_PG_OCC forces one): same arithmetic, so the choice - which depends on the launch size, i.e. on the
+    for larger ones; cdx_pregrasp_set_tuning forces one): same arithmetic, so the choice - which depends on the launch size, i.e. on the
     shard - never shows in the results.  B = 101 also has a warp whose second candidate lies past the end of the batch."""
     from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
     from compliancedex_b200.synthetic import surface_center, synthetic_candidates
@@ -149,11 +149,11 @@ def test_step_kernel_occupancy_variants_are_bit_identical(B, monkeypatch):
     q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=9)
 
     def run(occ):
-        monkeypatch.setenv("CDX_PG_OCC", str(occ))
         opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
                                           palm_offset=palm, num_iters=25, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
                                           com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True,
                                           noise_seed=5)
+        opt.set_tuning(occupancy=occ)
         res = [t.clone() for t in opt.optimize(q0.cuda(), T0.cuda(), k0.cuda(), 1.0, gp, verbose=False)]
         return res + [opt.opt_value.clone()]
 
@@ -161,6 +161,115 @@ def test_step_kernel_occupancy_variants_are_bit_identical(B, monkeypatch):
     three = run(3)
     for a, b in zip(two, three):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("B,iters", [(100, 107), (1030, 53)])
+def test_graph_loop_is_bit_identical_to_direct_launches(B, iters):
+    """cdx_pregrasp_run replays the loop as a CUDA graph of 50-iteration chunks (+ directly launched remainder); the captured
+    nodes read the chunk's base iteration from device memory.  Same results as launching every iteration from the host,
+    also when the cached graph is re-used for a second run with other inputs, and after a run of a different length."""
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path("mug_state"))
+    doc = load_hand("leap")
+    d = np.load(state_path("mug_state"))
+    center = surface_center(d["X1"], d["y1"])
+
+    def make(seed):
+        q0, T0, k0, palm = synthetic_candidates(doc, B, center, seed=seed)
+        opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                          palm_offset=palm, num_iters=iters, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
+                                          com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True, noise_seed=3)
+        return opt, q0.cuda(), T0.cuda(), k0.cuda()
+
+    def run(opt, q0, T0, k0, graph):
+        opt.set_tuning(use_graph=graph)
+        res = [t.clone() for t in opt.optimize(q0, T0, k0, 1.0, gp, verbose=False)]
+        return res + [opt.opt_value.clone()] + [t.clone() for t in opt.current()]
+
+    for seed in (21, 22):                       # the second seed re-uses the executable graph captured for the first
+        opt, q0, T0, k0 = make(seed)
+        direct = run(opt, q0, T0, k0, False)
+        graphed = run(opt, q0, T0, k0, True)
+        for a, b in zip(direct, graphed):
+            assert torch.equal(a, b)
+    # split runs: 60 iterations (graph chunk + remainder), then the rest, continue the same trajectory
+    opt, q0, T0, k0 = make(22)
+    opt.set_tuning(use_graph=True)
+    opt._init(q0, T0, k0, 1.0, gp)
+    opt.step(min(60, iters))
+    opt.step(iters - min(60, iters))
+    for a, b in zip(opt.results() + opt.current(), graphed[:5] + [graphed[5]] + graphed[6:]):
+        assert torch.equal(a, b)
+
+
+def test_two_hands_share_one_gpis_context():
+    """Optimizers with different hands (Leap, Allegro: both 16 dof) on ONE GPIS object alternate: each run uses its own
+    kinematics (the context keeps the loaded hand's identity), and an optimizer whose state was taken over refuses to read
+    it instead of returning the other batch."""
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    d = np.load(state_path("mug_state"))
+    center = surface_center(d["X1"], d["y1"])
+
+    def make(hand, B, gp_seed):
+        doc = load_hand(hand)
+        q0, T0, k0, palm = synthetic_candidates(doc, B, center, seed=gp_seed)
+        opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                          palm_offset=palm, num_iters=12, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
+                                          optimize_palm=True, noise_seed=1)
+        return opt, q0.cuda(), T0.cuda(), k0.cuda()
+
+    shared = GPIS(0.08, 1.0)
+    shared.load_state_data(state_path("mug_state"))
+    a, qa, Ta, ka = make("leap", 24, 1)
+    b, qb, Tb, kb = make("allegro", 40, 2)
+    ra1 = [t.clone() for t in a.optimize(qa, Ta, ka, 1.0, shared, verbose=False)]
+    rb = [t.clone() for t in b.optimize(qb, Tb, kb, 1.0, shared, verbose=False)]
+    with pytest.raises(RuntimeError):
+        a.results()                                      # b owns the context's pregrasp state now (and it holds 40 candidates)
+    ra2 = a.optimize(qa, Ta, ka, 1.0, shared, verbose=False)
+    for x, y in zip(ra1, ra2):
+        assert torch.equal(x, y)                         # not Allegro's kinematics
+    own = GPIS(0.08, 1.0)
+    own.load_state_data(state_path("mug_state"))
+    b2, _, _, _ = make("allegro", 40, 2)
+    for x, y in zip(rb, b2.optimize(qb, Tb, kb, 1.0, own, verbose=False)):
+        assert torch.equal(x, y)
+    # the C ABI itself rejects buffers sized for another batch
+    import ctypes
+    from compliancedex_b200 import _lib
+    buf = torch.empty(24, dtype=torch.float64, device="cuda")
+    rc = _lib.load().cdx_pregrasp_results(own._ctx, 24, None, None, None, None, None, ctypes.c_void_p(buf.data_ptr()), None)
+    assert rc == _lib.CDX_ERR_ARG
+
+
+def test_nan_record():
+    """the reference prints "NaN detected" and continues (optimize_pregrasp.py:819); here the step kernel counts NaN
+    candidate-iterations on the device.  One candidate starts from a NaN joint angle: it stays NaN for every iteration, the
+    others are untouched (bit-identical to a run without it)."""
+    from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
+    from compliancedex_b200.synthetic import surface_center, synthetic_candidates
+    gp = GPIS(0.08, 1.0)
+    gp.load_state_data(state_path("mug_state"))
+    doc = load_hand("leap")
+    d = np.load(state_path("mug_state"))
+    q0, T0, k0, palm = synthetic_candidates(doc, 20, surface_center(d["X1"], d["y1"]), seed=4)
+    opt = ProbabilisticGraspOptimizer("leap", ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
+                                      palm_offset=palm, num_iters=30, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
+                                      optimize_palm=True, noise_seed=8)
+    clean = [t.clone() for t in opt.optimize(q0.cuda(), T0.cuda(), k0.cuda(), 1.0, gp, verbose=False)]
+    assert opt.nan_count() == (0, -1)
+    qn = q0.clone()
+    qn[7, 3] = float("nan")
+    res = opt.optimize(qn.cuda(), T0.cuda(), k0.cuda(), 1.0, gp, verbose=False)
+    assert opt.nan_count() == (30, 0)
+    keep = [i for i in range(20) if i != 7]
+    for x, y in zip(clean, res):
+        assert torch.equal(x[keep], y[keep])
+    assert torch.isinf(opt.opt_value[7])                 # a NaN loss never becomes the best iterate (:822-829)
+    assert opt.argmin()[1] != 7
 
 
 def test_distinct_pregrasp_coefficients_against_oracle(golden_dir):
