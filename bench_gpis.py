@@ -99,23 +99,29 @@ def run_gpis_c3(args, rank, world, local):
     peaks, src = measured_peaks()
     fp64_equiv = flop_per_query * M / (kernel_ms * 1e-3) / 1e12    # algorithmic FP64 flop of this rank's launch / its time
     dmma_peak = pipes.get("dmma_m8n8k4_tflops")
-    info = g.std_path_info() if hasattr(g, "std_path_info") else {}
     i8 = args.var_mode != -1 and 1024 <= Np <= 8192
     if i8:
         S = args.var_mode if args.var_mode >= 4 else 5
-        ops_per_query = info.get("int8_ops_per_query") or 2 * (S * (S + 1) // 2) * 64 * 64 * ((Np // 64) * (Np // 64 + 1) // 2)
+        # INT8 multiply-adds the kernel ISSUES per query (cdx_query_i8x.cu, CTA pair): S(S+1)/2 slice pairs x 128-row tiles x
+        # 32-point stages; round r of a pair walks the k chunks up to the diagonal of its LAST tile
+        NT, NC = (Np + 127) // 128, Np // 32
+        stages = sum(min((r * 2 + 2) * 4, NC) for r in range((NT + 1) // 2)) * 2
+        ops_per_query = 2 * (S * (S + 1) // 2) * 128 * 32 * stages
+        useful_ops_per_query = 2 * (S * (S + 1) // 2) * (N * (N + 1) // 2)
         achieved = ops_per_query * M / (kernel_ms * 1e-3) / 1e12
         peak = i8_peak(pipes)
-        roof = {"bound": "tensor", "kernel": info.get("kernel", "gpis_std_i8_kernel<%d>" % S) + " (tcgen05 kind::i8, INT32 accumulators in TMEM)",
+        roof = {"bound": "tensor", "kernel": "gpis_std_i8x_kernel<%d, CTA pair> (tcgen05.mma.cta_group::2 kind::i8, INT32 accumulators in TMEM)" % S,
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                 "peak_source": "tcgen05.mma kind::i8 issue rate MEASURED in this run by csrc/cdx_pipebench (best of the operand "
                                "shapes it times; MEASURED_PEAKS.json has no INT8 figure, its bf16 %s = %.0f TF/s); achieved counts "
                                "the INT8 multiply-adds the kernel issues x 2 (TOP/s)" % (src, peaks.get("bf16_tflops", 0)),
-                "int8_ops_per_query": ops_per_query, "slices": S,
+                "int8_ops_per_query": ops_per_query, "int8_ops_per_query_lower_triangle_only": useful_ops_per_query, "slices": S,
                 "algorithmic_fp64_tflops": fp64_equiv, "fp64_dmma_peak_tflops": dmma_peak,
                 "speedup_over_fp64_dmma_peak_rate": fp64_equiv / dmma_peak if dmma_peak else None,
                 "note": "the FP64 contraction L^-1 k* (N^2 flop/query) is evaluated as error-free INT8 slice products "
-                        "(S(S+1)/2 byte-slice pairs); mean / grad_mean come from the separate TMA-staged FP64 mean kernel"}
+                        "(S(S+1)/2 byte-slice pairs); the FP64 generation of the k* slices does not overlap the INT8 MMAs on this "
+                        "chip (DESIGN.md section 4: FP64 instructions and tcgen05 MMAs serialise); mean / grad_mean come from the "
+                        "separate TMA-staged FP64 mean kernel"}
     else:
         roof = {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,128,unit> (FP64 DMMA)", "achieved": fp64_equiv,
                 "peak": dmma_peak, "unit": "TFLOP/s", "frac": (fp64_equiv / dmma_peak) if dmma_peak else None,

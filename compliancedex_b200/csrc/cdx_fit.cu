@@ -191,7 +191,7 @@ int gpis_reserve(cdx_ctx* ctx, int64_t N) {
   g.N = N;
   g.Np = Np;
   g.ready = false;
-  g.i8_S = 0;   // the sliced copy of U belongs to the previous state
+  g.i8x_S = 0;   // the sliced copy of U belongs to the previous state
   return CDX_OK;
 }
 
@@ -333,7 +333,7 @@ extern "C" int cdx_destroy(cdx_ctx* ctx) {
   cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.dR2); cudaFree(g.flag);
   cudaFree(ctx->hx); cudaFree(ctx->hout);
   for (int i = 0; i < 6; i++) if (g.fit_ev[i]) cudaEventDestroy(g.fit_ev[i]);
-  cdx_i8_free(ctx);
+  cdx_i8x_free(ctx);
   cdx_pregrasp_free(ctx);
   cdx_sdf_free(ctx);
   delete ctx;

@@ -66,15 +66,17 @@ struct cdx_gpis_state {
   int* flag = nullptr;      // device int: first non-SPD column + 1 (0 = ok)
   int64_t cap = 0;          // allocated Np
   bool ready = false;
-  // INT8-sliced copy of U for the tcgen05 std path (cdx_query_i8.cu), built lazily at the first eligible query
-  int8_t* i8_B = nullptr;   // [Np/64][Np/64][S][4][64][16]
-  double* i8_sb = nullptr;  // [Np] 2^e_n (0 on padded rows)
-  int* i8_eb = nullptr;     // [Np]
-  double* i8_pts = nullptr; // [Np,4] (-2x,-2y,-2z,|x|^2)
-  double* i8_bb = nullptr;  // [6] bounding box of the training points
-  int i8_S = 0;             // slices the copy was built with (0 = not built for the current state)
-  size_t i8_cap = 0;        // bytes allocated for i8_B
-  int64_t i8_np = 0;        // Np the small arrays were allocated for
+  // INT8-sliced copy of U for the tcgen05 std path (cdx_query_i8x.cu), built lazily at the first eligible query: the digits
+  // tiled in the shared-memory image of the MMA's A operand
+  int8_t* i8x_A = nullptr;  // [row tiles 128][Np/32][S][2][128][16]
+  double* i8x_sb = nullptr; // [rows] 2^e_n (0 on padded rows)
+  int* i8x_eb = nullptr;
+  double* i8x_pts = nullptr;
+  double* i8x_bb = nullptr;
+  int i8x_S = 0;
+  size_t i8x_cap = 0;
+  int64_t i8x_rows = 0;
+  int i8_variant = 3;       // cdx_gpis_set_i8_variant: 3 = CTA pair (cta_group::2), 1 = 2-CTA cluster sharing k* over DSMEM, 2 = no cluster
   // optional phase timing of the fit (cdx_gpis_fit_profile): events at the phase boundaries
   bool fit_prof = false;
   cudaEvent_t fit_ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -175,10 +177,10 @@ __device__ __forceinline__ void cdx_cp_async_wait() { asm volatile("cp.async.wai
 // ta: A is stored [K,M] (else [M,K]);  tb: B is stored [K,N] (else [N,K], i.e. C = A B^T).
 // ktri: skip k ranges known to be zero (1: k >= n0, 2: k < m0+64, 3: k >= m0; 0: none).
 // lower_only: skip tiles strictly above the diagonal (requires M == N tiles aligned).  batch via strides.
-// tcgen05 INT8-sliced std query (cdx_query_i8.cu); S slices in {4,5,6}
+// tcgen05 INT8-sliced std query (cdx_query_i8x.cu); S slices in {4,5,6}
 bool cdx_i8_eligible(const cdx_ctx* ctx);
-int cdx_i8_std(cdx_ctx* ctx, int S, const double* X, int64_t M, double* stdv, cudaStream_t st);
-void cdx_i8_free(cdx_ctx* ctx);
+int cdx_i8x_std(cdx_ctx* ctx, int S, int cluster, const double* X, int64_t M, double* stdv, cudaStream_t st);
+void cdx_i8x_free(cdx_ctx* ctx);
 void cdx_sdf_free(cdx_ctx* ctx);
 
 int cdx_dgemm(cdx_ctx* ctx, bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int64_t lda,

@@ -1,7 +1,7 @@
 // Pipe-rate microbenchmarks for the FP64 units this path runs on (MEASURED_PEAKS.json has only HBM and bf16).
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/cdx_pipebench cdx_pipebench.cu
 // Prints one JSON object: DFMA TF/s, DMMA(m8n8k4) TF/s, both interleaved, FP32 FFMA TF/s, MUFU.RSQ rate, and the
-// tcgen05.mma kind::i8 issue rate (TOP/s) for the operand shapes of gpis_std_i8_kernel.
+// tcgen05.mma kind::i8 issue rate (TOP/s) for the operand shapes of gpis_std_i8x_kernel.
 #include <cstdio>
 #include <cuda_runtime.h>
 
@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256) pipe_kernel(double* out, int iters) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
-// The k* generator of gpis_std_i8_kernel in isolation (cdx_query_i8.cu, generator warps): per (query, training point) pair
+// The k* generator of gpis_std_i8x_kernel in isolation (cdx_query_i8x.cu, generator warps): per (query, training point) pair
 // 4 FP64 for the expanded squared distance, float rsqrt seed by bit moves, 1 Newton step (3 FP64), cubic + fixed-point magic
 // (2 FP64), then the 4x4 byte transposes.  No tensor memory, no barriers: measures what the FP64 / ALU / XU pipes sustain for
 // this instruction mix at the kernel's occupancy (512 generator threads per SM).
@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(CAP) gen_kernel(const double* __restrict__ pts
   out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 
-// ---- tcgen05 kind::i8 issue rate (the roof of gpis_std_i8_kernel): one CTA per SM, one thread issues `count` MMAs of
+// ---- tcgen05 kind::i8 issue rate (the roof of gpis_std_i8x_kernel): one CTA per SM, one thread issues `count` MMAs of
 // M=128 x N x K=32 onto two alternating TMEM accumulators, operands constant in shared memory (SS) or A in tensor memory (TS)
 __device__ __forceinline__ unsigned pb_s32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ unsigned long long pb_desc(unsigned saddr, unsigned lbo, unsigned sbo) {

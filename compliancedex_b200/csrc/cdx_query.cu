@@ -387,13 +387,14 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
                : launch_var<KERNEL, 64, true, 128>(ctx, X, M, mean, gmean, stdv, gstd, st);
   }
   if (stdv) {
-    // large TPS states: std on the INT8 tensor cores (tcgen05, cdx_query_i8.cu), mean / grad_mean by the
+    // large TPS states: std on the INT8 tensor cores (tcgen05, cdx_query_i8x.cu), mean / grad_mean by the
     // TMA-staged mean kernel.  auto = 5 slices (|d var| < 1e-8 prior measured; the gate is 1e-6 prior).
     const int vm = g.var_mode;
     // the choice depends on the STATE only, never on the batch: a query's result is bit-identical for every chunking / shard
     const bool i8 = vm != -1 && cdx_i8_eligible(ctx) && (vm >= 4 || g.Np >= 1024);
     if (i8) {
-      int rc = cdx_i8_std(ctx, vm >= 4 ? vm : 5, X, M, stdv, st);
+      const int S = vm >= 4 ? vm : 5;
+      int rc = cdx_i8x_std(ctx, S, g.i8_variant == 1 ? 2 : (g.i8_variant == 3 ? 3 : 1), X, M, stdv, st);
       if (rc) return rc;
       if (mean || gmean) return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
       return CDX_OK;

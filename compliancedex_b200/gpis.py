@@ -94,6 +94,8 @@ class GPIS:
             self._ctx = _lib.new_context(idx)
             self._device = idx
             _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, getattr(self, "_var_mode", 0)))
+            if hasattr(self, "_i8_variant"):
+                _lib.check(_lib.load().cdx_gpis_set_i8_variant(self._ctx, self._i8_variant))
         return self._ctx
 
     def _check_factorisation(self):
@@ -117,6 +119,13 @@ class GPIS:
         self._var_mode = int(mode)
         if self._ctx is not None:
             _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, self._var_mode))
+
+    def set_i8_variant(self, variant):
+        """launch shape of the tcgen05 INT8 std path (include/cdx.h cdx_gpis_set_i8_variant): 3 CTA pair with
+        tcgen05.mma.cta_group::2 (default), 1 two-CTA cluster exchanging k* over distributed shared memory, 2 no cluster."""
+        self._i8_variant = int(variant)
+        if self._ctx is not None:
+            _lib.check(_lib.load().cdx_gpis_set_i8_variant(self._ctx, self._i8_variant))
 
     # ---- fit / state -----------------------------------------------------------------------------------
     def fit(self, X1, y1, noise=0.0):

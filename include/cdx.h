@@ -69,11 +69,17 @@ int cdx_gpis_query(cdx_ctx* ctx, const double* X_dev, int64_t M, double* mean_de
                    double* std_dev, double* grad_std_dev, void* stream);
 /* which arithmetic evaluates std when grad_std is not requested (the contraction L^-1 k* is N^2 flop/query):
  *   -1  FP64 tensor MMA (mma.sync m8n8k4) always - bit-identical across batch sizes;
- *    0  auto: TPS states with 1024 <= padded N <= 8192 use the tcgen05 INT8 path with 5 byte slices (error-free integer
- *       products of a 38-bit fixed-point k* and L^-1; measured |d var| < 2e-8 prior), else FP64 MMA.  The choice depends on
+ *    0  auto: TPS states with 1024 <= padded N <= 8192 use the tcgen05 INT8 path (csrc/cdx_query_i8x.cu) with 5 byte slices
+ *       (error-free integer products of a 38-bit fixed-point k* and L^-1; measured |d var| < 2e-8 prior), else FP64 MMA.  The choice depends on
  *       the state only, so a query's result does not depend on the batch it is part of;
  *  4..6 INT8 path with that many slices whenever the state is eligible (TPS, padded N <= 8192), any M. */
 int cdx_gpis_set_var_mode(cdx_ctx* ctx, int mode);
+/* launch shape of the tcgen05 INT8 path (same slices, same exact integer products, same summation tree per query):
+ *   3 (default) a CTA PAIR issues tcgen05.mma.cta_group::2 (256 rows of L^-1 as the M dimension, 96 queries as N); each CTA
+ *     generates the k* byte slices of half the queries into its own half of the B operand;
+ *   1 a 2-CTA cluster of single-CTA MMAs that exchange the generated k* slices through distributed shared memory;
+ *   2 no cluster (every CTA generates all of its block's k*). */
+int cdx_gpis_set_i8_variant(cdx_ctx* ctx, int variant);
 /* same through HOST buffers (copies on `stream`, synchronises before returning) - the e2e path of bench.py */
 int cdx_gpis_query_host(cdx_ctx* ctx, const double* X_host, int64_t M, double* mean_host, double* grad_mean_host,
                         double* std_host, double* grad_std_host, void* stream);

@@ -16,14 +16,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def run_cuda(hand, state, B, iters, per_iteration=True):
+def run_cuda(hand, state, B, iters, per_iteration=True, total=None):
     from compliancedex_b200 import GPIS, ProbabilisticGraspOptimizer, load_hand, state_path
     from compliancedex_b200.synthetic import surface_center, synthetic_candidates
     gp = GPIS(0.08, 1.0)
     gp.load_state_data(state_path(f"{state}_state"))
     doc = load_hand(hand)
     d = np.load(state_path(f"{state}_state"))
-    q0, T0, k0, palm = synthetic_candidates(doc, B, surface_center(d["X1"], d["y1"]), seed=100)
+    q0, T0, k0, palm = synthetic_candidates(doc, total or B, surface_center(d["X1"], d["y1"]), seed=100)
+    q0, T0, k0, palm = q0[:B], T0[:B], k0[:B], palm[:B]          # the leading shard of the global batch
     opt = ProbabilisticGraspOptimizer(hand, ee_link_names=doc["ee_link_name"], ee_link_offsets=doc["ee_link_offset"],
                                       palm_offset=palm, num_iters=iters, optimize_target=True, ref_q=doc["ref_q"], mass=0.1,
                                       com=[0.0, 0.0, 0.0], gravity=True, uncertainty=20.0, optimize_palm=True, noise_seed=2024)
@@ -78,7 +79,7 @@ def main():
     hand, state, B, iters = cfg
     g = np.load(os.path.join(ROOT, "tests", "golden", f"pregrasp_scale_{a.case}.npz"))
     t0 = time.time()
-    losses, ov, res, best, nans, inputs = run_cuda(hand, state, B, iters)
+    losses, ov, res, best, nans, inputs = run_cuda(hand, state, B, iters, total=int(g["full"]))
     out = {"case": a.case, "hand": hand, "state": state, "B": B, "iters": iters, "cuda_seconds": time.time() - t0,
            "cuda_argmin_full_batch": {"value": best[0], "index": best[1]}, "nan_candidate_iterations": nans[0],
            "vs_reference": compare("reference fixture (first %d rows)" % g["opt_value"].shape[0], losses, ov, g["losses"], g["opt_value"])}

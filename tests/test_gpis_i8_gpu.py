@@ -1,4 +1,4 @@
-"""GPU parity of the tcgen05 INT8-sliced std path (csrc/cdx_query_i8.cu) against the reference-generated golden vectors,
+"""GPU parity of the tcgen05 INT8-sliced std path (csrc/cdx_query_i8x.cu) against the reference-generated golden vectors,
 the oracle and the FP64 tensor-MMA path.  Gate (BASELINE.json): std^2 within 1e-6 * prior (R^3) absolute; mean and
 grad_mean <= 1e-5 relative (they come from the FP64 mean kernel on this path)."""
 import os
@@ -12,20 +12,28 @@ pytestmark = pytest.mark.gpu
 NAMES = ["mug", "mug2", "coffeebottle", "lego", "hammer", "banana", "dummy"]
 
 
-def _gpis(name, mode):
+def _gpis(name, mode, variant=None):
     from compliancedex_b200 import GPIS, state_path
     g = GPIS(0.08, 1.0)
     g.set_var_mode(mode)
+    if variant is not None:
+        g.set_i8_variant(variant)
     g.load_state_data(state_path(f"{name}_state"))
     return g
 
 
+# launch shapes of the tcgen05 path (cdx_gpis_set_i8_variant): CTA pair / cta_group::2 (default), 2-CTA cluster exchanging k*
+# over distributed shared memory, no cluster
+VARIANTS = [3, 1, 2]
+
+
 @pytest.mark.parametrize("name", NAMES)
 @pytest.mark.parametrize("slices", [5, 6])
-def test_shipped_states_against_reference_golden(name, slices, golden_dir):
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_shipped_states_against_reference_golden(name, slices, variant, golden_dir):
     """every shipped state (N = 196..401, padded to 256..448): forced INT8 path vs the reference's own outputs"""
     ref = np.load(os.path.join(golden_dir, f"gpis_{name}.npz"))
-    g = _gpis(name, slices)
+    g = _gpis(name, slices, variant)
     X = torch.from_numpy(ref["X"]).cuda()
     prior = float(g.R) ** 3
     with torch.no_grad():
@@ -37,10 +45,11 @@ def test_shipped_states_against_reference_golden(name, slices, golden_dir):
     assert np.abs(mean - ref["mean"]).max() <= 1e-5 * np.abs(ref["mean"]).max()
 
 
-@pytest.mark.parametrize("M", [1, 127, 128, 129, 1000])
-def test_ragged_batches(M):
-    """query counts around the 128-row tile: tail rows are masked, results match the FP64 MMA path"""
-    g = _gpis("hammer", 5)
+@pytest.mark.parametrize("M", [1, 95, 96, 97, 127, 128, 129, 1000])
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_ragged_batches(M, variant):
+    """query counts around the 96-query block / 128-row tile: tail queries are masked, results match the FP64 MMA path"""
+    g = _gpis("hammer", 5, variant)
     gen = torch.Generator().manual_seed(M)
     X = ((torch.rand(M, 3, generator=gen, dtype=torch.float64) - 0.5) * 0.36).cuda()
     with torch.no_grad():
@@ -67,7 +76,7 @@ def test_far_queries_scale():
     assert (((s1 ** 2 - s0 ** 2).abs() / scale).max()).item() <= 1e-6
 
 
-@pytest.mark.parametrize("N", [1024, 2048])
+@pytest.mark.parametrize("N", [1024, 2048, 1100])
 def test_synthetic_large_state_auto_mode(N):
     """auto mode (padded N >= 1024, any batch) runs the INT8 path; parity vs the FP64 MMA path and vs the oracle on a sample"""
     from compliancedex_b200 import GPIS
@@ -144,7 +153,7 @@ def test_c3_size_against_oracle_sample():
     before = lib.cdx_launch_count(g._ctx)
     with torch.no_grad():
         m1, s1 = g.pred(Xd)
-    assert lib.cdx_launch_count(g._ctx) - before == 5        # rowscale + slice + points + gpis_std_i8_kernel + mean: the INT8 path ran
+    assert lib.cdx_launch_count(g._ctx) - before == 5        # rowscale + slice + points + gpis_std_i8x_kernel + mean: the INT8 path ran
     n1 = g.compute_normal(Xd)
     with torch.no_grad():
         g.set_var_mode(-1)
