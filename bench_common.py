@@ -219,8 +219,9 @@ def reference_kind():
 def cpu_baseline_subprocess(workload, extra=()):
     """The cpu_baseline leg: the reference arm of the same workload in a child process with CUDA hidden (the reference
     harness patches torch for CPU execution - kept out of this process).  One bounded step."""
+    warm = "1" if workload.startswith("pregrasp") or workload == "gpis_c3" else "0"    # cheap steps: keep import / first-call costs out
     cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", workload, "--steps", "1",
-           "--warmup", "0", "--secondary", "none"] + list(extra)
+           "--warmup", warm, "--secondary", "none"] + list(extra)
     env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
     env["CUDA_VISIBLE_DEVICES"] = ""
     try:

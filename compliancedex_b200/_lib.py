@@ -55,6 +55,7 @@ SIGNATURES = {
                               ctypes.POINTER(c_double), ctypes.POINTER(c_int), c_void_p]),
     "cdx_gpis_query": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_gpis_set_var_mode": (c_int, [c_void_p, c_int]),
+    "cdx_gpis_set_ext_mode": (c_int, [c_void_p, c_int]),
     "cdx_gpis_set_i8_variant": (c_int, [c_void_p, c_int]),
     "cdx_gpis_query_host": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "cdx_gpis_query_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p]),

@@ -212,23 +212,45 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   const int nb = Np / 64;
   const size_t potrf_smem_bytes = sizeof(double) * 2 * 64 * 65;
   CDX_CUDA(cudaFuncSetAttribute(potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)potrf_smem_bytes));
+  // Right-looking with ONE panel of look-ahead: after the panel solve of step k only the next panel's 64 columns are updated
+  // on the main stream, so that the serial part of step k + 1 (64x64 factorisation + inverse: ~90 us, panel solve) runs
+  // while the rest of step k's trailing update (columns >= k + 2) is still executing on a second stream.
+  if (!g.fit_side) {
+    CDX_CUDA(cudaStreamCreateWithFlags(&g.fit_side, cudaStreamNonBlocking));
+    CDX_CUDA(cudaEventCreateWithFlags(&g.fit_ev_trsm, cudaEventDisableTiming));
+    CDX_CUDA(cudaEventCreateWithFlags(&g.fit_ev_rest, cudaEventDisableTiming));
+  }
+  CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, st));
+  CDX_CUDA(cudaStreamWaitEvent(g.fit_side, g.fit_ev_trsm, 0));      // the side stream starts after everything queued so far
   for (int kb = 0; kb < nb; kb++) {
     double* Akk = g.L + (int64_t)kb * 64 * (ld + 1);
     potrf_diag_kernel<<<1, 256, potrf_smem_bytes, st>>>(Akk, ld, g.Dinv + (int64_t)kb * 4096, g.U + (int64_t)kb * 64 * (ld + 1), g.flag,
                                          kb * 64);
     CDX_CHECK_LAUNCH(ctx);
-    int m = Np - (kb + 1) * 64;
+    const int m = Np - (kb + 1) * 64;
     if (m > 0) {
       double* A21 = Akk + 64 * ld;
       // L21 = A21 * inv(Lkk)^T   (in place: each CTA reads its own 64x64 row block completely before writing it)
       int rc = cdx_dgemm(ctx, false, false, m, 64, 64, 1.0, A21, ld, g.Dinv + (int64_t)kb * 4096, 64, 0.0, A21, ld, false,
                          0, 1, 0, 0, 0, st);
       if (rc) return rc;
-      // A22 -= L21 L21^T  (lower tiles only)
-      rc = cdx_dgemm(ctx, false, false, m, m, 64, -1.0, A21, ld, A21, ld, 1.0, A21 + 64, ld, true, 0, 1, 0, 0, 0, st);
+      CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, st));
+      // the next panel's columns: A[k+1.., k+1] -= L21 L21[0:64]^T - after the previous step's trailing update touched them
+      if (kb > 0) CDX_CUDA(cudaStreamWaitEvent(st, g.fit_ev_rest, 0));
+      rc = cdx_dgemm(ctx, false, false, m, 64, 64, -1.0, A21, ld, A21, ld, 1.0, A21 + 64, ld, false, 0, 1, 0, 0, 0, st);
       if (rc) return rc;
+      // the rest of the trailing matrix (rows / columns >= k + 2, lower tiles only) on the side stream
+      const int m2 = m - 64;
+      if (m2 > 0) {
+        CDX_CUDA(cudaStreamWaitEvent(g.fit_side, g.fit_ev_trsm, 0));
+        double* A32 = A21 + 64 * ld;
+        rc = cdx_dgemm(ctx, false, false, m2, m2, 64, -1.0, A32, ld, A32, ld, 1.0, A32 + 128, ld, true, 0, 1, 0, 0, 0, g.fit_side);
+        if (rc) return rc;
+      }
+      CDX_CUDA(cudaEventRecord(g.fit_ev_rest, g.fit_side));
     }
   }
+  CDX_CUDA(cudaStreamWaitEvent(st, g.fit_ev_rest, 0));
   dim3 g2((Np + 255) / 256, Np);
   zero_upper_kernel<<<g2, 256, 0, st>>>(g.L, Np);
   CDX_CHECK_LAUNCH(ctx);
@@ -333,6 +355,7 @@ extern "C" int cdx_destroy(cdx_ctx* ctx) {
   cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.dR2); cudaFree(g.flag);
   cudaFree(ctx->hx); cudaFree(ctx->hout);
   for (int i = 0; i < 6; i++) if (g.fit_ev[i]) cudaEventDestroy(g.fit_ev[i]);
+  if (g.fit_side) { cudaStreamDestroy(g.fit_side); cudaEventDestroy(g.fit_ev_trsm); cudaEventDestroy(g.fit_ev_rest); }
   cdx_i8x_free(ctx);
   cdx_pregrasp_free(ctx);
   cdx_sdf_free(ctx);

@@ -77,10 +77,13 @@ struct cdx_gpis_state {
   size_t i8x_cap = 0;
   int64_t i8x_rows = 0;
   int i8_variant = 3;       // cdx_gpis_set_i8_variant: 3 = CTA pair (cta_group::2), 1 = 2-CTA cluster sharing k* over DSMEM, 2 = no cluster
+  cudaStream_t fit_side = nullptr;                      // second stream of the look-ahead Cholesky
+  cudaEvent_t fit_ev_trsm = nullptr, fit_ev_rest = nullptr;
   // optional phase timing of the fit (cdx_gpis_fit_profile): events at the phase boundaries
   bool fit_prof = false;
   cudaEvent_t fit_ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t i8_ready = nullptr;  // recorded after the slices were built: queries on any other stream wait for it
+  int ext_mode = 0;         // cdx_gpis_set_ext_mode: 0 = all-columns extended kernel for states <= 448 padded points, 1 = column-tiled kernel always
   int var_mode = 0;         // cdx_gpis_set_var_mode: 0 auto, -1 always FP64 DMMA, 4/5/6 = INT8 slices whenever eligible
 };
 

@@ -231,6 +231,177 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
   if (csplit > 1) cg::this_cluster().sync();   // remote shared memory stays alive until rank 0 has read it
 }
 
+// ------------------------------------------------------------------------------------------ extended query, small states
+// gpis_ext_kernel: {mean, grad mean, std, grad std} for states of up to 448 padded training points - the shape of every
+// pregrasp iteration (optimize_pregrasp.py:714-716,733-736: 4 contact points per candidate, N = 196..401).  w = E11^-1 k* is a
+// [TQ, Np] x [Np, Np] product.  gpis_var_kernel walks it column tile by column tile and regenerates k* (FP64: distance, sqrt,
+// cubic) for every one of the Np/64 column tiles on the pipe the DMMA shares.  Here a CTA of 16 warps keeps the accumulators
+// of ALL Np columns of its TQ query rows in registers (8 column groups x 2 row groups: a warp owns Np/8 columns = NBW = Np/64
+// DMMA tiles of TQ/2 rows), so the K loop runs once: each 16-point chunk of k* is generated exactly once and
+// E11^-1 streams through shared memory exactly once per query tile, in 16-row slabs of Np columns (cp.async ring, 2-4 slabs deep;
+// E11^-1 is symmetric, so slab rows are contiguous).  The epilogue evaluates k and c once per (query, column) for
+// var = k(x,x) - k*.w and grad var = -2 sum_i w_i c_i (x - x_i): 2 kernel evaluations per (query, training point) instead
+// of Np/64 + 1.  CTAs are persistent over query tiles.  A query's arithmetic - the 16 interleaved partial sums of the mean,
+// the chunk order of the DMMA accumulation, the fixed column-warp order of the epilogue - does not depend on TQ or on the
+// tile it lands in, so results are bit-identical for every batch size and shard.
+constexpr int EW = 8;      // column groups (warps along the columns)
+constexpr int ERG = 2;     // row groups: 16 warps per CTA - a DMMA holds its warp for several cycles, four warps per scheduler keep the pipe fed
+__host__ __device__ constexpr int ext_slab_stages(int nbw) { return nbw <= 4 ? 4 : (nbw <= 5 ? 3 : 2); }   // 227 KB of shared memory per CTA
+template <int KERNEL, int NBW, int TQ>
+__global__ void __launch_bounds__(EW * ERG * 32, 1)
+gpis_ext_kernel(const double* __restrict__ Xq, int64_t M, const double* __restrict__ Xa, const double* __restrict__ Pm,
+                int N, int Np, cdx_kparams kp, double bias, double prior, double* __restrict__ mean,
+                double* __restrict__ gmean, double* __restrict__ stdv, double* __restrict__ gstd, int64_t ntiles) {
+  constexpr int RPG = TQ / ERG;         // query rows per row group
+  constexpr int MT = RPG / 8;           // 8-row DMMA blocks per warp
+  constexpr int NTHR = EW * ERG * 32;
+  constexpr int NBS = ext_slab_stages(NBW);   // slabs of E11^-1 in flight
+  extern __shared__ __align__(16) double smem[];
+  double* Bs = smem;                          // [NBS][Np * LDS] slab of E11^-1: rows = output columns n, 16 k each
+  double* As = Bs + NBS * (size_t)Np * LDS;   // [NA][TQ * LDS]  generated k* chunks
+  double* sxq = As + NA * TQ * LDS;           // [TQ][3]
+  double* red = sxq + TQ * 3;                 // [EW][TQ][4]
+  double* sXa = red + EW * TQ * 4;            // [Np][4] the training records (x, y, z, alpha): resident for the CTA's lifetime
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int fr = lane >> 2, fk = lane & 3;
+  const int cg = warp % EW, rg = warp / EW;   // this warp's column group and row group
+  const int WN = NBW * 8;                     // columns per warp
+  const int kpad = (N + TK - 1) / TK * TK, nch = kpad / TK;
+  for (int e = t; e < Np * 2; e += NTHR)
+    reinterpret_cast<double2*>(sXa)[e] = __ldg(reinterpret_cast<const double2*>(Xa) + e);
+  const double2* Xa2 = reinterpret_cast<const double2*>(sXa);
+  // generator role: 16 threads per query row, thread s of them owns training point s of every 16-point chunk and one of the
+  // query's 16 interleaved partial sums of the mean - for every TQ (with TQ = 16 the upper half of the CTA has no row)
+  const int qg = t >> 4, kslot = t & 15;
+  const bool gen = qg < TQ;
+
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t q0 = tile * TQ;
+    __syncthreads();                          // the previous tile's epilogue has finished with sxq / red / the rings
+    for (int e = t; e < TQ * 3; e += NTHR) {
+      const int64_t q = q0 + e / 3;
+      sxq[e] = q < M ? Xq[q * 3 + e % 3] : 0.0;
+    }
+    __syncthreads();
+    const double xq = gen ? sxq[qg * 3] : 0.0, yq = gen ? sxq[qg * 3 + 1] : 0.0, zq = gen ? sxq[qg * 3 + 2] : 0.0;
+    double ma = 0.0, gxa = 0.0, gya = 0.0, gza = 0.0;
+    double acc[MT][NBW][2];
+#pragma unroll
+    for (int i = 0; i < MT; i++)
+#pragma unroll
+      for (int j = 0; j < NBW; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    auto issueB = [&](int c, int buf) {
+      double* dst = Bs + (size_t)buf * Np * LDS;
+      for (int p = t; p < Np * 8; p += NTHR) {
+        const int row = p >> 3, seg = p & 7;
+        cdx_cp_async16(dst + row * LDS + seg * 2, Pm + (int64_t)row * Np + c * TK + seg * 2);
+      }
+    };
+    auto genA = [&](int c, int buf) {
+      if (!gen) return;
+      const int j = c * TK + kslot;
+      const double2 p0 = Xa2[2 * j], p1 = Xa2[2 * j + 1];
+      const double dx = xq - p0.x, dy = yq - p0.y, dz = zq - p1.x;
+      double k, cc;
+      cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, cc);
+      if (j >= N) k = 0.0;
+      As[buf * TQ * LDS + qg * LDS + kslot] = k;
+      const double a = p1.y;  // alpha (0 on padded rows)
+      ma = fma(a, k, ma);
+      const double ac = a * cc;
+      gxa = fma(ac, dx, gxa); gya = fma(ac, dy, gya); gza = fma(ac, dz, gza);
+    };
+
+#pragma unroll
+    for (int p = 0; p < NBS - 1; p++) {       // NBS - 1 slabs in flight before the first product
+      if (p < nch) issueB(p, p);
+      cdx_cp_async_commit();
+    }
+    genA(0, 0);
+    for (int c = 0; c < nch; c++) {
+      if (c + 1 < nch) genA(c + 1, (c + 1) % NA);
+      cdx_cp_async_wait<NBS - 2>();           // slab c has landed (the NBS - 2 younger groups may still be in flight)
+      __syncthreads();                        // chunk c (slab + k*) visible; every warp is done with chunk c - 1
+      if (c + NBS - 1 < nch) issueB(c + NBS - 1, (c + NBS - 1) % NBS);   // into the slot chunk c - 1 has just left
+      cdx_cp_async_commit();
+      const double* a_s = As + (c % NA) * TQ * LDS + (rg * RPG + fr) * LDS + fk;
+      const double* b_s = Bs + (size_t)(c % NBS) * Np * LDS + (cg * WN + fr) * LDS + fk;
+#pragma unroll
+      for (int ks = 0; ks < TK; ks += 4) {
+        double a[MT], b[NBW];
+#pragma unroll
+        for (int i = 0; i < MT; i++) a[i] = a_s[i * 8 * LDS + ks];
+#pragma unroll
+        for (int j = 0; j < NBW; j++) b[j] = b_s[j * 8 * LDS + ks];
+#pragma unroll
+        for (int i = 0; i < MT; i++)
+#pragma unroll
+          for (int j = 0; j < NBW; j++) cdx_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+      }
+    }
+    // ---- mean / grad mean: the 16 slot sums of a query, butterfly over its 16 lanes (every lane takes part)
+#pragma unroll
+    for (int o = 1; o < 16; o <<= 1) {
+      ma += __shfl_xor_sync(0xffffffffu, ma, o); gxa += __shfl_xor_sync(0xffffffffu, gxa, o);
+      gya += __shfl_xor_sync(0xffffffffu, gya, o); gza += __shfl_xor_sync(0xffffffffu, gza, o);
+    }
+    if (gen && kslot == 0 && q0 + qg < M) {
+      if (mean) mean[q0 + qg] = ma + bias;
+      if (gmean) { gmean[(q0 + qg) * 3] = gxa; gmean[(q0 + qg) * 3 + 1] = gya; gmean[(q0 + qg) * 3 + 2] = gza; }
+    }
+    // ---- epilogue: (k.w, w c dx, w c dy, w c dz) over this warp's columns, per owned row
+#pragma unroll
+    for (int i = 0; i < MT; i++) {
+      const int r = rg * RPG + i * 8 + fr;
+      const double rx = sxq[r * 3], ry = sxq[r * 3 + 1], rz = sxq[r * 3 + 2];
+      double ev[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int j = 0; j < NBW; j++)
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          const int col = cg * WN + j * 8 + 2 * fk + e;
+          if (col < N) {
+            const double2 p0 = Xa2[2 * col], p1 = Xa2[2 * col + 1];
+            const double dx = rx - p0.x, dy = ry - p0.y, dz = rz - p1.x;
+            double k, cc;
+            cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, cc);
+            const double w = acc[i][j][e];
+            ev[0] = fma(k, w, ev[0]);
+            const double wc = w * cc;
+            ev[1] = fma(wc, dx, ev[1]); ev[2] = fma(wc, dy, ev[2]); ev[3] = fma(wc, dz, ev[3]);
+          }
+        }
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        double sres = ev[e];
+        sres += __shfl_xor_sync(0xffffffffu, sres, 1); sres += __shfl_xor_sync(0xffffffffu, sres, 2);
+        if (fk == 0) red[(cg * TQ + r) * 4 + e] = sres;
+      }
+    }
+    __syncthreads();
+    if (t < TQ && q0 + t < M) {
+      const int64_t q = q0 + t;
+      double v[4];
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        double sres = red[(0 * TQ + t) * 4 + e];
+#pragma unroll
+        for (int w = 1; w < EW; w++) sres += red[(w * TQ + t) * 4 + e];      // column groups in order
+        v[e] = sres;
+      }
+      const double var = prior - v[0];
+      const double sd = sqrt(fabs(var));  // gpis.py:59
+      if (stdv) stdv[q] = sd;
+      if (gstd) {
+        // d sqrt|var| = sign(var) dvar / (2 sd),  dvar = -2 sum_i w_i c_i (x - x_i)
+        const double f = (var < 0.0 ? 1.0 : -1.0) / sd;
+        gstd[q * 3] = f * v[1]; gstd[q * 3 + 1] = f * v[2]; gstd[q * 3 + 2] = f * v[3];
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ mean only
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
@@ -371,6 +542,37 @@ int launch_var(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* g
   return CDX_OK;
 }
 
+
+template <int KERNEL, int NBW, int TQ>
+int launch_ext(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
+               cudaStream_t st) {
+  cdx_gpis_state& g = ctx->g;
+  const size_t smem = sizeof(double) * (ext_slab_stages(NBW) * (size_t)g.Np * LDS + NA * TQ * LDS + TQ * 3 + EW * TQ * 4 + 4 * (size_t)g.Np);
+  if (int rc = cdx_smem_attr(ctx, gpis_ext_kernel<KERNEL, NBW, TQ>, smem)) return rc;
+  const int64_t ntiles = (M + TQ - 1) / TQ;
+  const int grid = (int)min(ntiles, (int64_t)ctx->sms);
+  gpis_ext_kernel<KERNEL, NBW, TQ><<<grid, EW * ERG * 32, smem, st>>>(X, M, g.Xa, g.P, (int)g.N, (int)g.Np, cdx_make_kparams(g), g.bias,
+                                                               g.prior, mean, gmean, stdv, gstd, ntiles);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}
+
+// the all-columns extended kernel covers states of up to 448 padded points (7 DMMA column tiles per warp); 16-query tiles
+// while 32-query tiles would leave SMs idle
+template <int KERNEL>
+int dispatch_ext(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
+                 cudaStream_t st) {
+  const int nbw = (int)(ctx->g.Np / 64);
+  const bool small = (M + 31) / 32 < (int64_t)ctx->sms;
+#define CDX_EXT(NB) case NB: return small ? launch_ext<KERNEL, NB, 16>(ctx, X, M, mean, gmean, stdv, gstd, st) \
+                                          : launch_ext<KERNEL, NB, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
+  switch (nbw) {
+    CDX_EXT(1); CDX_EXT(2); CDX_EXT(3); CDX_EXT(4); CDX_EXT(5); CDX_EXT(6); CDX_EXT(7);
+  }
+#undef CDX_EXT
+  return -1;
+}
+
 template <int KERNEL>
 int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
                    cudaStream_t st) {
@@ -381,6 +583,7 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
   // the column tile TN depends on the state only, never on the batch size: a query's result is then bit-identical
   // whichever TQ variant (or shard) evaluates it
   if (gstd) {
+    if (g.Np <= 448 && g.ext_mode == 0) return dispatch_ext<KERNEL>(ctx, X, M, mean, gmean, stdv, gstd, st);
     if (small_batch) return big ? launch_var<KERNEL, 128, true, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
                                 : launch_var<KERNEL, 64, true, 32>(ctx, X, M, mean, gmean, stdv, gstd, st);
     return big ? launch_var<KERNEL, 128, true, 128>(ctx, X, M, mean, gmean, stdv, gstd, st)
@@ -423,6 +626,12 @@ extern "C" int cdx_gpis_query(cdx_ctx* ctx, const double* X, int64_t M, double* 
     case CDX_KERNEL_RBF: return query_dispatch<CDX_KERNEL_RBF>(ctx, X, M, mean, gmean, stdv, gstd, st);
     default: return query_dispatch<CDX_KERNEL_JOINT>(ctx, X, M, mean, gmean, stdv, gstd, st);
   }
+}
+
+extern "C" int cdx_gpis_set_ext_mode(cdx_ctx* ctx, int mode) {
+  if (!ctx || mode < 0 || mode > 1) { cdx_set_error("cdx_gpis_set_ext_mode: 0 or 1"); return CDX_ERR_ARG; }
+  ctx->g.ext_mode = mode;
+  return CDX_OK;
 }
 
 extern "C" int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha, const double* X, int64_t M, double* mean,

@@ -94,6 +94,8 @@ class GPIS:
             self._ctx = _lib.new_context(idx)
             self._device = idx
             _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, getattr(self, "_var_mode", 0)))
+            if hasattr(self, "_ext_mode"):
+                _lib.check(_lib.load().cdx_gpis_set_ext_mode(self._ctx, self._ext_mode))
             if hasattr(self, "_i8_variant"):
                 _lib.check(_lib.load().cdx_gpis_set_i8_variant(self._ctx, self._i8_variant))
         return self._ctx
@@ -119,6 +121,13 @@ class GPIS:
         self._var_mode = int(mode)
         if self._ctx is not None:
             _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, self._var_mode))
+
+    def set_ext_mode(self, mode):
+        """kernel of the extended query (mean, std and both gradients) on states of up to 448 padded points: 0 all-columns
+        kernel (default), 1 the column-tiled kernel that larger states use (include/cdx.h cdx_gpis_set_ext_mode)."""
+        self._ext_mode = int(mode)
+        if self._ctx is not None:
+            _lib.check(_lib.load().cdx_gpis_set_ext_mode(self._ctx, self._ext_mode))
 
     def set_i8_variant(self, variant):
         """launch shape of the tcgen05 INT8 std path (include/cdx.h cdx_gpis_set_i8_variant): 3 CTA pair with
