@@ -110,7 +110,8 @@ def run_gpis_c3(args, rank, world, local):
         useful_ops_per_query = 2 * (S * (S + 1) // 2) * (N * (N + 1) // 2)
         achieved = ops_per_query * M / (kernel_ms * 1e-3) / 1e12
         peak = i8_peak(pipes)
-        roof = {"bound": "tensor", "kernel": "gpis_std_i8x_kernel<%d, CTA pair> (tcgen05.mma.cta_group::2 kind::i8, INT32 accumulators in TMEM)" % S,
+        roof = {"bound": "tensor", "kernel": "gpis_std_i8x_kernel<%d, CTA pair> (tcgen05.mma.cta_group::2 kind::i8, INT32 accumulators in TMEM); "
+                                           "its time here includes i8x_kstar_kernel, which generates the k* byte slices once per query chunk" % S,
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                 "peak_source": "tcgen05.mma kind::i8 issue rate MEASURED in this run by csrc/cdx_pipebench (best of the operand "
                                "shapes it times; MEASURED_PEAKS.json has no INT8 figure, its bf16 %s = %.0f TF/s); achieved counts "
@@ -119,8 +120,9 @@ def run_gpis_c3(args, rank, world, local):
                 "algorithmic_fp64_tflops": fp64_equiv, "fp64_dmma_peak_tflops": dmma_peak,
                 "speedup_over_fp64_dmma_peak_rate": fp64_equiv / dmma_peak if dmma_peak else None,
                 "note": "the FP64 contraction L^-1 k* (N^2 flop/query) is evaluated as error-free INT8 slice products "
-                        "(S(S+1)/2 byte-slice pairs); the FP64 generation of the k* slices does not overlap the INT8 MMAs on this "
-                        "chip (DESIGN.md section 4: FP64 instructions and tcgen05 MMAs serialise); mean / grad_mean come from the "
+                        "(S(S+1)/2 byte-slice pairs); FP64 instructions and tcgen05 MMAs exclude each other on this chip "
+                        "(csrc/cdx_mixbench.cu, DESIGN.md section 4), so the k* slices are generated ONCE per query by a separate "
+                        "FP64 kernel into the B-operand image and the MMA kernel is pure INT8; mean / grad_mean come from the "
                         "separate TMA-staged FP64 mean kernel"}
     else:
         roof = {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,128,unit> (FP64 DMMA)", "achieved": fp64_equiv,

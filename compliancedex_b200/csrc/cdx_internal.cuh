@@ -76,6 +76,9 @@ struct cdx_gpis_state {
   int i8x_S = 0;
   size_t i8x_cap = 0;
   int64_t i8x_rows = 0;
+  int8_t* i8x_kq = nullptr;    // scratch: k* byte slices of one chunk of queries in the B-operand image (CTA-pair path)
+  double* i8x_scq = nullptr;   // per-query fixed-point scales of the chunk
+  size_t i8x_kq_cap = 0;
   int i8_variant = 3;       // cdx_gpis_set_i8_variant: 3 = CTA pair (cta_group::2), 1 = 2-CTA cluster sharing k* over DSMEM, 2 = no cluster
   cudaStream_t fit_side = nullptr;                      // second stream of the look-ahead Cholesky
   cudaEvent_t fit_ev_trsm = nullptr, fit_ev_rest = nullptr;

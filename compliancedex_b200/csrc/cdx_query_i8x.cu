@@ -24,6 +24,7 @@
 // (both operands from shared memory, M = 128, N = 96, K = 32) and releases the stage in every CTA with a multicast
 // tcgen05.commit; warp 13 streams the U slices + the stage's training points (cp.async.bulk); warps 14-21 drain the S
 // diagonal accumulators after each row tile (tcgen05.ld), recombine them, square, and reduce over the 128 rows.
+#include <algorithm>
 #include "cdx_internal.cuh"
 
 namespace {
@@ -254,15 +255,90 @@ __device__ __forceinline__ double x_query_scale(double x, double y, double z, co
   return ldexp(1.0, 8 * S - e - 1);
 }
 
+// ------------------------------------------------------------------------------------------- k* slices, generated once
+// per-query fixed-point scale (a power of two), once per query
+template <int S>
+__global__ void __launch_bounds__(256) i8x_scale_kernel(const double* __restrict__ Xq, int64_t M, int64_t Mc, const double* __restrict__ bb,
+                                                        double R, double R3, double* __restrict__ scq) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= Mc) return;
+  const bool ok = i < M;
+  scq[i] = x_query_scale<S>(ok ? Xq[i * 3] : 0.0, ok ? Xq[i * 3 + 1] : 0.0, ok ? Xq[i * 3 + 2] : 0.0, bb, R, R3);
+}
+
+// One thread per (query, 16 training points): 9 FP64 operations + 1 MUFU.RSQ per value (expanded squared distance, float rsqrt
+// seed built by integer bit moves, one Newton step, cubic, fixed-point conversion by the 1.5 * 2^52 trick), PRMT byte
+// transposes, and one 16-byte store per slice straight into the image the MMA kernel's bulk copies expect:
+//   kq[(query block, CTA of the pair)][stage of 32 points][slice][16-point group][query row of that CTA][16 bytes].
+// A warp = 32 consecutive queries at the same 16 points (uniform point loads, 512 contiguous bytes per store instruction).
+template <int S, int C, bool PAIR>
+__global__ void __launch_bounds__(256) i8x_kstar_kernel(const double* __restrict__ Xq, int64_t M, int64_t Mc, const double* __restrict__ pts,
+                                                        const double* __restrict__ scq, int Np, double R, double R3,
+                                                        int8_t* __restrict__ kq) {
+  using G = xcfg<S, PAIR>;
+  const int64_t gid = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  const int64_t ql = gid % Mc;
+  const int c16 = (int)(gid / Mc);
+  if (c16 >= Np / 16) return;
+  const bool ok = ql < M;
+  const double xq = ok ? Xq[ql * 3] : 0.0, yq = ok ? Xq[ql * 3 + 1] : 0.0, zq = ok ? Xq[ql * 3 + 2] : 0.0;
+  const double qq = fma(xq, xq, fma(yq, yq, zq * zq)) + 1e-16;   // keeps the expanded squared distance positive
+  const double sc = scq[ql];
+  const double c2 = 2.0 * sc, c3 = -3.0 * R * sc, c0m = R3 * sc + X_MAGIC;
+  const double2* P2 = reinterpret_cast<const double2*>(pts) + (size_t)c16 * 32;
+  unsigned ow[S][4];
+#pragma unroll
+  for (int gq = 0; gq < 4; gq++) {
+    unsigned L[4], H[4];
+#pragma unroll
+    for (int p = 0; p < 4; p++) {
+      const int j = gq * 4 + p;
+      const double2 a = __ldg(P2 + 2 * j), b = __ldg(P2 + 2 * j + 1);
+      const double sd = fma(xq, a.x, fma(yq, a.y, fma(zq, b.x, b.y + qq)));
+      const unsigned shi = (unsigned)__double2hiint(sd), slo = (unsigned)__double2loint(sd);
+      const unsigned fb = __funnelshift_l(slo, shi - 0x38000000u, 3);     // float(s) by bit moves (no F2F)
+      const unsigned yb = __float_as_uint(xrsqrt_ftz(__uint_as_float(fb)));
+      const double yd = __hiloint2double((int)((yb >> 3) + 0x38000000u), (int)(yb << 29));
+      const double hy = __hiloint2double((int)((yb >> 3) + 0x37F00000u), (int)(yb << 29));   // y / 2
+      double d = sd * yd;
+      d = fma(fma(-d, d, sd), hy, d);
+      if (S >= 6) d = fma(fma(-d, d, sd), hy, d);
+      const double res = fma(sd, fma(c2, d, c3), c0m);     // rint(k sc) in the low mantissa bits
+      L[p] = (unsigned)__double2loint(res);
+      H[p] = (unsigned)__double2hiint(res);
+    }
+    const unsigned t0 = __byte_perm(L[0], L[1], 0x5140), t1 = __byte_perm(L[2], L[3], 0x5140);
+    const unsigned t2 = __byte_perm(L[0], L[1], 0x7362), t3 = __byte_perm(L[2], L[3], 0x7362);
+    const unsigned t4 = __byte_perm(H[0], H[1], 0x5140), t5 = __byte_perm(H[2], H[3], 0x5140);
+    unsigned by[6];
+    by[0] = __byte_perm(t0, t1, 0x5410); by[1] = __byte_perm(t0, t1, 0x7632);
+    by[2] = __byte_perm(t2, t3, 0x5410); by[3] = __byte_perm(t2, t3, 0x7632);
+    by[4] = __byte_perm(t4, t5, 0x5410); by[5] = __byte_perm(t4, t5, 0x7632);
+#pragma unroll
+    for (int i = 0; i < S; i++) ow[i][gq] = by[S - 1 - i];
+  }
+  const int64_t block = ql / G::NQ;
+  const int qcol = (int)(ql % G::NQ), cta = PAIR ? qcol / G::NB : 0, row = PAIR ? qcol % G::NB : qcol;
+  const int NC = Np / X_BK, c = c16 >> 1, kg = c16 & 1;
+  int8_t* dst = kq + ((size_t)(block * C + cta) * NC + c) * G::B_BYTES + kg * (G::NB * 16) + row * 16;
+#pragma unroll
+  for (int i = 0; i < S; i++) *reinterpret_cast<uint4*>(dst + (size_t)i * G::B_SLICE) = make_uint4(ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
+}
+
 // ------------------------------------------------------------------------------------------- the query kernel
 // One cluster of C CTAs per block of NQ queries; CTA `rank` takes the row tiles rank, rank + C, ... (a "round" = one tile per
 // CTA); every CTA of the cluster walks the same stage sequence (round r: k chunks 0 .. (r C + C) 128/32 - 1, the bound of
 // the round's LAST tile; the few chunks above a tile's own diagonal hold zero digits).
-template <int S, int C, bool PAIR>
+// PRE: the k* byte slices were generated beforehand (i8x_kstar_kernel) into `kq`, laid out per (query block, CTA, stage) in
+// the shared-memory image of the B operand: the loader brings them in with one more bulk copy per stage and the generator
+// warps have nothing to do.  On B200 FP64 instructions and tcgen05 MMAs exclude each other (csrc/cdx_mixbench.cu: while
+// MMAs are queued the FP64 pipe issues ~2 % of its rate), so generating inside this kernel only ADDS the generation time to
+// the MMA time - and repeats it for every round; generated once, on the whole chip, it costs a few per cent of the MMAs.
+template <int S, int C, bool PAIR, bool PRE>
 __global__ void __launch_bounds__(X_THREADS, 1)
 gpis_std_i8x_kernel(const double* __restrict__ Xq, int64_t M, const double* __restrict__ pts, const int8_t* __restrict__ Asl,
                     const double* __restrict__ sb, const double* __restrict__ bb, int Np, int NT, double R, double R3, double prior,
-                    double* __restrict__ stdv) {
+                    double* __restrict__ stdv, const int8_t* __restrict__ kq) {
   static_assert(!PAIR || C == 2, "a CTA pair is a cluster of two");
   using G = xcfg<S, PAIR>;
   constexpr int NQ = G::NQ, NB = G::NB, NST = G::NST, QPC = NQ / C;  // QPC: queries whose k* this CTA generates
@@ -329,7 +405,7 @@ gpis_std_i8x_kernel(const double* __restrict__ Xq, int64_t M, const double* __re
 
   if (warp < X_GEN_WARPS) {
     // ===================================================== generators
-    const int grp = warp / WPS, wg = warp % WPS;
+    const int grp = PRE ? NGRP : warp / WPS, wg = warp % WPS;     // PRE: no generation in this kernel
     const int item = wg * 32 + lane;
     const bool active = grp < NGRP && item < ITEMS;
     const int nact = min(32, ITEMS - wg * 32);                       // active lanes of this warp (the same in every CTA)
@@ -416,7 +492,23 @@ gpis_std_i8x_kernel(const double* __restrict__ Xq, int64_t M, const double* __re
     // ===================================================== U slices (operand ring) + training points (their own, deeper ring)
     // one thread walks both schedules: the points of stage k are requested NP - NST stages before the U tile of stage k - so
     // the generators' arithmetic is never inside the operand ring's re-use loop (TMA latency + generation + MMA per NST stages)
-    if (lane == 0) {
+    if (lane == 0 && PRE) {
+      // U digit slices + the pre-generated k* slices of this CTA's rows of the B operand: two bulk copies per stage
+      const int8_t* kqc = kq + ((size_t)(blockIdx.x / C) * C + rank) * (size_t)NC * G::B_BYTES;
+      int g = 0;
+      for (int r = 0; r < rounds; r++) {
+        const int ns = stages_of(r);
+        const int nt = r * C + (int)rank;
+        for (int c = 0; c < ns; c++, g++) {
+          const int sa = g % NST;
+          xmb_wait_relaxed(empty + 8 * sa, ((unsigned)(g / NST) & 1u) ^ 1u);
+          xmb_expect_tx(a_full + 8 * sa, (unsigned)(G::A_BYTES + G::B_BYTES));
+          const unsigned dst = smem0 + (unsigned)sa * G::SLOT;
+          xbulk_g2s(dst, Asl + (size_t)(nt * NC + c) * G::A_BYTES, (unsigned)G::A_BYTES, a_full + 8 * sa);
+          xbulk_g2s(dst + G::A_BYTES, kqc + (size_t)c * G::B_BYTES, (unsigned)G::B_BYTES, a_full + 8 * sa);
+        }
+      }
+    } else if (lane == 0) {
       int total = 0;
       for (int r = 0; r < rounds; r++) total += stages_of(r);
       constexpr int D = NP - NST;
@@ -457,7 +549,7 @@ gpis_std_i8x_kernel(const double* __restrict__ Xq, int64_t M, const double* __re
           const int s = g % NST;
           const unsigned ph = (unsigned)(g / NST) & 1u;
           xmb_wait(a_full + 8 * s, ph);
-          xmb_wait(b_full + 8 * s, ph);
+          if (!PRE) xmb_wait(b_full + 8 * s, ph);
           if (lane == 0) xmb_arrive_remote_relaxed(lead_ready + 8 * s);
           __syncwarp();
         }
@@ -471,9 +563,9 @@ gpis_std_i8x_kernel(const double* __restrict__ Xq, int64_t M, const double* __re
           const int s = g % NST;
           const unsigned ph = (unsigned)(g / NST) & 1u;
           xmb_wait(a_full + 8 * s, ph);
-          xmb_wait(b_full + 8 * s, ph);
+          if (!PRE) xmb_wait(b_full + 8 * s, ph);
           if (PAIR) xmb_wait(peer_ready + 8 * s, ph);
-          xfence_proxy_async_cta();     // k* bytes written through the generic proxy (locally, or by st.async from the peers)
+          if (!PRE) xfence_proxy_async_cta();   // k* bytes written through the generic proxy (locally, or by st.async from the peers)
           xtc_fence_after();
           const unsigned abase = smem0 + (unsigned)s * G::SLOT, bbase = abase + G::A_BYTES;
           if (xelect_one()) {
@@ -637,28 +729,59 @@ int x_prepare(cdx_ctx* ctx, cudaStream_t st) {
 template <int S, int C, bool PAIR>
 int x_launch(cdx_ctx* ctx, const double* X, int64_t M, double* stdv, cudaStream_t st) {
   using G = xcfg<S, PAIR>;
+  constexpr bool PRE = PAIR;           // the CTA-pair path consumes k* slices generated beforehand (see gpis_std_i8x_kernel)
   int rc = x_prepare<S>(ctx, st);
   if (rc) return rc;
   cdx_gpis_state& g = ctx->g;
-  if (int rca = cdx_smem_attr(ctx, gpis_std_i8x_kernel<S, C, PAIR>, G::SMEM)) return rca;
+  if (int rca = cdx_smem_attr(ctx, gpis_std_i8x_kernel<S, C, PAIR, PRE>, G::SMEM)) return rca;
   CDX_CUDA(cudaStreamWaitEvent(st, g.i8_ready, 0));   // the slices may have been built on another stream
-  const int NT = (int)((g.Np + X_TM - 1) / X_TM);
-  const int64_t blocks = (M + G::NQ - 1) / G::NQ;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(blocks * C), 1, 1);
-  cfg.blockDim = dim3(X_THREADS, 1, 1);
-  cfg.dynamicSmemBytes = G::SMEM;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = C;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = C > 1 ? 1 : 0;
-  CDX_CUDA(cudaLaunchKernelEx(&cfg, gpis_std_i8x_kernel<S, C, PAIR>, X, M, (const double*)g.i8x_pts, (const int8_t*)g.i8x_A,
-                              (const double*)g.i8x_sb, (const double*)g.i8x_bb, (int)g.Np, NT, g.R, g.R * g.R * g.R, g.prior, stdv));
-  CDX_CHECK_LAUNCH(ctx);
+  const int NT = (int)((g.Np + X_TM - 1) / X_TM), NC = (int)(g.Np / X_BK);
+  // queries are processed in chunks whose k* image fits the scratch buffer (20 KB per query at N = 4096, S = 5)
+  const int64_t chunk_blocks = PRE ? 8 * (int64_t)(ctx->sms / C) : (M + G::NQ - 1) / G::NQ;
+  const int64_t chunk_q = chunk_blocks * G::NQ;
+  if (PRE) {
+    const int64_t blocks = std::min<int64_t>(chunk_blocks, (M + G::NQ - 1) / G::NQ);
+    const size_t need = (size_t)blocks * C * NC * G::B_BYTES;
+    if (need > g.i8x_kq_cap) {
+      CDX_CUDA(cudaStreamSynchronize(st));
+      cudaFree(g.i8x_kq); cudaFree(g.i8x_scq);
+      g.i8x_kq = nullptr; g.i8x_scq = nullptr; g.i8x_kq_cap = 0;
+      if (cudaMalloc((void**)&g.i8x_kq, need) != cudaSuccess || cudaMalloc((void**)&g.i8x_scq, sizeof(double) * blocks * G::NQ) != cudaSuccess) {
+        cudaGetLastError();
+        cdx_set_error("out of device memory for the k* slices of %lld queries (%zu bytes)", (long long)(blocks * G::NQ), need);
+        return CDX_ERR_ALLOC;
+      }
+      g.i8x_kq_cap = need;
+    }
+  }
+  for (int64_t q0 = 0; q0 < M; q0 += chunk_q) {
+    const int64_t mc = std::min<int64_t>(chunk_q, M - q0);
+    const int64_t blocks = (mc + G::NQ - 1) / G::NQ, Mc = blocks * G::NQ;
+    if (PRE) {
+      i8x_scale_kernel<S><<<(unsigned)((Mc + 255) / 256), 256, 0, st>>>(X + q0 * 3, mc, Mc, g.i8x_bb, g.R, g.R * g.R * g.R, g.i8x_scq);
+      CDX_CHECK_LAUNCH(ctx);
+      const int64_t items = Mc * (g.Np / 16);
+      i8x_kstar_kernel<S, C, PAIR><<<(unsigned)((items + 255) / 256), 256, 0, st>>>(X + q0 * 3, mc, Mc, g.i8x_pts, g.i8x_scq, (int)g.Np, g.R,
+                                                                                  g.R * g.R * g.R, g.i8x_kq);
+      CDX_CHECK_LAUNCH(ctx);
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(blocks * C), 1, 1);
+    cfg.blockDim = dim3(X_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = G::SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = C > 1 ? 1 : 0;
+    CDX_CUDA(cudaLaunchKernelEx(&cfg, gpis_std_i8x_kernel<S, C, PAIR, PRE>, X + q0 * 3, mc, (const double*)g.i8x_pts, (const int8_t*)g.i8x_A,
+                                (const double*)g.i8x_sb, (const double*)g.i8x_bb, (int)g.Np, NT, g.R, g.R * g.R * g.R, g.prior,
+                                stdv + q0, (const int8_t*)g.i8x_kq));
+    CDX_CHECK_LAUNCH(ctx);
+  }
   return CDX_OK;
 }
 
@@ -714,6 +837,8 @@ extern "C" int cdx_gpis_set_var_mode(cdx_ctx* ctx, int mode) {
 void cdx_i8x_free(cdx_ctx* ctx) {
   cdx_gpis_state& g = ctx->g;
   cudaFree(g.i8x_A); cudaFree(g.i8x_sb); cudaFree(g.i8x_eb); cudaFree(g.i8x_pts); cudaFree(g.i8x_bb);
+  cudaFree(g.i8x_kq); cudaFree(g.i8x_scq);
+  g.i8x_kq = nullptr; g.i8x_scq = nullptr; g.i8x_kq_cap = 0;
   g.i8x_A = nullptr; g.i8x_sb = nullptr; g.i8x_eb = nullptr; g.i8x_pts = nullptr; g.i8x_bb = nullptr;
   g.i8x_S = 0; g.i8x_cap = 0; g.i8x_rows = 0;
   if (g.i8_ready) { cudaEventDestroy(g.i8_ready); g.i8_ready = nullptr; }

@@ -22,6 +22,11 @@ def _gpis(name, mode, variant=None):
     return g
 
 
+def _chunks(M):
+    """query chunks of the CTA-pair path: 8 waves of 74 pairs x 96 queries (csrc/cdx_query_i8x.cu x_launch)"""
+    return -(-M // (8 * 74 * 96))
+
+
 # launch shapes of the tcgen05 path (cdx_gpis_set_i8_variant): CTA pair / cta_group::2 (default), 2-CTA cluster exchanging k*
 # over distributed shared memory, no cluster
 VARIANTS = [3, 1, 2]
@@ -95,7 +100,7 @@ def test_synthetic_large_state_auto_mode(N):
     with torch.no_grad():
         m1, s1 = g.pred(X)                      # auto -> INT8 (prepare kernels + std kernel + mean kernel)
     launched = _lib.load().cdx_launch_count(g._ctx) - before
-    assert launched == 5, launched               # rowscale + slice + points + std_i8 + mean
+    assert launched == 3 + 3 * _chunks(M) + 1, launched    # rowscale + slice + points | per chunk: scale + k* slices + MMA kernel | mean
     with torch.no_grad():
         g.set_var_mode(-1)
         m0, s0 = g.pred(X)
@@ -153,7 +158,7 @@ def test_c3_size_against_oracle_sample():
     before = lib.cdx_launch_count(g._ctx)
     with torch.no_grad():
         m1, s1 = g.pred(Xd)
-    assert lib.cdx_launch_count(g._ctx) - before == 5        # rowscale + slice + points + gpis_std_i8x_kernel + mean: the INT8 path ran
+    assert lib.cdx_launch_count(g._ctx) - before == 3 + 3 * _chunks(M) + 1   # the INT8 path ran: prepare | per chunk scale + k* + MMA | mean
     n1 = g.compute_normal(Xd)
     with torch.no_grad():
         g.set_var_mode(-1)
