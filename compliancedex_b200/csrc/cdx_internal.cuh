@@ -78,6 +78,7 @@ struct cdx_gpis_state {
   int64_t i8x_rows = 0;
   int8_t* i8x_kq = nullptr;    // scratch: k* byte slices of one chunk of queries in the B-operand image (CTA-pair path)
   double* i8x_scq = nullptr;   // per-query fixed-point scales of the chunk
+  double* i8x_part = nullptr;  // [parts][queries][4] partial sums of the mean and its gradient
   size_t i8x_kq_cap = 0;
   int i8_variant = 3;       // cdx_gpis_set_i8_variant: 3 = CTA pair (cta_group::2), 1 = 2-CTA cluster sharing k* over DSMEM, 2 = no cluster
   cudaStream_t fit_side = nullptr;                      // second stream of the look-ahead Cholesky
@@ -185,7 +186,8 @@ __device__ __forceinline__ void cdx_cp_async_wait() { asm volatile("cp.async.wai
 // lower_only: skip tiles strictly above the diagonal (requires M == N tiles aligned).  batch via strides.
 // tcgen05 INT8-sliced std query (cdx_query_i8x.cu); S slices in {4,5,6}
 bool cdx_i8_eligible(const cdx_ctx* ctx);
-int cdx_i8x_std(cdx_ctx* ctx, int S, int cluster, const double* X, int64_t M, double* stdv, cudaStream_t st);
+int cdx_i8x_std(cdx_ctx* ctx, int S, int cluster, const double* X, int64_t M, double* stdv, double* mean, double* gmean,
+                bool* mean_done, cudaStream_t st);
 void cdx_i8x_free(cdx_ctx* ctx);
 void cdx_sdf_free(cdx_ctx* ctx);
 

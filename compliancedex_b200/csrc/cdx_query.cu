@@ -597,9 +597,10 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
     const bool i8 = vm != -1 && cdx_i8_eligible(ctx) && (vm >= 4 || g.Np >= 1024);
     if (i8) {
       const int S = vm >= 4 ? vm : 5;
-      int rc = cdx_i8x_std(ctx, S, g.i8_variant == 1 ? 2 : (g.i8_variant == 3 ? 3 : 1), X, M, stdv, st);
+      bool mean_done = false;
+      int rc = cdx_i8x_std(ctx, S, g.i8_variant == 1 ? 2 : (g.i8_variant == 3 ? 3 : 1), X, M, stdv, mean, gmean, &mean_done, st);
       if (rc) return rc;
-      if (mean || gmean) return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
+      if ((mean || gmean) && !mean_done) return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
       return CDX_OK;
     }
     if (small_batch) return big ? launch_var<KERNEL, 128, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st)

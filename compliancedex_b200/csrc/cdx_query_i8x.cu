@@ -266,63 +266,97 @@ __global__ void __launch_bounds__(256) i8x_scale_kernel(const double* __restrict
   scq[i] = x_query_scale<S>(ok ? Xq[i * 3] : 0.0, ok ? Xq[i * 3 + 1] : 0.0, ok ? Xq[i * 3 + 2] : 0.0, bb, R, R3);
 }
 
-// One thread per (query, 16 training points): 9 FP64 operations + 1 MUFU.RSQ per value (expanded squared distance, float rsqrt
-// seed built by integer bit moves, one Newton step, cubic, fixed-point conversion by the 1.5 * 2^52 trick), PRMT byte
-// transposes, and one 16-byte store per slice straight into the image the MMA kernel's bulk copies expect:
+// One thread per (query, 512 training points): per value 9 FP64 operations + 1 MUFU.RSQ (expanded squared distance, float
+// rsqrt seed built by integer bit moves, one Newton step, cubic, fixed-point conversion by the 1.5 * 2^52 trick), PRMT byte
+// transposes, and per 16 points one 16-byte store per slice straight into the image the MMA kernel's bulk copies expect:
 //   kq[(query block, CTA of the pair)][stage of 32 points][slice][16-point group][query row of that CTA][16 bytes].
-// A warp = 32 consecutive queries at the same 16 points (uniform point loads, 512 contiguous bytes per store instruction).
-template <int S, int C, bool PAIR>
-__global__ void __launch_bounds__(256) i8x_kstar_kernel(const double* __restrict__ Xq, int64_t M, int64_t Mc, const double* __restrict__ pts,
-                                                        const double* __restrict__ scq, int Np, double R, double R3,
-                                                        int8_t* __restrict__ kq) {
+// A warp = 32 consecutive queries at the same points (uniform point loads, 512 contiguous bytes per store instruction).
+// MEAN: the posterior mean and its gradient (gpis.py:55, :80-82) need the same distances: mu = sum_k alpha_k k,
+// grad mu = sum_k alpha_k c_k (x - x_k) are accumulated on the way (10 more FP64 operations per pair instead of a second
+// kernel's 20) into one partial per (512-point part, query); i8x_mean_reduce_kernel adds the parts in order - the split
+// depends on the state only, so a query's mean is the same for every batch.
+constexpr int X_PART = 512;
+template <int S, int C, bool PAIR, bool MEAN>
+__global__ void __launch_bounds__(128) i8x_kstar_kernel(const double* __restrict__ Xq, int64_t M, int64_t Mc, const double* __restrict__ pts,
+                                                        const double* __restrict__ Xa, const double* __restrict__ scq, int Np, double R,
+                                                        double R3, int8_t* __restrict__ kq, double* __restrict__ part) {
   using G = xcfg<S, PAIR>;
-  const int64_t gid = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  const int64_t ql = gid % Mc;
-  const int c16 = (int)(gid / Mc);
-  if (c16 >= Np / 16) return;
+  const int64_t ql = (int64_t)blockIdx.x * 128 + threadIdx.x;
+  if (ql >= Mc) return;
   const bool ok = ql < M;
   const double xq = ok ? Xq[ql * 3] : 0.0, yq = ok ? Xq[ql * 3 + 1] : 0.0, zq = ok ? Xq[ql * 3 + 2] : 0.0;
   const double qq = fma(xq, xq, fma(yq, yq, zq * zq)) + 1e-16;   // keeps the expanded squared distance positive
   const double sc = scq[ql];
-  const double c2 = 2.0 * sc, c3 = -3.0 * R * sc, c0m = R3 * sc + X_MAGIC;
-  const double2* P2 = reinterpret_cast<const double2*>(pts) + (size_t)c16 * 32;
-  unsigned ow[S][4];
-#pragma unroll
-  for (int gq = 0; gq < 4; gq++) {
-    unsigned L[4], H[4];
-#pragma unroll
-    for (int p = 0; p < 4; p++) {
-      const int j = gq * 4 + p;
-      const double2 a = __ldg(P2 + 2 * j), b = __ldg(P2 + 2 * j + 1);
-      const double sd = fma(xq, a.x, fma(yq, a.y, fma(zq, b.x, b.y + qq)));
-      const unsigned shi = (unsigned)__double2hiint(sd), slo = (unsigned)__double2loint(sd);
-      const unsigned fb = __funnelshift_l(slo, shi - 0x38000000u, 3);     // float(s) by bit moves (no F2F)
-      const unsigned yb = __float_as_uint(xrsqrt_ftz(__uint_as_float(fb)));
-      const double yd = __hiloint2double((int)((yb >> 3) + 0x38000000u), (int)(yb << 29));
-      const double hy = __hiloint2double((int)((yb >> 3) + 0x37F00000u), (int)(yb << 29));   // y / 2
-      double d = sd * yd;
-      d = fma(fma(-d, d, sd), hy, d);
-      if (S >= 6) d = fma(fma(-d, d, sd), hy, d);
-      const double res = fma(sd, fma(c2, d, c3), c0m);     // rint(k sc) in the low mantissa bits
-      L[p] = (unsigned)__double2loint(res);
-      H[p] = (unsigned)__double2hiint(res);
-    }
-    const unsigned t0 = __byte_perm(L[0], L[1], 0x5140), t1 = __byte_perm(L[2], L[3], 0x5140);
-    const unsigned t2 = __byte_perm(L[0], L[1], 0x7362), t3 = __byte_perm(L[2], L[3], 0x7362);
-    const unsigned t4 = __byte_perm(H[0], H[1], 0x5140), t5 = __byte_perm(H[2], H[3], 0x5140);
-    unsigned by[6];
-    by[0] = __byte_perm(t0, t1, 0x5410); by[1] = __byte_perm(t0, t1, 0x7632);
-    by[2] = __byte_perm(t2, t3, 0x5410); by[3] = __byte_perm(t2, t3, 0x7632);
-    by[4] = __byte_perm(t4, t5, 0x5410); by[5] = __byte_perm(t4, t5, 0x7632);
-#pragma unroll
-    for (int i = 0; i < S; i++) ow[i][gq] = by[S - 1 - i];
-  }
+  const double m3R = -3.0 * R, m6R = -6.0 * R;
   const int64_t block = ql / G::NQ;
   const int qcol = (int)(ql % G::NQ), cta = PAIR ? qcol / G::NB : 0, row = PAIR ? qcol % G::NB : qcol;
-  const int NC = Np / X_BK, c = c16 >> 1, kg = c16 & 1;
-  int8_t* dst = kq + ((size_t)(block * C + cta) * NC + c) * G::B_BYTES + kg * (G::NB * 16) + row * 16;
+  const int NC = Np / X_BK;
+  int8_t* dst0 = kq + (size_t)(block * C + cta) * NC * G::B_BYTES + row * 16;
+  const int g0 = blockIdx.y * (X_PART / 16), g1 = min(g0 + X_PART / 16, Np / 16);
+  double am[4] = {0, 0, 0, 0}, ax[4] = {0, 0, 0, 0}, ay[4] = {0, 0, 0, 0}, az[4] = {0, 0, 0, 0};
+  for (int c16 = g0; c16 < g1; c16++) {
+    const double2* P2 = reinterpret_cast<const double2*>(pts) + (size_t)c16 * 32;
+    unsigned ow[S][4];
 #pragma unroll
-  for (int i = 0; i < S; i++) *reinterpret_cast<uint4*>(dst + (size_t)i * G::B_SLICE) = make_uint4(ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
+    for (int gq = 0; gq < 4; gq++) {
+      unsigned L[4], H[4];
+#pragma unroll
+      for (int p = 0; p < 4; p++) {
+        const int j = gq * 4 + p;
+        const double2 a = __ldg(P2 + 2 * j), b = __ldg(P2 + 2 * j + 1);
+        const double sd = fma(xq, a.x, fma(yq, a.y, fma(zq, b.x, b.y + qq)));
+        const unsigned shi = (unsigned)__double2hiint(sd), slo = (unsigned)__double2loint(sd);
+        const unsigned fb = __funnelshift_l(slo, shi - 0x38000000u, 3);     // float(s) by bit moves (no F2F)
+        const unsigned yb = __float_as_uint(xrsqrt_ftz(__uint_as_float(fb)));
+        const double yd = __hiloint2double((int)((yb >> 3) + 0x38000000u), (int)(yb << 29));
+        const double hy = __hiloint2double((int)((yb >> 3) + 0x37F00000u), (int)(yb << 29));   // y / 2
+        double d = sd * yd;
+        d = fma(fma(-d, d, sd), hy, d);
+        d = fma(fma(-d, d, sd), hy, d);                      // second Newton step: generated once per query, it is cheap here
+        const double k = fma(sd, fma(2.0, d, m3R), R3);      // 2 d^3 - 3 R d^2 + R^3 (gpis.py:26)
+        const double res = fma(k, sc, X_MAGIC);              // rint(k sc) in the low mantissa bits (sc is a power of two)
+        L[p] = (unsigned)__double2loint(res);
+        H[p] = (unsigned)__double2hiint(res);
+        if (MEAN) {
+          const double al = __ldg(Xa + 4 * (size_t)(c16 * 16 + j) + 3);   // alpha (0 on padded rows)
+          am[p] = fma(al, k, am[p]);
+          const double ac = al * fma(6.0, d, m6R);           // alpha c,  c = 6 (d - R)
+          ax[p] = fma(ac, fma(0.5, a.x, xq), ax[p]);        // x - x_k  (the record holds -2 x_k)
+          ay[p] = fma(ac, fma(0.5, a.y, yq), ay[p]);
+          az[p] = fma(ac, fma(0.5, b.x, zq), az[p]);
+        }
+      }
+      const unsigned t0 = __byte_perm(L[0], L[1], 0x5140), t1 = __byte_perm(L[2], L[3], 0x5140);
+      const unsigned t2 = __byte_perm(L[0], L[1], 0x7362), t3 = __byte_perm(L[2], L[3], 0x7362);
+      const unsigned t4 = __byte_perm(H[0], H[1], 0x5140), t5 = __byte_perm(H[2], H[3], 0x5140);
+      unsigned by[6];
+      by[0] = __byte_perm(t0, t1, 0x5410); by[1] = __byte_perm(t0, t1, 0x7632);
+      by[2] = __byte_perm(t2, t3, 0x5410); by[3] = __byte_perm(t2, t3, 0x7632);
+      by[4] = __byte_perm(t4, t5, 0x5410); by[5] = __byte_perm(t4, t5, 0x7632);
+#pragma unroll
+      for (int i = 0; i < S; i++) ow[i][gq] = by[S - 1 - i];
+    }
+    int8_t* dst = dst0 + (size_t)(c16 >> 1) * G::B_BYTES + (c16 & 1) * (G::NB * 16);
+#pragma unroll
+    for (int i = 0; i < S; i++) *reinterpret_cast<uint4*>(dst + (size_t)i * G::B_SLICE) = make_uint4(ow[i][0], ow[i][1], ow[i][2], ow[i][3]);
+  }
+  if (MEAN) {
+    double* o = part + ((size_t)blockIdx.y * Mc + ql) * 4;
+    o[0] = (am[0] + am[1]) + (am[2] + am[3]); o[1] = (ax[0] + ax[1]) + (ax[2] + ax[3]);
+    o[2] = (ay[0] + ay[1]) + (ay[2] + ay[3]); o[3] = (az[0] + az[1]) + (az[2] + az[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256) i8x_mean_reduce_kernel(const double* __restrict__ part, int parts, int64_t M, int64_t Mc, double bias,
+                                                              double* __restrict__ mean, double* __restrict__ gmean) {
+  const int64_t q = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (q >= M) return;
+  double v[4] = {0, 0, 0, 0};
+  for (int p = 0; p < parts; p++)
+#pragma unroll
+    for (int e = 0; e < 4; e++) v[e] += part[((size_t)p * Mc + q) * 4 + e];
+  if (mean) mean[q] = v[0] + bias;
+  if (gmean) { gmean[q * 3] = v[1]; gmean[q * 3 + 1] = v[2]; gmean[q * 3 + 2] = v[3]; }
 }
 
 // ------------------------------------------------------------------------------------------- the query kernel
@@ -727,7 +761,7 @@ int x_prepare(cdx_ctx* ctx, cudaStream_t st) {
 }
 
 template <int S, int C, bool PAIR>
-int x_launch(cdx_ctx* ctx, const double* X, int64_t M, double* stdv, cudaStream_t st) {
+int x_launch(cdx_ctx* ctx, const double* X, int64_t M, double* stdv, double* mean, double* gmean, bool* mean_done, cudaStream_t st) {
   using G = xcfg<S, PAIR>;
   constexpr bool PRE = PAIR;           // the CTA-pair path consumes k* slices generated beforehand (see gpis_std_i8x_kernel)
   int rc = x_prepare<S>(ctx, st);
@@ -739,14 +773,18 @@ int x_launch(cdx_ctx* ctx, const double* X, int64_t M, double* stdv, cudaStream_
   // queries are processed in chunks whose k* image fits the scratch buffer (20 KB per query at N = 4096, S = 5)
   const int64_t chunk_blocks = PRE ? 8 * (int64_t)(ctx->sms / C) : (M + G::NQ - 1) / G::NQ;
   const int64_t chunk_q = chunk_blocks * G::NQ;
+  const int parts = (int)((g.Np + X_PART - 1) / X_PART);
+  const bool with_mean = PRE && (mean || gmean);
+  *mean_done = with_mean;
   if (PRE) {
     const int64_t blocks = std::min<int64_t>(chunk_blocks, (M + G::NQ - 1) / G::NQ);
     const size_t need = (size_t)blocks * C * NC * G::B_BYTES;
     if (need > g.i8x_kq_cap) {
       CDX_CUDA(cudaStreamSynchronize(st));
-      cudaFree(g.i8x_kq); cudaFree(g.i8x_scq);
-      g.i8x_kq = nullptr; g.i8x_scq = nullptr; g.i8x_kq_cap = 0;
-      if (cudaMalloc((void**)&g.i8x_kq, need) != cudaSuccess || cudaMalloc((void**)&g.i8x_scq, sizeof(double) * blocks * G::NQ) != cudaSuccess) {
+      cudaFree(g.i8x_kq); cudaFree(g.i8x_scq); cudaFree(g.i8x_part);
+      g.i8x_kq = nullptr; g.i8x_scq = nullptr; g.i8x_part = nullptr; g.i8x_kq_cap = 0;
+      if (cudaMalloc((void**)&g.i8x_kq, need) != cudaSuccess || cudaMalloc((void**)&g.i8x_scq, sizeof(double) * blocks * G::NQ) != cudaSuccess ||
+          cudaMalloc((void**)&g.i8x_part, sizeof(double) * 4 * parts * blocks * G::NQ) != cudaSuccess) {
         cudaGetLastError();
         cdx_set_error("out of device memory for the k* slices of %lld queries (%zu bytes)", (long long)(blocks * G::NQ), need);
         return CDX_ERR_ALLOC;
@@ -760,10 +798,19 @@ int x_launch(cdx_ctx* ctx, const double* X, int64_t M, double* stdv, cudaStream_
     if (PRE) {
       i8x_scale_kernel<S><<<(unsigned)((Mc + 255) / 256), 256, 0, st>>>(X + q0 * 3, mc, Mc, g.i8x_bb, g.R, g.R * g.R * g.R, g.i8x_scq);
       CDX_CHECK_LAUNCH(ctx);
-      const int64_t items = Mc * (g.Np / 16);
-      i8x_kstar_kernel<S, C, PAIR><<<(unsigned)((items + 255) / 256), 256, 0, st>>>(X + q0 * 3, mc, Mc, g.i8x_pts, g.i8x_scq, (int)g.Np, g.R,
-                                                                                  g.R * g.R * g.R, g.i8x_kq);
+      const dim3 kgrid((unsigned)((Mc + 127) / 128), (unsigned)parts);
+      if (with_mean)
+        i8x_kstar_kernel<S, C, PAIR, true><<<kgrid, 128, 0, st>>>(X + q0 * 3, mc, Mc, g.i8x_pts, g.Xa, g.i8x_scq, (int)g.Np, g.R,
+                                                                g.R * g.R * g.R, g.i8x_kq, g.i8x_part);
+      else
+        i8x_kstar_kernel<S, C, PAIR, false><<<kgrid, 128, 0, st>>>(X + q0 * 3, mc, Mc, g.i8x_pts, g.Xa, g.i8x_scq, (int)g.Np, g.R,
+                                                                 g.R * g.R * g.R, g.i8x_kq, g.i8x_part);
       CDX_CHECK_LAUNCH(ctx);
+      if (with_mean) {
+        i8x_mean_reduce_kernel<<<(unsigned)((mc + 255) / 256), 256, 0, st>>>(g.i8x_part, parts, mc, Mc, g.bias, mean ? mean + q0 : nullptr,
+                                                                             gmean ? gmean + q0 * 3 : nullptr);
+        CDX_CHECK_LAUNCH(ctx);
+      }
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(blocks * C), 1, 1);
@@ -789,24 +836,26 @@ int x_launch(cdx_ctx* ctx, const double* X, int64_t M, double* stdv, cudaStream_
 
 // cluster: 1 = no cluster, 2 = two CTAs sharing the generated k* through distributed shared memory, 3 = a CTA PAIR
 // (tcgen05 cta_group::2, M = 256)
-int cdx_i8x_std(cdx_ctx* ctx, int S, int cluster, const double* X, int64_t M, double* stdv, cudaStream_t st) {
+// mean / gmean (nullable): computed here only on the CTA-pair path (*mean_done tells the caller)
+int cdx_i8x_std(cdx_ctx* ctx, int S, int cluster, const double* X, int64_t M, double* stdv, double* mean, double* gmean,
+                bool* mean_done, cudaStream_t st) {
   if (cluster == 1) {
     switch (S) {
-      case 4: return x_launch<4, 1, false>(ctx, X, M, stdv, st);
-      case 5: return x_launch<5, 1, false>(ctx, X, M, stdv, st);
-      case 6: return x_launch<6, 1, false>(ctx, X, M, stdv, st);
+      case 4: return x_launch<4, 1, false>(ctx, X, M, stdv, mean, gmean, mean_done, st);
+      case 5: return x_launch<5, 1, false>(ctx, X, M, stdv, mean, gmean, mean_done, st);
+      case 6: return x_launch<6, 1, false>(ctx, X, M, stdv, mean, gmean, mean_done, st);
     }
   } else if (cluster == 2) {
     switch (S) {
-      case 4: return x_launch<4, 2, false>(ctx, X, M, stdv, st);
-      case 5: return x_launch<5, 2, false>(ctx, X, M, stdv, st);
-      case 6: return x_launch<6, 2, false>(ctx, X, M, stdv, st);
+      case 4: return x_launch<4, 2, false>(ctx, X, M, stdv, mean, gmean, mean_done, st);
+      case 5: return x_launch<5, 2, false>(ctx, X, M, stdv, mean, gmean, mean_done, st);
+      case 6: return x_launch<6, 2, false>(ctx, X, M, stdv, mean, gmean, mean_done, st);
     }
   } else {
     switch (S) {
-      case 4: return x_launch<4, 2, true>(ctx, X, M, stdv, st);
-      case 5: return x_launch<5, 2, true>(ctx, X, M, stdv, st);
-      case 6: return x_launch<6, 2, true>(ctx, X, M, stdv, st);
+      case 4: return x_launch<4, 2, true>(ctx, X, M, stdv, mean, gmean, mean_done, st);
+      case 5: return x_launch<5, 2, true>(ctx, X, M, stdv, mean, gmean, mean_done, st);
+      case 6: return x_launch<6, 2, true>(ctx, X, M, stdv, mean, gmean, mean_done, st);
     }
   }
   cdx_set_error("cdx_i8x_std: slices must be 4, 5 or 6");
@@ -837,8 +886,8 @@ extern "C" int cdx_gpis_set_var_mode(cdx_ctx* ctx, int mode) {
 void cdx_i8x_free(cdx_ctx* ctx) {
   cdx_gpis_state& g = ctx->g;
   cudaFree(g.i8x_A); cudaFree(g.i8x_sb); cudaFree(g.i8x_eb); cudaFree(g.i8x_pts); cudaFree(g.i8x_bb);
-  cudaFree(g.i8x_kq); cudaFree(g.i8x_scq);
-  g.i8x_kq = nullptr; g.i8x_scq = nullptr; g.i8x_kq_cap = 0;
+  cudaFree(g.i8x_kq); cudaFree(g.i8x_scq); cudaFree(g.i8x_part);
+  g.i8x_kq = nullptr; g.i8x_scq = nullptr; g.i8x_part = nullptr; g.i8x_kq_cap = 0;
   g.i8x_A = nullptr; g.i8x_sb = nullptr; g.i8x_eb = nullptr; g.i8x_pts = nullptr; g.i8x_bb = nullptr;
   g.i8x_S = 0; g.i8x_cap = 0; g.i8x_rows = 0;
   if (g.i8_ready) { cudaEventDestroy(g.i8_ready); g.i8_ready = nullptr; }

@@ -100,7 +100,7 @@ def test_synthetic_large_state_auto_mode(N):
     with torch.no_grad():
         m1, s1 = g.pred(X)                      # auto -> INT8 (prepare kernels + std kernel + mean kernel)
     launched = _lib.load().cdx_launch_count(g._ctx) - before
-    assert launched == 3 + 3 * _chunks(M) + 1, launched    # rowscale + slice + points | per chunk: scale + k* slices + MMA kernel | mean
+    assert launched == 3 + 4 * _chunks(M), launched    # rowscale + slice + points | per chunk: scale + k* slices (+ mean partials) + mean reduce + MMA kernel
     with torch.no_grad():
         g.set_var_mode(-1)
         m0, s0 = g.pred(X)
@@ -158,7 +158,7 @@ def test_c3_size_against_oracle_sample():
     before = lib.cdx_launch_count(g._ctx)
     with torch.no_grad():
         m1, s1 = g.pred(Xd)
-    assert lib.cdx_launch_count(g._ctx) - before == 3 + 3 * _chunks(M) + 1   # the INT8 path ran: prepare | per chunk scale + k* + MMA | mean
+    assert lib.cdx_launch_count(g._ctx) - before == 3 + 4 * _chunks(M)   # the INT8 path ran: prepare | per chunk scale + k* (+ mean partials) + mean reduce + MMA
     n1 = g.compute_normal(Xd)
     with torch.no_grad():
         g.set_var_mode(-1)
