@@ -450,7 +450,7 @@ gpis_std_i8x_kernel(const double* __restrict__ Xq, int64_t M, const double* __re
     const double xq = ok ? Xq[q * 3] : 0.0, yq = ok ? Xq[q * 3 + 1] : 0.0, zq = ok ? Xq[q * 3 + 2] : 0.0;
     const double qq = fma(xq, xq, fma(yq, yq, zq * zq)) + 1e-16;
     const double sc = x_query_scale<S>(xq, yq, zq, bb, R, R3);
-    const double c2 = 2.0 * sc, c3 = -3.0 * R * sc, c0m = R3 * sc + X_MAGIC;
+    const double m3R = -3.0 * R;
     const unsigned boff = (unsigned)(G::A_BYTES + kg * (NB * 16) + (PAIR ? ql : qcol) * 16);     // within a stage slot, slice 0
     if (grp < NGRP) {
       int g = 0;
@@ -479,8 +479,8 @@ gpis_std_i8x_kernel(const double* __restrict__ Xq, int64_t M, const double* __re
               const double hy = __hiloint2double((int)((yb >> 3) + 0x37F00000u), (int)(yb << 29));   // y / 2
               double d = sd * yd;
               d = fma(fma(-d, d, sd), hy, d);
-              if (S >= 6) d = fma(fma(-d, d, sd), hy, d);
-              const double res = fma(sd, fma(c2, d, c3), c0m);     // rint(k sc) in the low mantissa bits
+              d = fma(fma(-d, d, sd), hy, d);
+              const double res = fma(fma(sd, fma(2.0, d, m3R), R3), sc, X_MAGIC);   // the arithmetic of i8x_kstar_kernel, bit for bit
               L[p] = (unsigned)__double2loint(res);
               H[p] = (unsigned)__double2hiint(res);
             }

@@ -1,7 +1,7 @@
 """Seeded synthetic inputs of the benchmark shapes: a GPIS training set shaped like
 train_gpis_completion.py:20-58 and pregrasp candidates following run_experiments.py:87-90 /
 optimize_pregrasp.py:19-24,889-891,940-941,956.  Data generators only - no GPIS or objective arithmetic.
-(oracle/ carries its own copies; tests/test_synthetic.py checks both produce identical arrays.)"""
+(oracle/ carries its own copies; tests/test_host_logic.py checks both produce identical arrays.)"""
 import math
 
 import numpy as np
