@@ -128,12 +128,133 @@ __global__ void __launch_bounds__(128) dgemm_kernel(int M, int N, int K, double 
     }
 }
 
+// ------------------------------------------------------------------------------------------ 128 x 128 tiles, cp.async ring
+// The large products of the fit (trailing updates of the Cholesky with K = 256, the recursive-doubling levels of L^-1,
+// E11^-1 = U^T U): 128x128x16 CTA tiles, 16 warps (4 x 4, each a 32x32 tile = 4x4 DMMA blocks), operands brought in with
+// 16-byte cp.async through a 4-stage shared-memory ring - a DMMA holds its warp for several cycles, so it takes four warps per
+// scheduler and loads that never wait on the math to keep the pipe fed (the 64x64 single-buffered kernel above reached
+// 0.40-0.50 of the DMMA peak).  Operand tiles keep the layout they have in memory: k-contiguous sources as [row][20]
+// (conflict-free for the fragment pattern row = T/4, k = T%4), row-contiguous sources (ta / tb) as [k][132].
+constexpr int GM = 128, GN = 128, GK = 16, GST = 4, LDT = 132;
+constexpr int G_TILE = GM * LDS > GK * LDT ? GM * LDS : GK * LDT;   // doubles per operand tile and stage
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(512, 1) dgemm128_kernel(int M, int N, int K, double alpha, const double* __restrict__ A,
+                                                          int64_t lda, const double* __restrict__ B, int64_t ldb, double beta,
+                                                          double* __restrict__ C, int64_t ldc, int lower_only, int ktri,
+                                                          int64_t sA, int64_t sB, int64_t sC) {
+  const int tm = blockIdx.y, tn = blockIdx.x;
+  if (lower_only && tn > tm) return;
+  A += (int64_t)blockIdx.z * sA;
+  B += (int64_t)blockIdx.z * sB;
+  C += (int64_t)blockIdx.z * sC;
+  extern __shared__ __align__(16) double gsm[];
+  double* As = gsm;                       // [GST][G_TILE]
+  double* Bs = gsm + GST * G_TILE;        // [GST][G_TILE]
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int wm = warp >> 2, wn = warp & 3;
+  const int fr = lane >> 2, fk = lane & 3;
+  const int m0 = tm * GM, n0 = tn * GN;
+  int kbeg = 0, kend = K;
+  if (ktri == 1) kbeg = n0;
+  if (ktri == 3) kbeg = m0;
+  if (ktri == 2) kend = min(K, m0 + GM);
+  const int nch = (kend - kbeg + GK - 1) / GK;
+
+  // one operand tile of chunk c into ring slot `buf`: 16-byte cp.async, rows outside the matrix are zero-filled
+  auto load_tile = [&](const double* __restrict__ P, int64_t ld, bool trans, int r0, int R, double* dst, int k0) {
+    if (!trans) {                         // P[rows, K]: 128 rows x 8 segments of 2 doubles
+      for (int p = t; p < GM * 8; p += 512) {
+        const int row = p >> 3, seg = p & 7;
+        double* d = dst + row * LDS + seg * 2;
+        if (r0 + row < R && k0 + seg * 2 < kend) cdx_cp_async16(d, P + (int64_t)(r0 + row) * ld + k0 + seg * 2);
+        else { d[0] = 0.0; d[1] = 0.0; }
+      }
+    } else {                              // P[K, rows]: 16 k x 64 segments of 2 doubles
+      for (int p = t; p < GK * 64; p += 512) {
+        const int kk = p >> 6, seg = p & 63;
+        double* d = dst + kk * LDT + seg * 2;
+        if (k0 + kk < kend && r0 + seg * 2 < R) cdx_cp_async16(d, P + (int64_t)(k0 + kk) * ld + r0 + seg * 2);
+        else { d[0] = 0.0; d[1] = 0.0; }
+      }
+    }
+  };
+  auto issue = [&](int c) {
+    if (c < nch) {
+      const int buf = c % GST, k0 = kbeg + c * GK;
+      load_tile(A, lda, TA, m0, M, As + buf * G_TILE, k0);
+      load_tile(B, ldb, TB, n0, N, Bs + buf * G_TILE, k0);
+    }
+    cdx_cp_async_commit();
+  };
+
+  double acc[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+#pragma unroll
+  for (int c = 0; c < GST - 1; c++) issue(c);
+  for (int c = 0; c < nch; c++) {
+    cdx_cp_async_wait<GST - 2>();         // chunk c has landed
+    __syncthreads();                      // ... for every thread; and every warp is done with chunk c - 1
+    issue(c + GST - 1);                   // into the slot chunk c - 1 has just left
+    const double* a_s = As + (c % GST) * G_TILE;
+    const double* b_s = Bs + (c % GST) * G_TILE;
+#pragma unroll
+    for (int ks = 0; ks < GK; ks += 4) {
+      double a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+        a[i] = TA ? a_s[(ks + fk) * LDT + wm * 32 + i * 8 + fr] : a_s[(wm * 32 + i * 8 + fr) * LDS + ks + fk];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        b[j] = TB ? b_s[(ks + fk) * LDT + wn * 32 + j * 8 + fr] : b_s[(wn * 32 + j * 8 + fr) * LDS + ks + fk];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) cdx_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int r = m0 + wm * 32 + i * 8 + fr;
+      const int c = n0 + wn * 32 + j * 8 + 2 * fk;
+      if (r < M && c < N) {               // N is even for every caller (multiples of 64): the pair never straddles the edge
+        double2* p = reinterpret_cast<double2*>(C + (int64_t)r * ldc + c);
+        double2 v = make_double2(alpha * acc[i][j][0], alpha * acc[i][j][1]);
+        if (beta != 0.0) { const double2 o = *p; v.x += beta * o.x; v.y += beta * o.y; }
+        *p = v;
+      }
+    }
+}
+
 }  // namespace
 
 int cdx_dgemm(cdx_ctx* ctx, bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int64_t lda,
               const double* B, int64_t ldb, double beta, double* C, int64_t ldc, bool lower_only, int ktri, int batch,
               int64_t sA, int64_t sB, int64_t sC, cudaStream_t st) {
   if (M <= 0 || N <= 0 || batch <= 0) return CDX_OK;
+  // large, aligned products go to the 128x128 cp.async kernel; thin / in-place panel operations keep the 64x64 one
+  if (M >= 128 && N >= 128 && (M % 2) == 0 && (N % 2) == 0 && (K % 2) == 0 && (lda % 2) == 0 && (ldb % 2) == 0 && (ldc % 2) == 0 &&
+      A != C && B != C) {
+    const size_t smem = sizeof(double) * 2 * GST * G_TILE;
+    dim3 grid128((N + GN - 1) / GN, (M + GM - 1) / GM, batch);
+    int lo128 = lower_only ? 1 : 0;
+#define CDX_G128(TA_, TB_)                                                                                                   \
+    do {                                                                                                                     \
+      if (int rc = cdx_smem_attr(ctx, dgemm128_kernel<TA_, TB_>, smem)) return rc;                                           \
+      dgemm128_kernel<TA_, TB_><<<grid128, 512, smem, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lo128, ktri, sA, sB, sC); \
+    } while (0)
+    if (!ta && !tb) CDX_G128(false, false); else if (!ta && tb) CDX_G128(false, true);
+    else if (ta && !tb) CDX_G128(true, false); else CDX_G128(true, true);
+#undef CDX_G128
+    CDX_CHECK_LAUNCH(ctx);
+    return CDX_OK;
+  }
   dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
   int lo = lower_only ? 1 : 0;
   if (!ta && !tb)
