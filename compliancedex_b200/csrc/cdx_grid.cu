@@ -5,6 +5,15 @@
 // the order numpy's boolean-mask indexing returns.
 #include "cdx_internal.cuh"
 
+#include <mutex>
+
+// Scratch of cdx_grid_surface_static (below): the per-block surface counts / offsets of a grid of at most 256^3 voxels
+// (65,536 blocks of 256 voxels, 256 KB).  Lives in every GPU that loads the library until the process exits.  In host code
+// this NAME is only a stand-in for the symbol - its device address comes from cudaGetSymbolAddress (grid_static_scratch).
+#define CDX_GRID_STATIC_MAX_STEPS 256
+#define CDX_GRID_STATIC_MAX_BLOCKS (CDX_GRID_STATIC_MAX_STEPS * CDX_GRID_STATIC_MAX_STEPS * CDX_GRID_STATIC_MAX_STEPS / 256)
+static __device__ __align__(256) unsigned cdx_grid_static_counts[CDX_GRID_STATIC_MAX_BLOCKS];
+
 namespace {
 
 __device__ __forceinline__ bool grid_is_surface(const float* __restrict__ m, int steps, int64_t lin) {
@@ -56,6 +65,25 @@ __global__ void __launch_bounds__(256) grid_scatter_kernel(const float* __restri
   if (on) idx[base + __popc(bal & ((1u << lane) - 1u))] = (long long)lin;
 }
 
+// device address of cdx_grid_static_counts on `device` (which must be current): looked up once per device
+int grid_static_scratch(int device, unsigned** out) {
+  static std::mutex mu;
+  static unsigned* addr[64] = {};
+  if (device < 0 || device >= 64) { cdx_set_error("cdx_grid_surface_static: device ordinal out of range"); return CDX_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[device]) {
+    unsigned* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, cdx_grid_static_counts);
+    if (e != cudaSuccess || !p) {
+      cdx_set_error("cdx_grid_surface_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return CDX_ERR_CUDA;
+    }
+    addr[device] = p;
+  }
+  *out = addr[device];
+  return CDX_OK;
+}
+
 }  // namespace
 
 extern "C" int cdx_grid_surface(cdx_ctx* ctx, const float* mean, int steps, long long* idx, long long* count, void* stream) {
@@ -77,5 +105,34 @@ extern "C" int cdx_grid_surface(cdx_ctx* ctx, const float* mean, int steps, long
   grid_scatter_kernel<<<nb, 256, 0, st>>>(mean, steps, total, counts, idx);
   CDX_CHECK_LAUNCH(ctx);
   CDX_CUDA(cudaFreeAsync(counts, st));
+  return CDX_OK;
+}
+
+// cdx_grid_surface for callers that must not allocate (CUDA graph capture, serving loops): same three kernels, the block
+// counts in the file-scope array above instead of a stream-ordered allocation.  No cudaMalloc / cudaFree of any kind.
+// Every call on a device shares that array: calls that overlap on the GPU (different streams) race.  Nothing in it has to
+// start at zero - grid_count_kernel overwrites entries [0, nb) before the scan reads them.
+extern "C" int cdx_grid_surface_static(cdx_ctx* ctx, const float* mean, int steps, long long* idx, long long* count, void* stream) {
+  if (!ctx || !mean || !idx || !count || steps < 1) {
+    cdx_set_error("cdx_grid_surface_static: bad argument");
+    return CDX_ERR_ARG;
+  }
+  if (steps > CDX_GRID_STATIC_MAX_STEPS) {
+    cdx_set_error("cdx_grid_surface_static: steps = %d exceeds the static scratch (steps <= %d); use cdx_grid_surface", steps,
+                  CDX_GRID_STATIC_MAX_STEPS);
+    return CDX_ERR_ARG;
+  }
+  CDX_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned* counts = nullptr;
+  if (int rc = grid_static_scratch(ctx->device, &counts)) return rc;
+  const int64_t total = (int64_t)steps * steps * steps;
+  const int nb = (int)((total + 255) / 256);
+  grid_count_kernel<<<nb, 256, 0, st>>>(mean, steps, total, counts);
+  CDX_CHECK_LAUNCH(ctx);
+  grid_scan_kernel<<<1, 1024, 0, st>>>(counts, nb, count);
+  CDX_CHECK_LAUNCH(ctx);
+  grid_scatter_kernel<<<nb, 256, 0, st>>>(mean, steps, total, counts, idx);
+  CDX_CHECK_LAUNCH(ctx);
   return CDX_OK;
 }

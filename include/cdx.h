@@ -96,6 +96,14 @@ int cdx_gpis_query_weights(cdx_ctx* ctx, const double* alpha_dev, const double* 
  * least one 6-neighbour with mean >= 0, interior voxels only.  Writes the linear indices in ascending order to
  * idx_dev (capacity steps^3) and their number to count_dev[0]. */
 int cdx_grid_surface(cdx_ctx* ctx, const float* mean_dev, int steps, long long* idx_dev, long long* count_dev, void* stream);
+/* NO COUNTERPART IN THE REFERENCE - added for callers that cannot allocate (CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same arguments and results as cdx_grid_surface,
+ * but the per-block counts live in a file-scope static __device__ array (256 KB per GPU that loads the library, held until
+ * exit) instead of a stream-ordered allocation: the call allocates and frees nothing.  Limit: steps <= 256 (CDX_ERR_ARG
+ * with a message beyond that).  All calls on one device share the array, so calls that overlap on the GPU race -
+ * serialise them on one stream. */
+int cdx_grid_surface_static(cdx_ctx* ctx, const float* mean_dev, int steps, long long* idx_dev, long long* count_dev,
+                            void* stream);
 
 /* ------------------------------------------------------------------ mesh distance (TorchSDF) ----------- */
 /* compute_sdf (thirdparty/TorchSDF/torchsdf/sdf.py:34-64; binding csrc/bindings.cpp:22-27 ->
