@@ -216,33 +216,39 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   // panel solve as a GEMM with the block inverse, update of the panel's own remaining columns) touch only the panel; the
   // trailing matrix is updated ONCE per panel with K = 256 - a quarter of the read-modify-write traffic of 64-wide steps and
   // four times the work per tile launch (with K = 64 every tile's prologue / epilogue outweighed its four k-chunks: 0.29 of
-  // the DMMA peak).  One panel of look-ahead: the next panel's 256 columns are updated first, on the main stream, so that
-  // the next panel's serial sub-steps run while the rest of the trailing update executes on a second stream.
+  // the DMMA peak).  One panel of look-ahead: the next panel's 256 columns are updated first, so that the next panel's
+  // serial sub-steps run while the rest of the trailing update executes.  The serial chain (sub-steps + look-ahead update)
+  // runs on the library's own HIGH-PRIORITY stream `hi`, the bulk update on the caller's stream: the chain's small grids
+  // must not queue behind the thousands of CTAs of a bulk update, or the overlap is lost (with equal priorities the phase
+  // took the SUM of the two, 89 ms at N = 16,384).
   if (!g.fit_side) {
-    CDX_CUDA(cudaStreamCreateWithFlags(&g.fit_side, cudaStreamNonBlocking));
+    int least = 0, greatest = 0;
+    CDX_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    CDX_CUDA(cudaStreamCreateWithPriority(&g.fit_side, cudaStreamNonBlocking, greatest));
     CDX_CUDA(cudaEventCreateWithFlags(&g.fit_ev_trsm, cudaEventDisableTiming));
     CDX_CUDA(cudaEventCreateWithFlags(&g.fit_ev_rest, cudaEventDisableTiming));
   }
+  cudaStream_t hi = g.fit_side;
   CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, st));
-  CDX_CUDA(cudaStreamWaitEvent(g.fit_side, g.fit_ev_trsm, 0));      // the side stream starts after everything queued so far
+  CDX_CUDA(cudaStreamWaitEvent(hi, g.fit_ev_trsm, 0));              // the chain starts after everything queued so far
   constexpr int PW = 256;
   bool rest_pending = false;
   for (int c0 = 0; c0 < Np; c0 += PW) {
     const int w = Np - c0 < PW ? Np - c0 : PW;                       // panel width (a multiple of 64)
     for (int j0 = c0; j0 < c0 + w; j0 += 64) {
       double* Ajj = g.L + (int64_t)j0 * (ld + 1);
-      potrf_diag_kernel<<<1, 256, potrf_smem_bytes, st>>>(Ajj, ld, g.Dinv + (int64_t)(j0 / 64) * 4096, g.U + (int64_t)j0 * (ld + 1), g.flag, j0);
+      potrf_diag_kernel<<<1, 256, potrf_smem_bytes, hi>>>(Ajj, ld, g.Dinv + (int64_t)(j0 / 64) * 4096, g.U + (int64_t)j0 * (ld + 1), g.flag, j0);
       CDX_CHECK_LAUNCH(ctx);
       const int m = Np - (j0 + 64);
       if (m <= 0) continue;
       double* A21 = Ajj + 64 * ld;
       // L21 = A21 * inv(Ljj)^T   (in place: each CTA reads its own 64x64 row block completely before writing it)
       int rc = cdx_dgemm(ctx, false, false, m, 64, 64, 1.0, A21, ld, g.Dinv + (int64_t)(j0 / 64) * 4096, 64, 0.0, A21, ld, false,
-                         0, 1, 0, 0, 0, st);
+                         0, 1, 0, 0, 0, hi);
       if (rc) return rc;
       const int wr = c0 + w - (j0 + 64);                             // columns of this panel still to the right
       if (wr > 0) {                                                  // A[j0+64.., j0+64 .. c0+w) -= L21 L21[0:wr]^T
-        rc = cdx_dgemm(ctx, false, false, m, wr, 64, -1.0, A21, ld, A21, ld, 1.0, A21 + 64, ld, false, 0, 1, 0, 0, 0, st);
+        rc = cdx_dgemm(ctx, false, false, m, wr, 64, -1.0, A21, ld, A21, ld, 1.0, A21 + 64, ld, false, 0, 1, 0, 0, 0, hi);
         if (rc) return rc;
       }
     }
@@ -250,25 +256,25 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
     if (m2 <= 0) break;
     double* L21 = g.L + (int64_t)(c0 + w) * ld + c0;                 // [m2, w]
     double* A22 = g.L + (int64_t)(c0 + w) * (ld + 1);
-    CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, st));
-    if (rest_pending) CDX_CUDA(cudaStreamWaitEvent(st, g.fit_ev_rest, 0));   // the previous panel's trailing update touched these columns
-    // next panel's columns first (main stream), K = w
+    CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, hi));                    // this panel's columns are final
+    if (rest_pending) CDX_CUDA(cudaStreamWaitEvent(hi, g.fit_ev_rest, 0));   // the previous bulk update touched the next panel's columns
+    // next panel's columns first (chain stream), K = w
     const int wn = m2 < PW ? m2 : PW;
-    int rc = cdx_dgemm(ctx, false, false, m2, wn, w, -1.0, L21, ld, L21, ld, 1.0, A22, ld, false, 0, 1, 0, 0, 0, st);
+    int rc = cdx_dgemm(ctx, false, false, m2, wn, w, -1.0, L21, ld, L21, ld, 1.0, A22, ld, false, 0, 1, 0, 0, 0, hi);
     if (rc) return rc;
-    // the rest (rows / columns >= c0 + w + 256, lower tiles only) on the side stream
+    // the rest (rows / columns >= c0 + w + 256, lower tiles only) on the caller's stream
     const int m3 = m2 - wn;
-    CDX_CUDA(cudaStreamWaitEvent(g.fit_side, g.fit_ev_trsm, 0));
+    CDX_CUDA(cudaStreamWaitEvent(st, g.fit_ev_trsm, 0));
     if (m3 > 0) {
       double* L31 = L21 + (int64_t)wn * ld;
-      rc = cdx_dgemm(ctx, false, false, m3, m3, w, -1.0, L31, ld, L31, ld, 1.0, A22 + (int64_t)wn * (ld + 1), ld, true, 0, 1, 0, 0, 0,
-                     g.fit_side);
+      rc = cdx_dgemm(ctx, false, false, m3, m3, w, -1.0, L31, ld, L31, ld, 1.0, A22 + (int64_t)wn * (ld + 1), ld, true, 0, 1, 0, 0, 0, st);
       if (rc) return rc;
     }
-    CDX_CUDA(cudaEventRecord(g.fit_ev_rest, g.fit_side));
+    CDX_CUDA(cudaEventRecord(g.fit_ev_rest, st));
     rest_pending = true;
   }
-  if (rest_pending) CDX_CUDA(cudaStreamWaitEvent(st, g.fit_ev_rest, 0));
+  CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, hi));                      // the caller's stream continues after the chain's last step
+  CDX_CUDA(cudaStreamWaitEvent(st, g.fit_ev_trsm, 0));
   dim3 g2((Np + 255) / 256, Np);
   zero_upper_kernel<<<g2, 256, 0, st>>>(g.L, Np);
   CDX_CHECK_LAUNCH(ctx);

@@ -4,7 +4,7 @@
 tag=$1; shift
 mkdir -p gpurun_out
 python bench.py "$@" --no-cpu-baseline > gpurun_out/launches_${tag}_plain.json 2> gpurun_out/launches_${tag}_plain.err &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02_launches_$tag.csv python bench.py "$@" --no-cpu-baseline > gpurun_out/launches_${tag}_ncu.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c ${NCU_COUNT:-600} --csv --log-file gpurun_out/r02_launches_$tag.csv python bench.py "$@" --no-cpu-baseline > gpurun_out/launches_${tag}_ncu.log 2>&1
 echo "exit $?"; python - <<PY
 import csv, collections
 rows = [r for r in csv.reader(open("gpurun_out/r02_launches_$tag.csv")) if len(r) > 10 and r[0].isdigit()]
