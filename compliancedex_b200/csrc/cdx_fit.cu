@@ -63,7 +63,14 @@ __global__ void unpad_copy_kernel(const double* __restrict__ src, int N, int Np,
   if (j < N) dst[(int64_t)i * N + j] = src[(int64_t)i * Np + j];
 }
 
-// Cholesky of one 64x64 diagonal block in shared memory + its triangular inverse.
+// Cholesky of one 64x64 diagonal block in shared memory + its triangular inverse.  This kernel is the head of the serial
+// chain of every 64-column sub-step, so its latency counts in full:
+//   * factorisation: two barriers per column - every thread of column j takes sqrt(a[j][j]) itself (the raw diagonal stays
+//     in place until the end, the root goes to the padding column), so no thread waits for a broadcast;
+//   * inverse: recursive doubling, inv([L11 0; L21 L22]) = [X11 0; -X22 L21 X11, X22], all 256 threads at every level (six
+//     levels, two barriers each) instead of 64 serial forward substitutions; the s x s temporaries T = L21 X11 live in the
+//     mirror-image block of `a`'s upper triangle, which is dead (zeroed before the write-back).
+// Shared memory stays at 2 x 64 x 65 doubles: one of these CTAs must fit on an SM next to a 160 KB dgemm128 CTA.
 __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A, int64_t ld, double* __restrict__ Dinv,
                                                          double* __restrict__ Udiag, int* flag, int col0) {
   extern __shared__ double potrf_smem[];
@@ -73,14 +80,18 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A,
   for (int e = t; e < 4096; e += 256) a[e >> 6][e & 63] = A[(int64_t)(e >> 6) * ld + (e & 63)];
   __syncthreads();
   for (int j = 0; j < 64; j++) {
-    if (t == 0) {
-      double d = a[j][j];
-      if (!(d > 0.0)) atomicCAS(flag, 0, col0 + j + 1);
-      a[j][j] = sqrt(d);
+    if (t >= j && t < 64) {
+      const double d = a[j][j];
+      const double r = sqrt(d);
+      if (t == j) {
+        if (!(d > 0.0)) atomicCAS(flag, 0, col0 + j + 1);
+        a[j][64] = r;                              // the padding column holds the roots until the loop is over
+      } else {
+        a[t][j] /= r;
+      }
     }
     __syncthreads();
-    if (t > j && t < 64) a[t][j] /= a[j][j];
-    __syncthreads();
+    // trailing update of the lower triangle right of column j: thread -> column c = j+1+(t&63) strided, rows from c down
     for (int e = t; e < 4096; e += 256) {
       int r = e >> 6, c = e & 63;
       if (c > j && r >= c) a[r][c] = fma(-a[r][j], a[c][j], a[r][c]);
@@ -89,23 +100,31 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A,
   }
   for (int e = t; e < 4096; e += 256) {
     int r = e >> 6, c = e & 63;
-    if (c > r) a[r][c] = 0.0;
-    x[r][c] = 0.0;
+    x[r][c] = r == c ? 1.0 / a[r][64] : 0.0;
   }
+  if (t < 64) a[t][t] = a[t][64];
   __syncthreads();
-  if (t < 64) {  // column t of the inverse by forward substitution
-    const int c = t;
-    x[c][c] = 1.0 / a[c][c];
-    for (int i = c + 1; i < 64; i++) {
-      double s = 0.0;
-      for (int j = c; j < i; j++) s = fma(a[i][j], x[j][c], s);
-      x[i][c] = -s / a[i][i];
+  for (int s = 1; s < 64; s *= 2) {
+    const int ss = s * s, nout = 32 * s;           // (32 / s) pairs x s x s outputs
+    for (int e = t; e < nout; e += 256) {          // T = L21 X11 (X11 lower triangular) -> a[upper mirror block]
+      const int p = e / ss, i = (e / s) % s, j = e % s, base = 2 * p * s;
+      double acc = 0.0;
+      for (int k = j; k < s; k++) acc = fma(a[base + s + i][base + k], x[base + k][base + j], acc);
+      a[base + i][base + s + j] = acc;
     }
+    __syncthreads();
+    for (int e = t; e < nout; e += 256) {          // X21 = -X22 T (X22 lower triangular)
+      const int p = e / ss, i = (e / s) % s, j = e % s, base = 2 * p * s;
+      double acc = 0.0;
+      for (int k = 0; k <= i; k++) acc = fma(x[base + s + i][base + s + k], a[base + k][base + s + j], acc);
+      x[base + s + i][base + j] = -acc;
+    }
+    __syncthreads();
   }
-  __syncthreads();
   for (int e = t; e < 4096; e += 256) {
     int r = e >> 6, c = e & 63;
-    A[(int64_t)r * ld + c] = a[r][c];
+    const double v = c > r ? 0.0 : a[r][c];
+    A[(int64_t)r * ld + c] = v;
     Dinv[e] = x[r][c];
     Udiag[(int64_t)r * ld + c] = x[r][c];
   }
