@@ -122,8 +122,8 @@ def run_gpis_c3(args, rank, world, local):
                 "note": "the FP64 contraction L^-1 k* (N^2 flop/query) is evaluated as error-free INT8 slice products "
                         "(S(S+1)/2 byte-slice pairs); FP64 instructions and tcgen05 MMAs exclude each other on this chip "
                         "(csrc/cdx_mixbench.cu, DESIGN.md section 4), so the k* slices are generated ONCE per query by a separate "
-                        "FP64 kernel into the B-operand image and the MMA kernel is pure INT8; mean / grad_mean come from the "
-                        "separate TMA-staged FP64 mean kernel"}
+                        "FP64 kernel into the B-operand image and the MMA kernel is pure INT8; mean / grad_mean are "
+                        "accumulated by that same k* kernel (same distances) and reduced by i8x_mean_reduce_kernel"}
     else:
         roof = {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,128,unit> (FP64 DMMA)", "achieved": fp64_equiv,
                 "peak": dmma_peak, "unit": "TFLOP/s", "frac": (fp64_equiv / dmma_peak) if dmma_peak else None,
