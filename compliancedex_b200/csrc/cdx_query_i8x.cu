@@ -281,6 +281,19 @@ __global__ void __launch_bounds__(128) i8x_kstar_kernel(const double* __restrict
                                                         const double* __restrict__ Xa, const double* __restrict__ scq, int Np, double R,
                                                         double R3, int8_t* __restrict__ kq, double* __restrict__ part) {
   using G = xcfg<S, PAIR>;
+  // the part's training records (32 B each) and weights, staged once per CTA: every warp reads them at warp-uniform
+  // addresses, which from shared memory is a broadcast with a short, fixed latency - from global memory (through L1) the
+  // same loads left the kernel waiting on the scoreboard (ncu: long_scoreboard 7.5 stall cycles per issue, FP64 pipe 32 %)
+  __shared__ double2 sP[X_PART * 2];
+  __shared__ double sAl[X_PART];
+  {
+    const int p0 = blockIdx.y * X_PART, np = min(X_PART, Np - p0);
+    const double2* src = reinterpret_cast<const double2*>(pts) + (size_t)p0 * 2;
+    for (int i = threadIdx.x; i < np * 2; i += 128) sP[i] = __ldg(src + i);
+    if (MEAN)
+      for (int i = threadIdx.x; i < np; i += 128) sAl[i] = __ldg(Xa + 4 * (size_t)(p0 + i) + 3);
+  }
+  __syncthreads();
   const int64_t ql = (int64_t)blockIdx.x * 128 + threadIdx.x;
   if (ql >= Mc) return;
   const bool ok = ql < M;
@@ -295,7 +308,7 @@ __global__ void __launch_bounds__(128) i8x_kstar_kernel(const double* __restrict
   const int g0 = blockIdx.y * (X_PART / 16), g1 = min(g0 + X_PART / 16, Np / 16);
   double am[4] = {0, 0, 0, 0}, ax[4] = {0, 0, 0, 0}, ay[4] = {0, 0, 0, 0}, az[4] = {0, 0, 0, 0};
   for (int c16 = g0; c16 < g1; c16++) {
-    const double2* P2 = reinterpret_cast<const double2*>(pts) + (size_t)c16 * 32;
+    const double2* P2 = sP + (c16 - g0) * 32;
     unsigned ow[S][4];
 #pragma unroll
     for (int gq = 0; gq < 4; gq++) {
@@ -303,7 +316,7 @@ __global__ void __launch_bounds__(128) i8x_kstar_kernel(const double* __restrict
 #pragma unroll
       for (int p = 0; p < 4; p++) {
         const int j = gq * 4 + p;
-        const double2 a = __ldg(P2 + 2 * j), b = __ldg(P2 + 2 * j + 1);
+        const double2 a = P2[2 * j], b = P2[2 * j + 1];
         const double sd = fma(xq, a.x, fma(yq, a.y, fma(zq, b.x, b.y + qq)));
         const unsigned shi = (unsigned)__double2hiint(sd), slo = (unsigned)__double2loint(sd);
         const unsigned fb = __funnelshift_l(slo, shi - 0x38000000u, 3);     // float(s) by bit moves (no F2F)
@@ -318,7 +331,7 @@ __global__ void __launch_bounds__(128) i8x_kstar_kernel(const double* __restrict
         L[p] = (unsigned)__double2loint(res);
         H[p] = (unsigned)__double2hiint(res);
         if (MEAN) {
-          const double al = __ldg(Xa + 4 * (size_t)(c16 * 16 + j) + 3);   // alpha (0 on padded rows)
+          const double al = sAl[(c16 - g0) * 16 + j];      // alpha (0 on padded rows)
           am[p] = fma(al, k, am[p]);
           const double ac = al * fma(6.0, d, m6R);           // alpha c,  c = 6 (d - R)
           ax[p] = fma(ac, fma(0.5, a.x, xq), ax[p]);        // x - x_k  (the record holds -2 x_k)

@@ -33,8 +33,10 @@ elif what == "i8":
     M = 96 * 74 * waves
     X = synthetic_queries(M, 0, M).cuda()
     std = torch.empty(M, dtype=torch.float64, device="cuda")
-    for _ in range(3):
-        _lib.check(lib.cdx_gpis_query(g._ctx, X.data_ptr(), M, None, None, std.data_ptr(), None, st))
+    mean = torch.empty(M, dtype=torch.float64, device="cuda")
+    gm = torch.empty(M, 3, dtype=torch.float64, device="cuda")
+    for _ in range(3):      # the unit query of bench.py's gpis_c3: {mean, grad_mean, std}
+        _lib.check(lib.cdx_gpis_query(g._ctx, X.data_ptr(), M, mean.data_ptr(), gm.data_ptr(), std.data_ptr(), None, st))
     torch.cuda.synchronize()
 elif what == "fit":
     from compliancedex_b200.synthetic import synthetic_training_set
