@@ -130,6 +130,13 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A,
   }
 }
 
+// E11^-1 in the slab order of gpis_extw_kernel: [chunk c][column n][16 k], the 16-byte piece index XORed with 2 (n & 3)
+__global__ void pack_slab_kernel(const double* __restrict__ P, int Np, double* __restrict__ out) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x, n = blockIdx.y;
+  if (k >= Np) return;
+  const int c = k >> 4, kk = k & 15;
+  out[((size_t)c * Np + n) * 16 + ((((kk >> 1) ^ ((n & 3) << 1)) << 1) | (kk & 1))] = P[(size_t)n * Np + k];   // P is symmetric
+}
 __global__ void zero_upper_kernel(double* __restrict__ A, int Np) {
   int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
   if (j < Np && j > i) A[(int64_t)i * Np + j] = 0.0;
@@ -190,7 +197,8 @@ int gpis_reserve(cdx_ctx* ctx, int64_t N) {
   int64_t Np = (N + CDX_NPAD - 1) / CDX_NPAD * CDX_NPAD;
   if (Np > g.cap) {
     cudaFree(g.Xa); cudaFree(g.y1); cudaFree(g.E11); cudaFree(g.L); cudaFree(g.U); cudaFree(g.P);
-    cudaFree(g.Dinv); cudaFree(g.tmp);
+    cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.Pslab);
+    g.Pslab = nullptr;
     g.cap = 0;
     size_t mat = sizeof(double) * (size_t)Np * (size_t)Np;
     if (cudaMalloc(&g.Xa, sizeof(double) * 4 * Np) != cudaSuccess || cudaMalloc(&g.y1, sizeof(double) * Np) != cudaSuccess ||
@@ -202,6 +210,11 @@ int gpis_reserve(cdx_ctx* ctx, int64_t N) {
       return CDX_ERR_ALLOC;
     }
     g.cap = Np;
+  }
+  if (Np <= 448 && !g.Pslab && cudaMalloc(&g.Pslab, sizeof(double) * 448 * 448) != cudaSuccess) {
+    cudaGetLastError();
+    cdx_set_error("out of device memory for the slab copy of E11^-1");
+    return CDX_ERR_ALLOC;
   }
   if (!g.dR2) {
     CDX_CUDA(cudaMalloc(&g.dR2, sizeof(double)));
@@ -326,6 +339,10 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   if (rc) return rc;
   mirror_lower_kernel<<<g2, 256, 0, st>>>(g.P, Np);
   CDX_CHECK_LAUNCH(ctx);
+  if (Np <= 448) {
+    pack_slab_kernel<<<g2, 256, 0, st>>>(g.P, Np, g.Pslab);
+    CDX_CHECK_LAUNCH(ctx);
+  }
   fit_mark(g, 4, st);
   // alpha = U^T (U y1)
   trmv_lower_kernel<<<(Np + 7) / 8, 256, 0, st>>>(g.U, Np, g.y1, g.tmp);
@@ -395,7 +412,7 @@ extern "C" int cdx_destroy(cdx_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cdx_gpis_state& g = ctx->g;
   cudaFree(g.Xa); cudaFree(g.y1); cudaFree(g.E11); cudaFree(g.L); cudaFree(g.U); cudaFree(g.P);
-  cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.dR2); cudaFree(g.flag);
+  cudaFree(g.Dinv); cudaFree(g.tmp); cudaFree(g.dR2); cudaFree(g.flag); cudaFree(g.Pslab);
   cudaFree(ctx->hx); cudaFree(ctx->hout);
   for (int i = 0; i < 6; i++) if (g.fit_ev[i]) cudaEventDestroy(g.fit_ev[i]);
   if (g.fit_side) { cudaStreamDestroy(g.fit_side); cudaEventDestroy(g.fit_ev_trsm); cudaEventDestroy(g.fit_ev_rest); }

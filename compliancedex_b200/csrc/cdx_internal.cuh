@@ -60,6 +60,8 @@ struct cdx_gpis_state {
   double* L = nullptr;      // [Np,Np] lower Cholesky factor (upper part zero)
   double* U = nullptr;      // [Np,Np] L^-1 (lower, upper part zero)
   double* P = nullptr;      // [Np,Np] E11^-1 = U^T U (full symmetric)
+  double* Pslab = nullptr;  // states of <= 448 padded points: E11^-1 in slab order [Np/16][Np][16], 16-byte pieces XOR-swizzled by the
+                            // column index (piece ^ 2 (n & 3)) - the bulk-TMA stream of gpis_extw_kernel (cdx_query.cu)
   double* Dinv = nullptr;   // [Np/64, 64, 64] inverses of the diagonal blocks of L
   double* tmp = nullptr;    // [Np] scratch vector
   double* dR2 = nullptr;    // device scalar: max pairwise squared distance
@@ -87,7 +89,7 @@ struct cdx_gpis_state {
   bool fit_prof = false;
   cudaEvent_t fit_ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t i8_ready = nullptr;  // recorded after the slices were built: queries on any other stream wait for it
-  int ext_mode = 0;         // cdx_gpis_set_ext_mode: 0 = all-columns extended kernel for states <= 448 padded points, 1 = column-tiled kernel always
+  int ext_mode = 0;         // cdx_gpis_set_ext_mode: 0 = warp-specialised all-columns extended kernel for states <= 448 padded points, 2 = its single-role predecessor, 1 = column-tiled kernel always
   int var_mode = 0;         // cdx_gpis_set_var_mode: 0 auto, -1 always FP64 DMMA, 4/5/6 = INT8 slices whenever eligible
 };
 

@@ -421,6 +421,223 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, unsigne
                    (unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
 
+__device__ __forceinline__ void mbar_expect_tx_only(uint64_t* bar, unsigned bytes) {   // adds to the tx-count, does not arrive
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------ extended query, warp-specialised
+// gpis_extw_kernel: the all-columns extended query (see gpis_ext_kernel above for the arithmetic) with the roles separated.
+// Ablations of gpis_ext_kernel at 131,072 queries on hammer (N = 317): 1,245 us as is, 835 us with the DMMAs removed, 492 us
+// with the fragment loads removed as well, and the DMMAs alone are 730 us - the kernel took the SUM of its tensor time and
+// of everything else, because all sixteen warps did "everything else" (generate k*, issue 2,560 cp.async per slab, wait,
+// __syncthreads) together, chunk after chunk, and the tensor pipe idled meanwhile.  Here
+//   * warps 0-15 (consumers) only load fragments and issue DMMAs; they wait on / release mbarriers per ring slot, never
+//     the whole CTA; the epilogue uses a named barrier of their 512 threads;
+//   * warps 16-19 (generators) produce the k* chunks (and the mean / grad-mean sums) up to D chunks ahead;
+//   * the slabs of E11^-1 arrive by ONE bulk-TMA stream (a lane of the first generator warp issues <= 4 cp.async.bulk per
+//     slab) from a copy packed at fit time in slab order [chunk][column][16] (cdx_gpis_state::Pslab), whose 16-byte
+//     pieces are XOR-swizzled by the column index (piece ^ 2 (column & 3)): rows are 128 B with no padding, and the DMMA
+//     fragment pattern - lane (fr, fk) of step s reads k = 4s + fk of column fr, i.e. pieces 2s and 2s + 1 - touches 8
+//     distinct pieces per half-warp: conflict-free.  The k order of the accumulation is the one of the other two kernels,
+//     so w = E11^-1 k* is the same bit for bit.
+// A query's arithmetic (16 interleaved partial sums of the mean; chunk order of the accumulation; column-group order of the
+// epilogue) does not depend on TQ or the tile it lands in: results are bit-identical for every batch size and shard.
+constexpr int XW_GEN = 4;                       // generator warps
+constexpr int XW_THREADS = (EW * ERG + XW_GEN) * 32;
+constexpr int XW_LA = LDS;                      // k* tile row stride (doubles)
+__host__ __device__ constexpr int extw_depth(int nbw) { return nbw <= 5 ? 4 : 3; }
+__host__ __device__ constexpr size_t extw_smem(int nbw, int tq) {
+  return (size_t)extw_depth(nbw) * (nbw * 64) * 128 + sizeof(double) * ((size_t)extw_depth(nbw) * tq * XW_LA + 4 * (size_t)(nbw * 64) + 2 * tq * 3 +
+                                                                       EW * tq * 4) + 8 * (2 * extw_depth(nbw) + 2);
+}
+template <int KERNEL, int NBW, int TQ>
+__global__ void __launch_bounds__(XW_THREADS, 1)
+gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restrict__ Xa, const double* __restrict__ Pslab,
+                 int N, cdx_kparams kp, double bias, double prior, double* __restrict__ mean,
+                 double* __restrict__ gmean, double* __restrict__ stdv, double* __restrict__ gstd, int64_t ntiles) {
+  constexpr int Np = NBW * 64;
+  constexpr int RPG = TQ / ERG, MT = RPG / 8, WN = NBW * 8, D = extw_depth(NBW);
+  constexpr unsigned SLAB = Np * 128u;          // bytes
+  constexpr int QPG = TQ / 8;                   // queries per generator thread
+  extern __shared__ __align__(128) unsigned char xw_smem[];
+  double* Bs = reinterpret_cast<double*>(xw_smem);          // [D][Np][16] swizzled
+  double* As = Bs + (size_t)D * Np * 16;                    // [D][TQ][XW_LA]
+  double* sXa = As + D * TQ * XW_LA;                        // [Np][4]
+  double* sxq = sXa + 4 * Np;                               // [2][TQ][3]
+  double* red = sxq + 2 * TQ * 3;                           // [EW][TQ][4]
+  uint64_t* full = reinterpret_cast<uint64_t*>(red + EW * TQ * 4);   // [D] slab landed (tx bytes) + k* written (XW_GEN arrivals)
+  uint64_t* empty = full + D;                                        // [D] the 16 consumer warps have finished with the slot
+  uint64_t* epi = empty + D;                                         // [2] the consumers have finished the epilogue of a tile of this parity
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int kpad = (N + TK - 1) / TK * TK, nch = kpad / TK;
+  if (t == 0) {
+    for (int i = 0; i < D; i++) { mbar_init(full + i, XW_GEN); mbar_init(empty + i, EW * ERG); }
+    mbar_init(epi, EW * ERG); mbar_init(epi + 1, EW * ERG);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  for (int e = t; e < Np * 2; e += XW_THREADS)
+    reinterpret_cast<double2*>(sXa)[e] = __ldg(reinterpret_cast<const double2*>(Xa) + e);
+  __syncthreads();
+  const double2* Xa2 = reinterpret_cast<const double2*>(sXa);
+
+  if (warp >= EW * ERG) {
+    // ===================================================== generators: k* chunks, slab stream, mean / grad mean
+    const int gt = t - EW * ERG * 32, kslot = gt & 15, qb = gt >> 4;   // queries qb + 8 i
+    int64_t gcs = 0;
+    int ti = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ti++) {
+      const int64_t q0 = tile * TQ;
+      const int par = ti & 1;
+      mbar_wait(epi + par, ((ti >> 1) & 1) ^ 1);     // the epilogue of tile ti - 2 has finished with sxq[par]
+      double xq[QPG], yq[QPG], zq[QPG], ma[QPG], gxa[QPG], gya[QPG], gza[QPG];
+#pragma unroll
+      for (int i = 0; i < QPG; i++) {
+        const int64_t q = q0 + qb + 8 * i;
+        const bool ok = q < M;
+        xq[i] = ok ? Xq[q * 3] : 0.0; yq[i] = ok ? Xq[q * 3 + 1] : 0.0; zq[i] = ok ? Xq[q * 3 + 2] : 0.0;
+        ma[i] = gxa[i] = gya[i] = gza[i] = 0.0;
+        if (kslot < 3) sxq[par * TQ * 3 + (qb + 8 * i) * 3 + kslot] = kslot == 0 ? xq[i] : (kslot == 1 ? yq[i] : zq[i]);
+      }
+      for (int c = 0; c < nch; c++, gcs++) {
+        const int slot = (int)(gcs % D);
+        mbar_wait(empty + slot, (unsigned)(((gcs / D) & 1) ^ 1));
+        if (gt == 0) {
+          mbar_expect_tx_only(full + slot, SLAB);
+          const char* src = reinterpret_cast<const char*>(Pslab) + (size_t)c * SLAB;
+          char* dst = reinterpret_cast<char*>(Bs) + (size_t)slot * SLAB;
+          for (unsigned off = 0; off < SLAB; off += 16384u) tma_bulk_g2s(dst + off, src + off, min(16384u, SLAB - off), full + slot);
+        }
+        const int j = c * TK + kslot;
+        const double2 p0 = Xa2[2 * j], p1 = Xa2[2 * j + 1];
+        double* arow = As + (size_t)slot * TQ * XW_LA + kslot;
+#pragma unroll
+        for (int i = 0; i < QPG; i++) {
+          const double dx = xq[i] - p0.x, dy = yq[i] - p0.y, dz = zq[i] - p1.x;
+          double k, cc;
+          cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, cc);
+          if (j >= N) k = 0.0;
+          arow[(qb + 8 * i) * XW_LA] = k;
+          const double a = p1.y;  // alpha (0 on padded rows)
+          ma[i] = fma(a, k, ma[i]);
+          const double ac = a * cc;
+          gxa[i] = fma(ac, dx, gxa[i]); gya[i] = fma(ac, dy, gya[i]); gza[i] = fma(ac, dz, gza[i]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(full + slot);
+      }
+      // mean / grad mean: the 16 slot sums of a query, butterfly over its 16 lanes
+#pragma unroll
+      for (int i = 0; i < QPG; i++) {
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+          ma[i] += __shfl_xor_sync(0xffffffffu, ma[i], o); gxa[i] += __shfl_xor_sync(0xffffffffu, gxa[i], o);
+          gya[i] += __shfl_xor_sync(0xffffffffu, gya[i], o); gza[i] += __shfl_xor_sync(0xffffffffu, gza[i], o);
+        }
+        const int64_t q = q0 + qb + 8 * i;
+        if (kslot == 0 && q < M) {
+          if (mean) mean[q] = ma[i] + bias;
+          if (gmean) { gmean[q * 3] = gxa[i]; gmean[q * 3 + 1] = gya[i]; gmean[q * 3 + 2] = gza[i]; }
+        }
+      }
+    }
+    return;
+  }
+
+  // ======================================================= consumers: fragments + DMMA, epilogue
+  const int fr = lane >> 2, fk = lane & 3;
+  const int cg = warp % EW, rg = warp / EW;
+  const int a_off = (rg * RPG + fr) * XW_LA + fk;           // k = 4 s + fk
+  const int b_off = (cg * WN + fr) * 16 + (fk & 1);
+  const int xs = fk >> 1, xr = (fr & 3) << 1;               // 16-byte piece of step s: (2 s + xs) ^ xr
+  int64_t gcs = 0;
+  int ti = 0;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ti++) {
+    const int64_t q0 = tile * TQ;
+    const int par = ti & 1;
+    double acc[MT][NBW][2];
+#pragma unroll
+    for (int i = 0; i < MT; i++)
+#pragma unroll
+      for (int j = 0; j < NBW; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+    for (int c = 0; c < nch; c++, gcs++) {
+      const int slot = (int)(gcs % D);
+      mbar_wait(full + slot, (unsigned)((gcs / D) & 1));
+      const double* a_s = As + (size_t)slot * TQ * XW_LA + a_off;
+      const double* b_s = Bs + (size_t)slot * Np * 16 + b_off;
+#pragma unroll
+      for (int s4 = 0; s4 < 4; s4++) {
+        const int xo = ((2 * s4 + xs) ^ xr) * 2;
+        double a[MT], b[NBW];
+#pragma unroll
+        for (int i = 0; i < MT; i++) a[i] = a_s[i * 8 * XW_LA + 4 * s4];
+#pragma unroll
+        for (int j = 0; j < NBW; j++) b[j] = b_s[j * 128 + xo];
+#pragma unroll
+        for (int i = 0; i < MT; i++)
+#pragma unroll
+          for (int j = 0; j < NBW; j++) cdx_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty + slot);
+    }
+    // ---- epilogue: (k.w, w c dx, w c dy, w c dz) over this warp's columns, per owned row
+    const double* sq = sxq + par * TQ * 3;
+    asm volatile("bar.sync 1, %0;\n" ::"n"(EW * ERG * 32) : "memory");     // the previous tile's final sums have been read from `red`
+#pragma unroll
+    for (int i = 0; i < MT; i++) {
+      const int r = rg * RPG + i * 8 + fr;
+      const double rx = sq[r * 3], ry = sq[r * 3 + 1], rz = sq[r * 3 + 2];
+      double ev[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int j = 0; j < NBW; j++)
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          const int col = cg * WN + j * 8 + 2 * fk + e;
+          if (col < N) {
+            const double2 p0 = Xa2[2 * col], p1 = Xa2[2 * col + 1];
+            const double dx = rx - p0.x, dy = ry - p0.y, dz = rz - p1.x;
+            double k, cc;
+            cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, cc);
+            const double w = acc[i][j][e];
+            ev[0] = fma(k, w, ev[0]);
+            const double wc = w * cc;
+            ev[1] = fma(wc, dx, ev[1]); ev[2] = fma(wc, dy, ev[2]); ev[3] = fma(wc, dz, ev[3]);
+          }
+        }
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        double sres = ev[e];
+        sres += __shfl_xor_sync(0xffffffffu, sres, 1); sres += __shfl_xor_sync(0xffffffffu, sres, 2);
+        if (fk == 0) red[(cg * TQ + r) * 4 + e] = sres;
+      }
+    }
+    asm volatile("bar.sync 1, %0;\n" ::"n"(EW * ERG * 32) : "memory");
+    if (t < TQ && q0 + t < M) {
+      const int64_t q = q0 + t;
+      double v[4];
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        double sres = red[(0 * TQ + t) * 4 + e];
+#pragma unroll
+        for (int w = 1; w < EW; w++) sres += red[(w * TQ + t) * 4 + e];      // column groups in order
+        v[e] = sres;
+      }
+      const double var = prior - v[0];
+      const double sd = sqrt(fabs(var));  // gpis.py:59
+      if (stdv) stdv[q] = sd;
+      if (gstd) {
+        const double f = (var < 0.0 ? 1.0 : -1.0) / sd;
+        gstd[q * 3] = f * v[1]; gstd[q * 3 + 1] = f * v[2]; gstd[q * 3 + 2] = f * v[3];
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(epi + par);      // sxq[par] may be overwritten (tile ti + 2)
+  }
+}
+
 constexpr int MQ = 64;  // queries per CTA pass (4 lanes each)
 
 template <int KERNEL>
@@ -557,6 +774,20 @@ int launch_ext(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* g
   return CDX_OK;
 }
 
+template <int KERNEL, int NBW, int TQ>
+int launch_extw(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
+                cudaStream_t st) {
+  cdx_gpis_state& g = ctx->g;
+  const size_t smem = extw_smem(NBW, TQ);
+  if (int rc = cdx_smem_attr(ctx, gpis_extw_kernel<KERNEL, NBW, TQ>, smem)) return rc;
+  const int64_t ntiles = (M + TQ - 1) / TQ;
+  const int grid = (int)min(ntiles, (int64_t)ctx->sms);
+  gpis_extw_kernel<KERNEL, NBW, TQ><<<grid, XW_THREADS, smem, st>>>(X, M, g.Xa, g.Pslab, (int)g.N, cdx_make_kparams(g), g.bias, g.prior,
+                                                                    mean, gmean, stdv, gstd, ntiles);
+  CDX_CHECK_LAUNCH(ctx);
+  return CDX_OK;
+}
+
 // the all-columns extended kernel covers states of up to 448 padded points (7 DMMA column tiles per warp); 16-query tiles
 // while 32-query tiles would leave SMs idle
 template <int KERNEL>
@@ -564,6 +795,14 @@ int dispatch_ext(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double*
                  cudaStream_t st) {
   const int nbw = (int)(ctx->g.Np / 64);
   const bool small = (M + 31) / 32 < (int64_t)ctx->sms;
+  if (ctx->g.ext_mode == 0 && ctx->g.Pslab) {      // warp-specialised kernel (bulk-TMA slab stream)
+#define CDX_EXTW(NB) case NB: return small ? launch_extw<KERNEL, NB, 16>(ctx, X, M, mean, gmean, stdv, gstd, st) \
+                                           : launch_extw<KERNEL, NB, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
+    switch (nbw) {
+      CDX_EXTW(1); CDX_EXTW(2); CDX_EXTW(3); CDX_EXTW(4); CDX_EXTW(5); CDX_EXTW(6); CDX_EXTW(7);
+    }
+#undef CDX_EXTW
+  }
 #define CDX_EXT(NB) case NB: return small ? launch_ext<KERNEL, NB, 16>(ctx, X, M, mean, gmean, stdv, gstd, st) \
                                           : launch_ext<KERNEL, NB, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
   switch (nbw) {
@@ -583,7 +822,7 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
   // the column tile TN depends on the state only, never on the batch size: a query's result is then bit-identical
   // whichever TQ variant (or shard) evaluates it
   if (gstd) {
-    if (g.Np <= 448 && g.ext_mode == 0) return dispatch_ext<KERNEL>(ctx, X, M, mean, gmean, stdv, gstd, st);
+    if (g.Np <= 448 && g.ext_mode != 1) return dispatch_ext<KERNEL>(ctx, X, M, mean, gmean, stdv, gstd, st);
     if (small_batch) return big ? launch_var<KERNEL, 128, true, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
                                 : launch_var<KERNEL, 64, true, 32>(ctx, X, M, mean, gmean, stdv, gstd, st);
     return big ? launch_var<KERNEL, 128, true, 128>(ctx, X, M, mean, gmean, stdv, gstd, st)
@@ -630,7 +869,7 @@ extern "C" int cdx_gpis_query(cdx_ctx* ctx, const double* X, int64_t M, double* 
 }
 
 extern "C" int cdx_gpis_set_ext_mode(cdx_ctx* ctx, int mode) {
-  if (!ctx || mode < 0 || mode > 1) { cdx_set_error("cdx_gpis_set_ext_mode: 0 or 1"); return CDX_ERR_ARG; }
+  if (!ctx || mode < 0 || mode > 2) { cdx_set_error("cdx_gpis_set_ext_mode: 0, 1 or 2"); return CDX_ERR_ARG; }
   ctx->g.ext_mode = mode;
   return CDX_OK;
 }

@@ -20,7 +20,7 @@ for name, box in (("mug", 0.1), ("hammer", 0.18), ("dummy", 0.1)):
                torch.empty(M, dtype=torch.float64, device="cuda"), torch.empty(M, 3, dtype=torch.float64, device="cuda")]
         st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
         res = []
-        for mode in (0, 1):
+        for mode in (0, 2, 1):
             g.set_ext_mode(mode)
 
             def step():

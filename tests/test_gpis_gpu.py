@@ -204,25 +204,29 @@ def test_normal_index_and_multinormals_against_reference_golden(name, golden_dir
 
 @pytest.mark.parametrize("name", NAMES)
 def test_extended_query_kernels_agree_and_are_batch_invariant(name, golden_dir):
-    """the extended query has two kernels for small states: the all-columns kernel (default: k* generated once per query
-    tile) and the column-tiled one.  Both against the reference golden; the all-columns kernel's results must not depend on
+    """the extended query has three kernels for small states: the warp-specialised all-columns kernel (default, mode 0: k*
+    generated once per query tile by generator warps, E11^-1 streamed by bulk TMA), its single-role predecessor (mode 2) and
+    the column-tiled one (mode 1).  All against the reference golden; the all-columns kernels' results must not depend on
     the batch (16- vs 32-query tiles, position in the batch)."""
     ref = np.load(os.path.join(golden_dir, f"gpis_{name}.npz"))
     g = _gpis(name)
     prior = float(g.R) ** 3
     X = torch.from_numpy(ref["X"]).cuda()
     outs = {}
-    for mode in (0, 1):
+    for mode in (0, 1, 2):
         g.set_ext_mode(mode)
         mean, std, gm, gs = g.pred_with_grads(X)
         _check(mean.cpu().numpy(), std.cpu().numpy(), gm.cpu().numpy(), gs.cpu().numpy(), ref, prior)
         outs[mode] = (mean, std, gm, gs)
-    for a, b in zip(outs[0], outs[1]):
-        assert (a - b).abs().max() <= 1e-9 * max(1.0, float(b.abs().max()))
-    g.set_ext_mode(0)
+    for m in (0, 2):
+        for a, b in zip(outs[m], outs[1]):
+            assert (a - b).abs().max() <= 1e-9 * max(1.0, float(b.abs().max()))
     b = 0.18 if name in ("hammer", "coffeebottle") else (0.15 if name == "banana" else 0.1)
     big = ((torch.rand(148 * 32 * 2 + 37, 3, generator=torch.Generator().manual_seed(3), dtype=torch.float64) * 2 - 1) * b).cuda()
-    full = g.pred_with_grads(big)                       # 32-query tiles, persistent CTAs walking several tiles
-    part = g.pred_with_grads(big[1001:1001 + 333])      # 16-query tiles, other positions
-    for a, b_ in zip(full, part):
-        assert torch.equal(a[1001:1001 + 333], b_)
+    for mode in (0, 2):
+        g.set_ext_mode(mode)
+        full = g.pred_with_grads(big)                       # 32-query tiles, persistent CTAs walking several tiles
+        part = g.pred_with_grads(big[1001:1001 + 333])      # 16-query tiles, other positions
+        for a, b_ in zip(full, part):
+            assert torch.equal(a[1001:1001 + 333], b_)
+    g.set_ext_mode(0)
