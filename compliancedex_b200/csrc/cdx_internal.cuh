@@ -157,6 +157,34 @@ __device__ __forceinline__ void cdx_kernel_eval(double s /* squared distance */,
   }
 }
 
+// k only, for NQ squared distances at once, written stage by stage so that the NQ dependent chains (conversion, rsqrt seed,
+// two Newton steps, cubic) overlap; each value is the one cdx_kernel_eval returns, bit for bit
+template <int KERNEL, int NQ>
+__device__ __forceinline__ void cdx_kernel_k_batch(const double (&s)[NQ], const cdx_kparams& kp, double (&k)[NQ]) {
+  if (KERNEL == CDX_KERNEL_RBF) {
+#pragma unroll
+    for (int i = 0; i < NQ; i++) k[i] = exp(-0.5 * s[i] * kp.inv_s2);
+    return;
+  }
+  float sf[NQ];
+  double y[NQ], d[NQ], hy[NQ];
+#pragma unroll
+  for (int i = 0; i < NQ; i++) sf[i] = fmaxf((float)s[i], 1e-30f);
+#pragma unroll
+  for (int i = 0; i < NQ; i++) y[i] = (double)rsqrtf(sf[i]);
+#pragma unroll
+  for (int i = 0; i < NQ; i++) { d[i] = s[i] * y[i]; hy[i] = 0.5 * y[i]; }
+#pragma unroll
+  for (int i = 0; i < NQ; i++) d[i] = fma(fma(-d[i], d[i], s[i]), hy[i], d[i]);
+#pragma unroll
+  for (int i = 0; i < NQ; i++) d[i] = fma(fma(-d[i], d[i], s[i]), hy[i], d[i]);
+#pragma unroll
+  for (int i = 0; i < NQ; i++) {
+    const double kt = fma(s[i], fma(2.0, d[i], -3.0 * kp.R), kp.R3);
+    k[i] = KERNEL == CDX_KERNEL_TPS ? kt : 0.3 * exp(-0.5 * s[i] * kp.inv_s2) + 0.7 * kt;
+  }
+}
+
 static inline cdx_kparams cdx_make_kparams(const cdx_gpis_state& g) {
   cdx_kparams kp;
   kp.kernel = g.kernel;

@@ -443,15 +443,16 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 //     fragment pattern - lane (fr, fk) of step s reads k = 4s + fk of column fr, i.e. pieces 2s and 2s + 1 - touches 8
 //     distinct pieces per half-warp: conflict-free.  The k order of the accumulation is the one of the other two kernels,
 //     so w = E11^-1 k* is the same bit for bit.
-// A query's arithmetic (16 interleaved partial sums of the mean; chunk order of the accumulation; column-group order of the
-// epilogue) does not depend on TQ or the tile it lands in: results are bit-identical for every batch size and shard.
+// A query's arithmetic (chunk order of the accumulation; column order inside a thread, then the four lanes of a row, then
+// the column groups in order in the epilogue) does not depend on TQ or the tile it lands in: results are bit-identical for
+// every batch size and shard.
 constexpr int XW_GEN = 4;                       // generator warps
 constexpr int XW_THREADS = (EW * ERG + XW_GEN) * 32;
 constexpr int XW_LA = LDS;                      // k* tile row stride (doubles)
 __host__ __device__ constexpr int extw_depth(int nbw) { return nbw <= 5 ? 4 : 3; }
 __host__ __device__ constexpr size_t extw_smem(int nbw, int tq) {
   return (size_t)extw_depth(nbw) * (nbw * 64) * 128 + sizeof(double) * ((size_t)extw_depth(nbw) * tq * XW_LA + 4 * (size_t)(nbw * 64) + 2 * tq * 3 +
-                                                                       EW * tq * 4) + 8 * (2 * extw_depth(nbw) + 2);
+                                                                       EW * tq * 8) + 8 * (2 * extw_depth(nbw) + 2);
 }
 template <int KERNEL, int NBW, int TQ>
 __global__ void __launch_bounds__(XW_THREADS, 1)
@@ -467,8 +468,8 @@ gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restr
   double* As = Bs + (size_t)D * Np * 16;                    // [D][TQ][XW_LA]
   double* sXa = As + D * TQ * XW_LA;                        // [Np][4]
   double* sxq = sXa + 4 * Np;                               // [2][TQ][3]
-  double* red = sxq + 2 * TQ * 3;                           // [EW][TQ][4]
-  uint64_t* full = reinterpret_cast<uint64_t*>(red + EW * TQ * 4);   // [D] slab landed (tx bytes) + k* written (XW_GEN arrivals)
+  double* red = sxq + 2 * TQ * 3;                           // [EW][TQ][8]
+  uint64_t* full = reinterpret_cast<uint64_t*>(red + EW * TQ * 8);   // [D] slab landed (tx bytes) + k* written (XW_GEN arrivals)
   uint64_t* empty = full + D;                                        // [D] the 16 consumer warps have finished with the slot
   uint64_t* epi = empty + D;                                         // [2] the consumers have finished the epilogue of a tile of this parity
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -484,7 +485,11 @@ gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restr
   const double2* Xa2 = reinterpret_cast<const double2*>(sXa);
 
   if (warp >= EW * ERG) {
-    // ===================================================== generators: k* chunks, slab stream, mean / grad mean
+    // ===================================================== generators: k* chunks, slab stream
+    // thread (kslot, qb) owns training point kslot of every chunk for the queries qb + 8 i.  Only k* is produced here: the
+    // generators share the FP64 pipe with the DMMAs, so their chain is kept short (the mean and its gradient, which need
+    // the same k and c, are formed in the consumers' epilogue, where k and c are evaluated per (query, column) anyway)
+    // and the QPG evaluations of a chunk are written stage by stage so that their dependent chains overlap.
     const int gt = t - EW * ERG * 32, kslot = gt & 15, qb = gt >> 4;   // queries qb + 8 i
     int64_t gcs = 0;
     int ti = 0;
@@ -492,13 +497,12 @@ gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restr
       const int64_t q0 = tile * TQ;
       const int par = ti & 1;
       mbar_wait(epi + par, ((ti >> 1) & 1) ^ 1);     // the epilogue of tile ti - 2 has finished with sxq[par]
-      double xq[QPG], yq[QPG], zq[QPG], ma[QPG], gxa[QPG], gya[QPG], gza[QPG];
+      double xq[QPG], yq[QPG], zq[QPG];
 #pragma unroll
       for (int i = 0; i < QPG; i++) {
         const int64_t q = q0 + qb + 8 * i;
         const bool ok = q < M;
         xq[i] = ok ? Xq[q * 3] : 0.0; yq[i] = ok ? Xq[q * 3 + 1] : 0.0; zq[i] = ok ? Xq[q * 3 + 2] : 0.0;
-        ma[i] = gxa[i] = gya[i] = gza[i] = 0.0;
         if (kslot < 3) sxq[par * TQ * 3 + (qb + 8 * i) * 3 + kslot] = kslot == 0 ? xq[i] : (kslot == 1 ? yq[i] : zq[i]);
       }
       for (int c = 0; c < nch; c++, gcs++) {
@@ -513,34 +517,17 @@ gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restr
         const int j = c * TK + kslot;
         const double2 p0 = Xa2[2 * j], p1 = Xa2[2 * j + 1];
         double* arow = As + (size_t)slot * TQ * XW_LA + kslot;
+        double sq[QPG], kv[QPG];
 #pragma unroll
         for (int i = 0; i < QPG; i++) {
           const double dx = xq[i] - p0.x, dy = yq[i] - p0.y, dz = zq[i] - p1.x;
-          double k, cc;
-          cdx_kernel_eval<KERNEL>(fma(dx, dx, fma(dy, dy, dz * dz)), kp, k, cc);
-          if (j >= N) k = 0.0;
-          arow[(qb + 8 * i) * XW_LA] = k;
-          const double a = p1.y;  // alpha (0 on padded rows)
-          ma[i] = fma(a, k, ma[i]);
-          const double ac = a * cc;
-          gxa[i] = fma(ac, dx, gxa[i]); gya[i] = fma(ac, dy, gya[i]); gza[i] = fma(ac, dz, gza[i]);
+          sq[i] = fma(dx, dx, fma(dy, dy, dz * dz));
         }
+        cdx_kernel_k_batch<KERNEL, QPG>(sq, kp, kv);
+#pragma unroll
+        for (int i = 0; i < QPG; i++) arow[(qb + 8 * i) * XW_LA] = j >= N ? 0.0 : kv[i];
         __syncwarp();
         if (lane == 0) mbar_arrive(full + slot);
-      }
-      // mean / grad mean: the 16 slot sums of a query, butterfly over its 16 lanes
-#pragma unroll
-      for (int i = 0; i < QPG; i++) {
-#pragma unroll
-        for (int o = 1; o < 16; o <<= 1) {
-          ma[i] += __shfl_xor_sync(0xffffffffu, ma[i], o); gxa[i] += __shfl_xor_sync(0xffffffffu, gxa[i], o);
-          gya[i] += __shfl_xor_sync(0xffffffffu, gya[i], o); gza[i] += __shfl_xor_sync(0xffffffffu, gza[i], o);
-        }
-        const int64_t q = q0 + qb + 8 * i;
-        if (kslot == 0 && q < M) {
-          if (mean) mean[q] = ma[i] + bias;
-          if (gmean) { gmean[q * 3] = gxa[i]; gmean[q * 3 + 1] = gya[i]; gmean[q * 3 + 2] = gza[i]; }
-        }
       }
     }
     return;
@@ -590,7 +577,7 @@ gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restr
     for (int i = 0; i < MT; i++) {
       const int r = rg * RPG + i * 8 + fr;
       const double rx = sq[r * 3], ry = sq[r * 3 + 1], rz = sq[r * 3 + 2];
-      double ev[4] = {0.0, 0.0, 0.0, 0.0};
+      double ev[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};   // k.w, w c (x - x_j) | alpha.k, alpha c (x - x_j)
 #pragma unroll
       for (int j = 0; j < NBW; j++)
 #pragma unroll
@@ -605,26 +592,31 @@ gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restr
             ev[0] = fma(k, w, ev[0]);
             const double wc = w * cc;
             ev[1] = fma(wc, dx, ev[1]); ev[2] = fma(wc, dy, ev[2]); ev[3] = fma(wc, dz, ev[3]);
+            ev[4] = fma(p1.y, k, ev[4]);
+            const double ac = p1.y * cc;
+            ev[5] = fma(ac, dx, ev[5]); ev[6] = fma(ac, dy, ev[6]); ev[7] = fma(ac, dz, ev[7]);
           }
         }
 #pragma unroll
-      for (int e = 0; e < 4; e++) {
+      for (int e = 0; e < 8; e++) {
         double sres = ev[e];
         sres += __shfl_xor_sync(0xffffffffu, sres, 1); sres += __shfl_xor_sync(0xffffffffu, sres, 2);
-        if (fk == 0) red[(cg * TQ + r) * 4 + e] = sres;
+        if (fk == 0) red[(cg * TQ + r) * 8 + e] = sres;
       }
     }
     asm volatile("bar.sync 1, %0;\n" ::"n"(EW * ERG * 32) : "memory");
     if (t < TQ && q0 + t < M) {
       const int64_t q = q0 + t;
-      double v[4];
+      double v[8];
 #pragma unroll
-      for (int e = 0; e < 4; e++) {
-        double sres = red[(0 * TQ + t) * 4 + e];
+      for (int e = 0; e < 8; e++) {
+        double sres = red[(0 * TQ + t) * 8 + e];
 #pragma unroll
-        for (int w = 1; w < EW; w++) sres += red[(w * TQ + t) * 4 + e];      // column groups in order
+        for (int w = 1; w < EW; w++) sres += red[(w * TQ + t) * 8 + e];      // column groups in order
         v[e] = sres;
       }
+      if (mean) mean[q] = v[4] + bias;
+      if (gmean) { gmean[q * 3] = v[5]; gmean[q * 3 + 1] = v[6]; gmean[q * 3 + 2] = v[7]; }
       const double var = prior - v[0];
       const double sd = sqrt(fabs(var));  // gpis.py:59
       if (stdv) stdv[q] = sd;
