@@ -205,7 +205,10 @@ def timed(step, steps, world, rank, local, sample_clocks=True):
         step()
     e1.record()
     barrier(world)
-    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    local_ms = e0.elapsed_time(e1)
+    ms = max_over_ranks(local_ms, world)
+    if world > 1:
+        sys.stderr.write("[bench] rank %d: %.3f ms per step on this rank, %.3f max over ranks\n" % (rank, local_ms / steps, ms / steps))
     return ms / steps, (sampler.stop() if sampler else None)
 
 
