@@ -13,17 +13,58 @@
 // (idle copy quads and out-of-range candidate groups evaluate a duplicate row whose results are dropped).  With a run-time
 // partial mask each double shuffle compiled into a WARPSYNC collective region (~13 instructions, 30 % of the kernel's SASS).
 constexpr unsigned PG_FULL = 0xffffffffu;
-__device__ __forceinline__ void pg_gather4(unsigned /*fmask*/, double v, double* out) {
+// The four lanes of a row exchange per-finger scalars either by width-4 shuffles (a double shuffle is two SHFL plus lane
+// arithmetic: the ~130 double shuffles of the step kernel were 2,600 of its 11,000 SASS instructions, and the kernel is
+// instruction-FETCH bound - ncu: `no_instruction` is 53 % of its stall samples at 1,024 candidates, every warp walks 177 KB
+// of straight-line code once) or, SMX, through a 448-byte shared-memory scratch per lane quad: one STS.64, one
+// __syncwarp and two LDS.128 per gather.  Two single-value slots alternate (the next gather's barrier orders the reuse),
+// followed by a [12][4] area for the batched gather of the reverse pass.  Values and summation order are the same.
+constexpr int PG_XQ = 60;   // doubles per quad: 2 x 4 + 12 x 4, padded to 480 B (quads of a warp then start 96 B apart mod 128)
+struct pg_xchg {
+  double* q;   // this quad's scratch (SMX) or nullptr
+  int n;       // gathers done so far (selects the slot)
+};
+template <bool SMX>
+__device__ __forceinline__ void pg_gather4(pg_xchg& x, int f, double v, double* out) {
+  if (SMX) {
+    double* slot = x.q + (x.n & 1) * 4;
+    x.n++;
+    slot[f] = v;
+    __syncwarp();
+    const double2 a = *reinterpret_cast<const double2*>(slot), b = *reinterpret_cast<const double2*>(slot + 2);
+    out[0] = a.x; out[1] = a.y; out[2] = b.x; out[3] = b.y;
+  } else {
 #pragma unroll
-  for (int j = 0; j < 4; j++) out[j] = __shfl_sync(PG_FULL, v, j, 4);
+    for (int j = 0; j < 4; j++) out[j] = __shfl_sync(PG_FULL, v, j, 4);
+  }
 }
-__device__ __forceinline__ double pg_sum4(unsigned fmask, double v) {   // ((v0 + v1) + v2) + v3, identical on the four lanes
+template <bool SMX>
+__device__ __forceinline__ double pg_sum4(pg_xchg& x, int f, double v) {   // ((v0 + v1) + v2) + v3, identical on the four lanes
   double g[4];
-  pg_gather4(fmask, v, g);
+  pg_gather4<SMX>(x, f, v, g);
   return ((g[0] + g[1]) + g[2]) + g[3];
 }
+// NV finger-ordered sums at once (NV <= 12)
+template <bool SMX, int NV>
+__device__ __forceinline__ void pg_sum4_batch(pg_xchg& x, int f, const double* v, double* out) {
+  if (SMX) {
+    double* area = x.q + 8;
+#pragma unroll
+    for (int e = 0; e < NV; e++) area[e * 4 + f] = v[e];
+    __syncwarp();
+#pragma unroll
+    for (int e = 0; e < NV; e++) {
+      const double2 a = *reinterpret_cast<const double2*>(area + e * 4), b = *reinterpret_cast<const double2*>(area + e * 4 + 2);
+      out[e] = ((a.x + a.y) + b.x) + b.y;
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < NV; e++) out[e] = pg_sum4<false>(x, f, v[e]);
+  }
+}
 
-__device__ __forceinline__ void cdx_pg_row_coop(int f, unsigned fmask, const double (*a)[3], const double (*T)[3],
+template <bool SMX>
+__device__ __forceinline__ void cdx_pg_row_coop(int f, pg_xchg& xc, const double (*a)[3], const double (*T)[3],
                                                 const double* k, const double* dist, const double* sd,
                                                 const double (*gmu)[3], const double (*gsd)[3], const double* tdist,
                                                 const double (*gT)[3], const double* noise, const cdx_pg_const& C,
@@ -88,21 +129,21 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, unsigned fmask, const dou
   const double mraw = ang - C.cos_mu;
   const double margin = mraw < -0.9999 ? -0.9999 : mraw;
   margin_f = margin;
-  const double reward = pg_sum4(fmask, 0.2 * log(ang + 1.0) + 0.8 * log(margin + 1.0));
+  const double reward = pg_sum4<SMX>(xc, f, 0.2 * log(ang + 1.0) + 0.8 * log(margin + 1.0));
   double fnf;
   {
     const double fx = kf * diff[0], fy = kf * diff[1], fz = kf * diff[2];
     fnf = sqrt(fx * fx + fy * fy + fz * fz);
   }
   double fn4[4];
-  pg_gather4(fmask, fnf, fn4);
+  pg_gather4<SMX>(xc, f, fnf, fn4);
   double fmin = fn4[0];
   for (int i = 1; i < 4; i++) fmin = fn4[i] < fmin ? fn4[i] : fmin;
   const double exf = exp(fmin - fnf);
-  const double esum = pg_sum4(fmask, exf);
+  const double esum = pg_sum4<SMX>(xc, f, exf);
   const double smf = exf / esum;
   const double zf = fnf * smf;
-  const double force_cost = -pg_sum4(fmask, zf > C.force_clamp ? C.force_clamp : zf);
+  const double force_cost = -pg_sum4<SMX>(xc, f, zf > C.force_clamp ? C.force_clamp : zf);
   // ---- compute_contact_margin (:703-710), GPIS terms (:733-736)
   double vv[3], dd[3];
   for (int r = 0; r < 3; r++) vv[r] = af[r] - Tf[r];
@@ -111,12 +152,12 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, unsigned fmask, const dou
   const double ang2 = cdx_dot3(dd, n);
   const double m2 = ang2 - C.cos_mu;
   double cm = 0.0;
-  if (C.w_cm != 0.0) cm = pg_sum4(fmask, 0.1 * log(ang2 + 1.0) + 0.9 * log(m2 + 1.0));
+  if (C.w_cm != 0.0) cm = pg_sum4<SMX>(xc, f, 0.1 * log(ang2 + 1.0) + 0.9 * log(m2 + 1.0));
   double dist_cost = 0.0, tar_cost = 0.0;
   for (int i = 0; i < 4; i++) { dist_cost += fabs(dist[i]); tar_cost += tdist[i]; }
   const double sdf = sd[f];
   double lsd[4];
-  pg_gather4(fmask, C.var_sum ? sdf : log(100.0 * sdf), lsd);
+  pg_gather4<SMX>(xc, f, C.var_sum ? sdf : log(100.0 * sdf), lsd);
   int fstar = 0;
   for (int i = 1; i < 4; i++)
     if (lsd[i] > lsd[fstar]) fstar = i;
@@ -132,7 +173,7 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, unsigned fmask, const dou
 
   // ================================================================================ reverse pass, finger f
   const double gzf = (zf <= C.force_clamp) ? -1.0 : 0.0;
-  const double zs = pg_sum4(fmask, gzf * zf);
+  const double zs = pg_sum4<SMX>(xc, f, gzf * zf);
   const double gfn = gzf * smf * (1.0 - fnf) + smf * zs;
   double gS1f[3], gS2f[3], Zr[9], gdiff[3];
   for (int r = 0; r < 3; r++) { ga[r] = 0.0; gTo[r] = 0.0; }
@@ -177,8 +218,14 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, unsigned fmask, const dou
       for (int r = 0; r < 3; r++) ga[r] += C.uncertainty / sdf * gsd[f][r];
   }
   double gR[9], gt[3];
-  for (int e = 0; e < 9; e++) gR[e] = pg_sum4(fmask, Zr[e]);
-  for (int r = 0; r < 3; r++) gt[r] = pg_sum4(fmask, gdiff[r]);
+  {
+    double zin[12], zout[12];
+    for (int e = 0; e < 9; e++) zin[e] = Zr[e];
+    for (int r = 0; r < 3; r++) zin[9 + r] = gdiff[r];
+    pg_sum4_batch<SMX, 12>(xc, f, zin, zout);
+    for (int e = 0; e < 9; e++) gR[e] = zout[e];
+    for (int r = 0; r < 3; r++) gt[r] = zout[9 + r];
+  }
   // t = sum_i w_i (S2_i - R S1_i) / W
   double rgt[3], gwf;
   cdx_mtv(R, gt, rgt);

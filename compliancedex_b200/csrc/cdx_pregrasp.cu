@@ -200,6 +200,8 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   __shared__ double sg[CPB][NPAR];      // gradient
   __shared__ double sq[CPB][NGP];       // GPIS outputs of this candidate
   __shared__ double sm1[CPB][NPAR], sm2[CPB][NPAR];
+  extern __shared__ __align__(16) double sx[];         // [CPB * 4][PG_XQ] quad exchange scratch of the row evaluation (prob variant; dynamic:
+                                                       // the static arrays above and below already fill 41 KB of the 48 KB static limit)
   __shared__ __align__(8) float sJ[CPB][4][3 * CDX_MAX_CHAIN_DOF];
   constexpr int HW = (int)((sizeof(cdx_hand_dev) + 3) / 4);
   __shared__ __align__(16) unsigned shand[CPB][HW];   // the group's own copy of the finger chains (FK walks them body by body)
@@ -294,7 +296,8 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
       for (int r = 0; r < 3; r++) a[f][r] = V ? tips[f][r] : Tp[f][r] + S.coeff[pc][f] * (tips[f][r] - Tp[f][r]);
     const double* gq = sq[cl];
     CDX_PG_TICK(8);
-    cdx_pg_row_coop(l, fmask, a, Tp, par + 16, gq + u * 4, gq + 16 + u * 4, reinterpret_cast<const double (*)[3]>(gq + 32 + u * 12),
+    pg_xchg xc = {V == 0 ? &sx[(cl * 4 + p) * PG_XQ] : nullptr, 0};
+    cdx_pg_row_coop<V == 0>(l, xc, a, Tp, par + 16, gq + u * 4, gq + 16 + u * 4, reinterpret_cast<const double (*)[3]>(gq + 32 + u * 12),
                     reinterpret_cast<const double (*)[3]>(gq + 80 + u * 12), m9, reinterpret_cast<const double (*)[3]>(g9), noise,
                     S.C, lossp, mg, ga, gTr, gkr);
     CDX_PG_TICK(6);
@@ -835,10 +838,15 @@ static int pg_iteration(cdx_ctx* ctx, cdx_pg_state* s, int do_step, double* loss
   mark(1, st);
   CDX_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
   mark(4, st);
+  constexpr size_t PG_SX_BYTES = sizeof(double) * CPB * 4 * PG_XQ;
+  if (s->setup.variant == 0) {
+    if (int rc2 = cdx_smem_attr(ctx, pg_step_kernel<0, 2>, PG_SX_BYTES)) return rc2;
+    if (int rc2 = cdx_smem_attr(ctx, pg_step_kernel<0, 3>, PG_SX_BYTES)) return rc2;
+  }
   int occ = (nb + CPB - 1) / CPB > 2 * (int64_t)ctx->sms ? 3 : 2;
   if (s->tune_occ == 2 || s->tune_occ == 3) occ = s->tune_occ;
 #define PG_STEP(V) PG_STEP_O(V, 2); else PG_STEP_O(V, 3)
-#define PG_STEP_O(V, O) if (occ == O) pg_step_kernel<V, O><<<(unsigned)((nb + CPB - 1) / CPB), CPB * 16, 0, st>>>(                                  \
+#define PG_STEP_O(V, O) if (occ == O) pg_step_kernel<V, O><<<(unsigned)((nb + CPB - 1) / CPB), CPB * 16, V == 0 ? PG_SX_BYTES : 0, st>>>(                                  \
       s->hand_dev, B, b0, b1, U, s->setup, s->prm, s->q, s->k, s->T, s->palm, s->tl, s->J, s->dist, s->sd, s->gmu, s->gsd,      \
       s->mean9, s->gmean9, loss, margin, grad, do_step, it_base, it_off, s->nan_dev, s->adam_tab, s->m1, s->m2, s->oq, s->ok,   \
       s->oT, s->opalm, s->omargin, s->ovalue, s->Xext, s->Xmean, s->mring, s->latched, s->latch)
