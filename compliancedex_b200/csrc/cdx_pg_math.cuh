@@ -214,7 +214,9 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
 
 // euler_angles_to_matrix(e, "XYZ") = Rx(e0) Ry(e1) Rz(e2)  (math_utils.py:97-123); optional partials dR/de_i
 CDX_HD void cdx_euler_xyz(const double* e, double* R, double* dR0, double* dR1, double* dR2) {
-  const double ca = cos(e[0]), sa = sin(e[0]), cb = cos(e[1]), sb = sin(e[1]), cc = cos(e[2]), sc = sin(e[2]);
+  // sincos shares the argument reduction of the pair (half the code and latency of separate calls; same values)
+  double ca, sa, cb, sb, cc, sc;
+  sincos(e[0], &sa, &ca); sincos(e[1], &sb, &cb); sincos(e[2], &sc, &cc);
   const double X[9] = {1, 0, 0, 0, ca, -sa, 0, sa, ca}, Y[9] = {cb, 0, sb, 0, 1, 0, -sb, 0, cb}, Z[9] = {cc, -sc, 0, sc, cc, 0, 0, 0, 1};
   double XY[9];
   cdx_mm(X, Y, XY);
