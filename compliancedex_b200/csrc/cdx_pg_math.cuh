@@ -86,7 +86,16 @@ CDX_HD void cdx_mmf(const float* A, const float* B, float* C) {
 // un-normalised quaternion (x,y,z,w) of CoordinateTransform.get_quaternion (spatial_vector_algebra.py:108-136):
 // branch -1 is `t > M33` (:118-122), branch i in {0,1,2} the i,j,k rotation of :123-133.  The map is affine in R;
 // with add_one = 0 it is applied to a differential dR.  Returns the component the normaliser is built from.
-CDX_HD float cdx_quat_raw(const float* R, int branch, float one, float* q) {
+template <int I>
+CDX_HD float cdx_quat_raw_axis(const float* R, float one, float* q) {
+  constexpr int i = I, j = (i + 1) % 3, k = (j + 1) % 3;
+  q[i] = R[i * 3 + i] - (R[j * 3 + j] + R[k * 3 + k]) + one;
+  q[j] = R[i * 3 + j] + R[j * 3 + i];
+  q[k] = R[k * 3 + i] + R[i * 3 + k];
+  q[3] = R[k * 3 + j] - R[j * 3 + k];
+  return q[i];
+}
+CDX_HD float cdx_quat_raw(const float* R, int branch, float one, float* q) {   // compile-time subscripts in every branch
   if (branch < 0) {
     q[0] = R[7] - R[5];
     q[1] = R[2] - R[6];
@@ -94,12 +103,9 @@ CDX_HD float cdx_quat_raw(const float* R, int branch, float one, float* q) {
     q[3] = R[0] + R[4] + R[8] + one;
     return q[3];
   }
-  const int i = branch, j = (i + 1) % 3, k = (j + 1) % 3;
-  q[i] = R[i * 3 + i] - (R[j * 3 + j] + R[k * 3 + k]) + one;
-  q[j] = R[i * 3 + j] + R[j * 3 + i];
-  q[k] = R[k * 3 + i] + R[i * 3 + k];
-  q[3] = R[k * 3 + j] - R[j * 3 + k];
-  return q[i];
+  if (branch == 0) return cdx_quat_raw_axis<0>(R, one, q);
+  if (branch == 1) return cdx_quat_raw_axis<1>(R, one, q);
+  return cdx_quat_raw_axis<2>(R, one, q);
 }
 
 // Fingertip position in the hand frame and the gradient the REFERENCE's autograd produces for it
@@ -116,14 +122,22 @@ CDX_HD float cdx_quat_raw(const float* R, int branch, float one, float* q) {
 template <bool REC = false>   // REC: q64 given (compile-time so that the non-recursive path keeps no per-joint rotation array)
 CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, float (*J)[CDX_MAX_CHAIN_DOF],
                           const double* q64 = nullptr) {
+  // Every local array below is indexed with compile-time subscripts only (the joint axis and the running dof count select
+  // through predicates): on the device they stay in registers.  With run-time subscripts (R[r * 3 + axis], om[nd][r], ...)
+  // the whole chain walked through local memory - a load-to-use latency on every step of a serial chain that four lanes
+  // per candidate execute alone.
   float R[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f};
   float p[3] = {0.f, 0.f, 0.f};
   float om[CDX_MAX_CHAIN_DOF][3], org[CDX_MAX_CHAIN_DOF][3];
+#pragma unroll
+  for (int c = 0; c < CDX_MAX_CHAIN_DOF; c++)
+    for (int r = 0; r < 3; r++) { om[c][r] = 0.f; org[c][r] = 0.f; }
   float jall[REC ? CDX_MAX_CHAIN : 1][9];
   int nd = 0;
   for (int i = 0; i < ch.n; i++) {
-    float* jr = jall[REC ? i : 0];
+    float jr[9];
     const float* F = ch.fixed_rot[i];
+    const int a = ch.axis[i];
     if (ch.dof[i] >= 0) {
       const float ang = CDX_FM(ch.sign[i], q32[ch.dof[i]]);
       float c, s;
@@ -134,32 +148,57 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
         c = cosf(ang); s = sinf(ang);             // torch.cos/sin on a CUDA float32 tensor are these libdevice functions
       }
       // fixed @ R_axis(ang): the two columns orthogonal to the axis mix, the axis column is kept
-      const int a = ch.axis[i], u = (a + 1) % 3, v = (a + 2) % 3;
+      const int u = (a + 1) % 3, v = (a + 2) % 3;
+#pragma unroll
       for (int r = 0; r < 3; r++) {
-        jr[r * 3 + u] = CDX_FA(CDX_FM(F[r * 3 + u], c), CDX_FM(F[r * 3 + v], s));
-        jr[r * 3 + v] = CDX_FS(CDX_FM(F[r * 3 + v], c), CDX_FM(F[r * 3 + u], s));
-        jr[r * 3 + a] = F[r * 3 + a];
+        const float fu = F[r * 3 + u], fv = F[r * 3 + v], fa = F[r * 3 + a];
+        const float ju = CDX_FA(CDX_FM(fu, c), CDX_FM(fv, s)), jv = CDX_FS(CDX_FM(fv, c), CDX_FM(fu, s));
+#pragma unroll
+        for (int col = 0; col < 3; col++) jr[r * 3 + col] = col == a ? fa : (col == u ? ju : jv);
       }
     } else {
+#pragma unroll
       for (int e = 0; e < 9; e++) jr[e] = F[e];
+    }
+    if (REC) {
+#pragma unroll
+      for (int b = 0; b < CDX_MAX_CHAIN; b++)
+        if (b == i)
+          for (int e = 0; e < 9; e++) jall[REC ? b : 0][e] = jr[e];
     }
     // CoordinateTransform.multiply_transform (spatial_vector_algebra.py:98-103)
     float Rn[9], pn[3];
     cdx_mmf(R, jr, Rn);
+    const float x0 = ch.xyz[i][0], x1 = ch.xyz[i][1], x2 = ch.xyz[i][2];
+#pragma unroll
     for (int r = 0; r < 3; r++)
-      pn[r] = CDX_FA(CDX_FA(CDX_FA(CDX_FM(R[r * 3], ch.xyz[i][0]), CDX_FM(R[r * 3 + 1], ch.xyz[i][1])), CDX_FM(R[r * 3 + 2], ch.xyz[i][2])), p[r]);
+      pn[r] = CDX_FA(CDX_FA(CDX_FA(CDX_FM(R[r * 3], x0), CDX_FM(R[r * 3 + 1], x1)), CDX_FM(R[r * 3 + 2], x2)), p[r]);
+#pragma unroll
     for (int e = 0; e < 9; e++) R[e] = Rn[e];
+#pragma unroll
     for (int r = 0; r < 3; r++) p[r] = pn[r];
     if (ch.dof[i] >= 0 && nd < CDX_MAX_CHAIN_DOF) {
-      const int a = ch.axis[i];
-      for (int r = 0; r < 3; r++) { om[nd][r] = ch.sign[i] * R[r * 3 + a]; org[nd][r] = p[r]; }
+      const float sg = ch.sign[i];
+#pragma unroll
+      for (int c = 0; c < CDX_MAX_CHAIN_DOF; c++)
+        if (c == nd) {
+#pragma unroll
+          for (int r = 0; r < 3; r++) {
+            om[c][r] = sg * (a == 0 ? R[r * 3] : (a == 1 ? R[r * 3 + 1] : R[r * 3 + 2]));
+            org[c][r] = p[r];
+          }
+        }
       nd++;
     }
   }
   if (REC) {   // recursive=True association (rigid_body.py:118-127)
     float Ra[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f}, pa[3] = {0.f, 0.f, 0.f};
     for (int i = ch.n - 1; i >= 0; i--) {
-      const float* jr = jall[i];
+      float jr[9];
+#pragma unroll
+      for (int b = 0; b < CDX_MAX_CHAIN; b++)
+        if (b == i)
+          for (int e = 0; e < 9; e++) jr[e] = jall[REC ? b : 0][e];
       float Rn[9], pn[3];
       cdx_mmf(jr, Ra, Rn);
       for (int r = 0; r < 3; r++)
@@ -176,7 +215,7 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
   if (!(t > 1.f)) {
     branch = 0;
     if (R[4] > R[0]) branch = 1;
-    if (R[8] > R[branch * 4]) branch = 2;
+    if (R[8] > (branch == 0 ? R[0] : R[4])) branch = 2;
   }
   float qr[4];
   const float tn = cdx_quat_raw(R, branch, 1.f, qr);
@@ -191,13 +230,21 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
   for (int r = 0; r < 3; r++)
     tip[r] = CDX_FA(p[r], CDX_FA(CDX_FA(CDX_FM(o[r], aw), CDX_FM(CDX_FM(cvo[r], qw), 2.f)), CDX_FM(CDX_FM(qv[r], qvo), 2.f)));
   for (int c = 0; c < nd; c++) {
-    float d[3] = {p[0] - org[c][0], p[1] - org[c][1], p[2] - org[c][2]}, dp[3];
-    cdx_cross3f(om[c], d, dp);
+    float omc[3], orc[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) { omc[r] = om[0][r]; orc[r] = org[0][r]; }
+#pragma unroll
+    for (int b = 1; b < CDX_MAX_CHAIN_DOF; b++)
+      if (b == c)
+        for (int r = 0; r < 3; r++) { omc[r] = om[b][r]; orc[r] = org[b][r]; }
+    float d[3] = {p[0] - orc[0], p[1] - orc[1], p[2] - orc[2]}, dp[3];
+    cdx_cross3f(omc, d, dp);
     float dR[9];  // [omega]x R
+#pragma unroll
     for (int col = 0; col < 3; col++) {
       const float rc[3] = {R[col], R[3 + col], R[6 + col]};
       float x[3];
-      cdx_cross3f(om[c], rc, x);
+      cdx_cross3f(omc, rc, x);
       dR[col] = x[0]; dR[3 + col] = x[1]; dR[6 + col] = x[2];
     }
     float dq[4];
@@ -206,10 +253,17 @@ CDX_HD void cdx_fk_finger(const cdx_chain& ch, const float* q32, float* tip, flo
     float dcvo[3];
     cdx_cross3f(dqv, o, dcvo);
     const float dqvo = cdx_dot3f(dqv, o);
-    for (int r = 0; r < 3; r++)
-      J[r][c] = dp[r] + (o[r] * (4.f * qw * dqw) + 2.f * (dqw * cvo[r] + qw * dcvo[r]) + 2.f * (dqv[r] * qvo + qv[r] * dqvo));
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+      const float jv = dp[r] + (o[r] * (4.f * qw * dqw) + 2.f * (dqw * cvo[r] + qw * dcvo[r]) + 2.f * (dqv[r] * qvo + qv[r] * dqvo));
+#pragma unroll
+      for (int b = 0; b < CDX_MAX_CHAIN_DOF; b++)
+        if (b == c) J[r][b] = jv;               // compile-time column subscript: a caller's local J stays in registers
+    }
   }
-  for (int c = nd; c < CDX_MAX_CHAIN_DOF; c++) J[0][c] = J[1][c] = J[2][c] = 0.f;
+#pragma unroll
+  for (int c = 0; c < CDX_MAX_CHAIN_DOF; c++)
+    if (c >= nd) J[0][c] = J[1][c] = J[2][c] = 0.f;
 }
 
 // euler_angles_to_matrix(e, "XYZ") = Rx(e0) Ry(e1) Rz(e2)  (math_utils.py:97-123); optional partials dR/de_i

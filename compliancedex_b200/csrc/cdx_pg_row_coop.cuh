@@ -81,14 +81,18 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, pg_xchg& xc, const double
   S2[4][0] = 0.0; S2[4][1] = 0.0; S2[4][2] = -C.dummy_M;
   w[4] = C.dummy_k;
   double c1[3] = {0, 0, 0}, c2[3] = {0, 0, 0}, W = 0.0;
-  for (int i = 0; i < np; i++) {
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    if (i >= np) continue;   // compile-time subscripts: the point sets stay in registers
     for (int r = 0; r < 3; r++) { c1[r] += S1[i][r]; c2[r] += S2[i][r]; }
     W += w[i];
   }
   for (int r = 0; r < 3; r++) { c1[r] /= np; c2[r] /= np; }
   double A[5][3], Bm[5][3], H[9];
   for (int e = 0; e < 9; e++) H[e] = 1e-6 * noise[e];
-  for (int i = 0; i < np; i++) {
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    if (i >= np) continue;   // compile-time subscripts: the point sets stay in registers
     for (int r = 0; r < 3; r++) { A[i][r] = w[i] * (S1[i][r] - c1[r]); Bm[i][r] = w[i] * (S2[i][r] - c2[r]); }
     for (int r = 0; r < 3; r++)
       for (int c = 0; c < 3; c++) H[r * 3 + c] += A[i][r] * Bm[i][c];
@@ -107,7 +111,9 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, pg_xchg& xc, const double
     for (int c = 0; c < 3; c++) R[r * 3 + c] = V[r * 3] * U[c * 3] + V[r * 3 + 1] * U[c * 3 + 1] + dsg * V[r * 3 + 2] * U[c * 3 + 2];
   const double lam[3] = {S[0], S[1], dsg * S[2]};
   double t[3] = {0, 0, 0}, RS1[5][3];
-  for (int i = 0; i < np; i++) {
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    if (i >= np) continue;   // compile-time subscripts: the point sets stay in registers
     cdx_mv(R, S1[i], RS1[i]);
     for (int r = 0; r < 3; r++) t[r] += w[i] * (S2[i][r] - RS1[i][r]);
   }
@@ -236,7 +242,9 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, pg_xchg& xc, const double
     const double wi = kf / W;
     for (int r = 0; r < 3; r++) { gS2f[r] = wi * gt[r]; gS1f[r] -= wi * rgt[r]; }
   }
-  for (int i = 0; i < np; i++) {
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    if (i >= np) continue;   // compile-time subscripts: the point sets stay in registers
     const double wi = w[i] / W;
     for (int r = 0; r < 3; r++)
       for (int c = 0; c < 3; c++) gR[r * 3 + c] -= wi * gt[r] * S1[i][c];
@@ -255,7 +263,9 @@ __device__ __forceinline__ void cdx_pg_row_coop(int f, pg_xchg& xc, const double
   cdx_mm(Rt, Y0, GH);
   // H = sum_i A_i B_i^T: the centroid terms need every point (replicated), the rest is this finger's
   double sA[3] = {0, 0, 0}, sB[3] = {0, 0, 0};
-  for (int i = 0; i < np; i++) {
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    if (i >= np) continue;   // compile-time subscripts: the point sets stay in registers
     double gAi[3], gBi[3];
     cdx_mv(GH, Bm[i], gAi);
     cdx_mtv(GH, A[i], gBi);

@@ -88,7 +88,8 @@ template <int V>   // V = optimizer variant (cdx_pregrasp_params.variant), compi
 __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ hand, const cdx_pg_setup& S, int U, int64_t b,
                                                int f, const double* q, const double* Tf, const double* palm6,
                                                double* __restrict__ tl, float* __restrict__ J, double* __restrict__ Xext,
-                                               double* __restrict__ Xmean, double* __restrict__ tips_out) {
+                                               double* __restrict__ Xmean, double* __restrict__ tips_out,
+                                               const float* q32s = nullptr) {
   const int64_t gid = b * 4 + f;
   double tlf[3], tw[3];
   float Jf[3][CDX_MAX_CHAIN_DOF];
@@ -97,9 +98,12 @@ __device__ __forceinline__ void pg_emit_points(const cdx_hand_dev* __restrict__ 
     for (int r = 0; r < 3; r++)
       for (int c = 0; c < CDX_MAX_CHAIN_DOF; c++) Jf[r][c] = 0.f;
   } else {
-    float q32[16], tip[3];
+    float q32l[16], tip[3];
+    if (!q32s) {
 #pragma unroll
-    for (int i = 0; i < 16; i++) q32[i] = i < S.n_dofs ? (float)q[i] : 0.f;                  // q.float(), :665
+      for (int i = 0; i < 16; i++) q32l[i] = i < S.n_dofs ? (float)q[i] : 0.f;               // q.float(), :665
+    }
+    const float* q32 = q32s ? q32s : q32l;   // step kernel: the float32 angles are staged in shared memory (run-time subscripts)
     // Kin variant: q stays float64 and the chain is composed recursively (:436, robot_model.py:243-251)
     cdx_fk_finger<V == 1>(hand->finger[f], q32, tip, Jf, V == 1 ? q : nullptr);
     for (int r = 0; r < 3; r++) tlf[r] = (double)tip[r];                                     // .double(), :666
@@ -203,6 +207,7 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
   extern __shared__ __align__(16) double sx[];         // [CPB * 4][PG_XQ] quad exchange scratch of the row evaluation (prob variant; dynamic:
                                                        // the static arrays above and below already fill 41 KB of the 48 KB static limit)
   __shared__ __align__(8) float sJ[CPB][4][3 * CDX_MAX_CHAIN_DOF];
+  __shared__ float sq32[V != 2 ? CPB : 1][16];        // float32 joint angles of the new iterate
   constexpr int HW = (int)((sizeof(cdx_hand_dev) + 3) / 4);
   __shared__ __align__(16) unsigned shand[CPB][HW];   // the group's own copy of the finger chains (FK walks them body by body)
   CDX_PG_TICK(7);
@@ -461,10 +466,11 @@ pg_step_kernel(const cdx_hand_dev* __restrict__ hand, int64_t B, int64_t b0, int
     else if (i < 32) T[b * 12 + i - 20] = pv;
     else palm[b * 6 + i - 32] = pv;
   }
+  if (V != 2) sq32[cl][sub] = sub < nd ? (float)par[sub] : 0.f;       // q.float() (:665) of the new iterate, for the FK below
   __syncwarp(gmask);
   CDX_PG_TICK(11);
   // ---- FK + GPIS query points of the NEW iterate (what pg_points_kernel does for the first iteration)
-  if (p == 0) pg_emit_points<V>(hs, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr);
+  if (p == 0) pg_emit_points<V>(hs, S, U, b, f, par, par + 20 + f * 3, par + 32, tl, J, Xext, Xmean, nullptr, V != 2 ? sq32[cl] : nullptr);
   CDX_PG_TICK(12);
 }
 
