@@ -28,7 +28,8 @@ def _candidates(hand, obj, total):
     from compliancedex_b200.synthetic import surface_center, synthetic_candidates
     doc = load_hand(hand)
     d = np.load(state_path(f"{obj}_state"))
-    q0, T0, k0, palm = synthetic_candidates(doc, total, surface_center(d["X1"], d["y1"]), seed=100)
+    center = surface_center(d["X1"], d["y1"])
+    q0, T0, k0, palm = synthetic_candidates(doc, total, center, seed=100)
     return doc, q0, T0, k0, palm, int(d["X1"].shape[0])
 
 
@@ -92,6 +93,27 @@ def run_pregrasp(args, rank, world, local, tag):
     nl = ctypes.c_int()
     _lib.check(lib.cdx_pregrasp_profile_read(gp._ctx, kms, ctypes.byref(nl), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
     _lib.check(lib.cdx_pregrasp_profile(gp._ctx, 0))
+    # the extended query ALONE at the same size (one group's queries, nothing else on the GPU): what the kernel does when it does
+    # not share the SMs with the other group's step / mean kernels
+    groups_p = max(1, nl.value // piters)
+    nq = (B + groups_p - 1) // groups_p * 4
+    Xa = ((torch.rand(nq, 3, generator=torch.Generator().manual_seed(5), dtype=torch.float64) * 2 - 1) * 0.1).to(q0d.device)
+    Xa += gp.X1.to(q0d.device).double().mean(dim=0)          # a 0.2 m box around the object
+    o = [torch.empty(nq, dtype=torch.float64, device=q0d.device), torch.empty(nq, 3, dtype=torch.float64, device=q0d.device),
+         torch.empty(nq, dtype=torch.float64, device=q0d.device), torch.empty(nq, 3, dtype=torch.float64, device=q0d.device)]
+    st_ = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def ext_alone():
+        _lib.check(lib.cdx_gpis_query(gp._ctx, Xa.data_ptr(), nq, o[0].data_ptr(), o[1].data_ptr(), o[2].data_ptr(), o[3].data_ptr(), st_))
+    for _ in range(3):
+        ext_alone()
+    ea0, ea1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ea0.record()
+    for _ in range(20):
+        ext_alone()
+    ea1.record()
+    torch.cuda.synchronize()
+    ext_alone_ms = ea0.elapsed_time(ea1) / 20
     if rank != 0:
         return None
     groups = max(1, nl.value // piters)
@@ -120,12 +142,17 @@ def run_pregrasp(args, rank, world, local, tag):
         "e2e": {"value": total_units / (ms_e2e * 1e-3), "unit": "candidate-iters/s",
                 "h2d_bytes_per_step": int(B * (16 + 12 + 4 + 6) * 8), "d2h_bytes_per_step": int(B * (16 + 4 + 12 + 6 + 4) * 8 + 16)},
         "gpu_launches": int(launches), "clocks": clocks,
-        "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,ext> (FP64 DMMA) inside the pregrasp iteration",
+        "roofline": {"bound": "tensor", "kernel": "gpis_extw_kernel<TPS> (FP64 DMMA; warp-specialised extended query) inside the pregrasp "
+                                                   "iteration, timed beside the other candidate group's kernels",
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if peak else None,
                      "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench (MEASURED_PEAKS.json has no "
                                     "FP64 figure; its bf16 %s = %.0f TF/s)" % (src, peaks.get("bf16_tflops", 0)),
                      "flop_per_query": flop_ext, "queries_per_launch": ext_queries, "launch_groups": groups,
-                     "traffic": ncu_traffic(args.ncu_summary_pg, "gpis_var_kernel"),
+                     "traffic": ncu_traffic(args.ncu_summary_pg, "gpis_extw_kernel"),
+                     "kernel_alone": {"ms": ext_alone_ms, "queries": nq,
+                                      "achieved": flop_ext * nq / (ext_alone_ms * 1e-3) / 1e12,
+                                      "frac": (flop_ext * nq / (ext_alone_ms * 1e-3) / 1e12 / peak) if peak else None,
+                                      "note": "same launch size, nothing else on the GPU"},
                      "kernel_ms_per_launch": per_launch, "kernel_share_of_group_critical_path": share,
                      "iteration_ms_vs_sum_of_group_critical_paths": {"timed_loop": ms_iter, "sum": crit * groups},
                      "note": "per-launch times from %d extra iterations with CUDA events around each launch, in the timed loop's own "
