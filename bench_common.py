@@ -143,9 +143,11 @@ def _physical_index(local):
     return local
 
 
-def i8_peak(pipes):
-    """best measured tcgen05.mma kind::i8 rate (TOP/s) over the operand shapes cdx_pipebench times"""
-    vals = [v for k, v in pipes.items() if k.startswith("i8_mma_") and isinstance(v, (int, float)) and v > 0]
+def i8_peak(pipes, sustained=False):
+    """best measured tcgen05.mma kind::i8 rate (TOP/s) over the operand shapes cdx_pipebench times: the burst figures (a kernel
+    timed alone) or the sustained ones (the same loop back to back for ~3 s under the power cap: a kernel timed inside a long step)"""
+    vals = [v for k, v in pipes.items() if k.startswith("i8_mma_") and k.endswith("_sustained") == sustained
+            and isinstance(v, (int, float)) and v > 0]
     return max(vals) if vals else None
 
 
