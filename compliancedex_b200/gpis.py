@@ -123,8 +123,9 @@ class GPIS:
             _lib.check(_lib.load().cdx_gpis_set_var_mode(self._ctx, self._var_mode))
 
     def set_ext_mode(self, mode):
-        """kernel of the extended query (mean, std and both gradients) on states of up to 448 padded points: 0 all-columns
-        kernel (default), 1 the column-tiled kernel that larger states use (include/cdx.h cdx_gpis_set_ext_mode)."""
+        """kernel of the extended query (mean, std and both gradients) on states of up to 448 padded points: 0 warp-specialised
+        all-columns kernel (default), 2 its single-role predecessor, 1 the column-tiled kernel that larger states use
+        (include/cdx.h cdx_gpis_set_ext_mode)."""
         self._ext_mode = int(mode)
         if self._ctx is not None:
             _lib.check(_lib.load().cdx_gpis_set_ext_mode(self._ctx, self._ext_mode))

@@ -75,8 +75,10 @@ int cdx_gpis_query(cdx_ctx* ctx, const double* X_dev, int64_t M, double* mean_de
  *  4..6 INT8 path with that many slices whenever the state is eligible (TPS, padded N <= 8192), any M. */
 int cdx_gpis_set_var_mode(cdx_ctx* ctx, int mode);
 /* kernel of the EXTENDED query (grad_std requested) for states of up to 448 padded training points: 0 (default) the
- * all-columns kernel (gpis_ext_kernel: k* generated once per query tile, E11^-1 streamed once), 1 the column-tiled kernel
- * (gpis_var_kernel<ext>) that larger states use.  Both meet the parity gates; their last bits differ (summation order). */
+ * warp-specialised all-columns kernel (gpis_extw_kernel: k* generated once per query tile by generator warps, E11^-1 streamed
+ * once by bulk TMA, DMMA warps synchronised by mbarriers), 2 its single-role predecessor (gpis_ext_kernel), 1 the
+ * column-tiled kernel (gpis_var_kernel<ext>) that larger states use.  All meet the parity gates; w = E11^-1 k* is the same
+ * bit for bit, the last bits of the outputs differ (summation order of the epilogue). */
 int cdx_gpis_set_ext_mode(cdx_ctx* ctx, int mode);
 /* launch shape of the tcgen05 INT8 path (same slices, same exact integer products, same summation tree per query):
  *   3 (default) a CTA PAIR issues tcgen05.mma.cta_group::2 (256 rows of L^-1 as the M dimension, 96 queries as N); each CTA
