@@ -786,7 +786,11 @@ template <int KERNEL>
 int dispatch_ext(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
                  cudaStream_t st) {
   const int nbw = (int)(ctx->g.Np / 64);
-  const bool small = (M + 31) / 32 < (int64_t)ctx->sms;
+  // tile size by rounds x cost of a round: a persistent CTA walks ceil(tiles / SMs) tiles; a 16-query tile costs ~0.55 of a
+  // 32-query one (measured: hammer 2,048 queries = one round of 16-query tiles 24.7 us, 16,384 queries = 4 rounds of 32-query
+  // tiles 151 us).  16,384 queries: 7 x 0.55 < 4 x 1.  Results do not depend on the choice (bit-identical per query).
+  const int64_t r32 = ((M + 31) / 32 + ctx->sms - 1) / ctx->sms, r16 = ((M + 15) / 16 + ctx->sms - 1) / ctx->sms;
+  const bool small = (double)r16 * 0.55 < (double)r32;
   if (ctx->g.ext_mode == 0 && ctx->g.Pslab) {      // warp-specialised kernel (bulk-TMA slab stream)
 #define CDX_EXTW(NB) case NB: return small ? launch_extw<KERNEL, NB, 16>(ctx, X, M, mean, gmean, stdv, gstd, st) \
                                            : launch_extw<KERNEL, NB, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
@@ -795,7 +799,8 @@ int dispatch_ext(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double*
     }
 #undef CDX_EXTW
   }
-#define CDX_EXT(NB) case NB: return small ? launch_ext<KERNEL, NB, 16>(ctx, X, M, mean, gmean, stdv, gstd, st) \
+  const bool small_single = (M + 31) / 32 < (int64_t)ctx->sms;     // the single-role kernel's 16-query tiles only pay below one round
+#define CDX_EXT(NB) case NB: return small_single ? launch_ext<KERNEL, NB, 16>(ctx, X, M, mean, gmean, stdv, gstd, st) \
                                           : launch_ext<KERNEL, NB, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
   switch (nbw) {
     CDX_EXT(1); CDX_EXT(2); CDX_EXT(3); CDX_EXT(4); CDX_EXT(5); CDX_EXT(6); CDX_EXT(7);
