@@ -142,8 +142,9 @@ def hand_urdf(hand):
     return {"leap": LEAP_URDF, "allegro": ALLEGRO_URDF}[hand]
 
 
-def load_gpis(state_name, bias=1.0):
-    """Reference GPIS object with the state assigned as gpis.py:162-168 does, minus `.cuda()`."""
+def load_gpis(state_name, bias=1.0, device=None):
+    """Reference GPIS object with the state assigned as gpis.py:162-168 does; `.cuda()` only when a device is given (the
+    reference-on-GPU parity run of scripts/scale_parity.py --ref-gpu, where CUDA is visible and nothing is patched to the host)."""
     install()
     from gpis import GPIS
     g = GPIS(0.08, bias)
@@ -153,6 +154,8 @@ def load_gpis(state_name, bias=1.0):
     g.y1 = torch.from_numpy(d["y1"])
     g.E11 = torch.from_numpy(d["E11"])
     g.bias = torch.from_numpy(d["bias"]).double()
+    if device is not None:
+        g.R, g.X1, g.y1, g.E11, g.bias = (t.to(device) for t in (g.R, g.X1, g.y1, g.E11, g.bias))
     return g
 
 
@@ -203,7 +206,7 @@ def pinned_kabsch_noise(seed, num_envs_offset=0, num_copies=3):
         E = t.shape[0]
         out = kabsch_noise(seed, counter["it"], E, num_envs_offset, num_copies)
         counter["it"] += 1
-        return out.to(t.dtype)
+        return out.to(device=t.device, dtype=t.dtype)
 
     torch.rand_like = fake
     try:
