@@ -786,11 +786,13 @@ template <int KERNEL>
 int dispatch_ext(cdx_ctx* ctx, const double* X, int64_t M, double* mean, double* gmean, double* stdv, double* gstd,
                  cudaStream_t st) {
   const int nbw = (int)(ctx->g.Np / 64);
-  // tile size by rounds x cost of a round: a persistent CTA walks ceil(tiles / SMs) tiles; a 16-query tile costs ~0.55 of a
-  // 32-query one (measured: hammer 2,048 queries = one round of 16-query tiles 24.7 us, 16,384 queries = 4 rounds of 32-query
-  // tiles 151 us).  16,384 queries: 7 x 0.55 < 4 x 1.  Results do not depend on the choice (bit-identical per query).
+  // tile size by rounds x cost of a round: a persistent CTA walks ceil(tiles / SMs) tiles, and a 16-query tile costs ~0.6 of a
+  // 32-query one inside the pregrasp iteration (it streams E11^-1 twice per 32 queries; alone it is cheaper - hammer, 16,384
+  // queries: 140 us in 7 rounds of 16 against 151 us in 4 rounds of 32 - but beside the other candidate group's kernels the
+  // 8,192-candidate iteration measured 0.397 ms with 16-query tiles and 0.384 ms with 32).  So 16-query tiles only where they
+  // save rounds outright: batches below one round of 32-query tiles.  Results do not depend on the choice (bit-identical).
   const int64_t r32 = ((M + 31) / 32 + ctx->sms - 1) / ctx->sms, r16 = ((M + 15) / 16 + ctx->sms - 1) / ctx->sms;
-  const bool small = (double)r16 * 0.55 < (double)r32;
+  const bool small = (double)r16 * 0.6 < (double)r32;
   if (ctx->g.ext_mode == 0 && ctx->g.Pslab) {      // warp-specialised kernel (bulk-TMA slab stream)
 #define CDX_EXTW(NB) case NB: return small ? launch_extw<KERNEL, NB, 16>(ctx, X, M, mean, gmean, stdv, gstd, st) \
                                            : launch_extw<KERNEL, NB, 32>(ctx, X, M, mean, gmean, stdv, gstd, st)
