@@ -230,3 +230,29 @@ def test_extended_query_kernels_agree_and_are_batch_invariant(name, golden_dir):
         for a, b_ in zip(full, part):
             assert torch.equal(a[1001:1001 + 333], b_)
     g.set_ext_mode(0)
+
+
+def test_refit_across_state_sizes_keeps_the_extended_query_consistent():
+    """one context refitted 150 -> 700 -> 330 -> 430 training points: the slab-ordered copy of E11^-1 that the warp-specialised
+    extended kernel streams (states of <= 448 padded points) is rebuilt with every fit, dropped / re-created as the state
+    crosses 448, and the kernel (mode 0) keeps agreeing with the column-tiled one (mode 1) and with the oracle."""
+    from compliancedex_b200 import GPIS
+    from oracle.gpis_oracle import GPISOracle, synthetic_training_set
+    g = GPIS(0.08, 1.0)
+    gen = torch.Generator().manual_seed(11)
+    for N in (150, 700, 330, 430):
+        X1, y1, noise = synthetic_training_set(N, seed=N)
+        g.fit(X1.cuda(), y1.cuda(), noise.cuda())
+        X = ((torch.rand(777, 3, generator=gen, dtype=torch.float64) * 2 - 1) * 0.1).cuda()
+        outs = {}
+        for mode in (0, 1):
+            g.set_ext_mode(mode)
+            outs[mode] = g.pred_with_grads(X)
+        g.set_ext_mode(0)
+        for a, b in zip(outs[0], outs[1]):
+            assert (a - b).abs().max() <= 1e-9 * max(1.0, float(b.abs().max())), N
+        o = GPISOracle(0.08, 1.0).fit(X1, y1, noise)
+        m, sd = o.pred_diag(X.cpu()[:64])
+        prior = float(o.R) ** 3
+        assert (outs[0][0][:64].cpu() - m.reshape(-1)).abs().max() <= 1e-5 * max(1.0, float(m.abs().max())), N
+        assert (outs[0][1][:64].cpu() ** 2 - sd.reshape(-1) ** 2).abs().max() <= 1e-6 * prior, N
