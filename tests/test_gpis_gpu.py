@@ -256,3 +256,28 @@ def test_refit_across_state_sizes_keeps_the_extended_query_consistent():
         prior = float(o.R) ** 3
         assert (outs[0][0][:64].cpu() - m.reshape(-1)).abs().max() <= 1e-5 * max(1.0, float(m.abs().max())), N
         assert (outs[0][1][:64].cpu() ** 2 - sd.reshape(-1) ** 2).abs().max() <= 1e-6 * prior, N
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("N", [3, 16, 17, 64, 65, 447, 448])
+def test_extended_query_tiny_and_boundary_states(N):
+    """the warp-specialised extended kernel at the corners of its shape space: states of a few points (one k chunk, one column
+    block), exactly 64 / 448 padded points, 449 -> the column-tiled kernel; batches of 1, one tile +- 1, more tiles than SMs.
+    Mode 0 against mode 1 (same w bit for bit, outputs to 1e-9) and finite everywhere."""
+    from compliancedex_b200 import GPIS
+    from oracle.gpis_oracle import synthetic_training_set
+    X1, y1, noise = synthetic_training_set(max(N, 64), seed=100 + N)
+    X1, y1, noise = X1[:N], y1[:N], noise[:N]
+    g = GPIS(0.08, 1.0)
+    g.fit(X1.cuda(), y1.cuda(), noise.cuda())
+    gen = torch.Generator().manual_seed(N)
+    for M in (1, 15, 16, 17, 33, 148 * 32 + 1):
+        X = ((torch.rand(M, 3, generator=gen, dtype=torch.float64) * 2 - 1) * 0.1).cuda()
+        outs = {}
+        for mode in (0, 1):
+            g.set_ext_mode(mode)
+            outs[mode] = g.pred_with_grads(X)
+        g.set_ext_mode(0)
+        for a, b in zip(outs[0], outs[1]):
+            assert torch.isfinite(a).all()
+            assert (a - b).abs().max() <= 1e-9 * max(1.0, float(b.abs().max())), (N, M)
