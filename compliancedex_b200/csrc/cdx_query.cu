@@ -505,30 +505,47 @@ gpis_extw_kernel(const double* __restrict__ Xq, int64_t M, const double* __restr
         xq[i] = ok ? Xq[q * 3] : 0.0; yq[i] = ok ? Xq[q * 3 + 1] : 0.0; zq[i] = ok ? Xq[q * 3 + 2] : 0.0;
         if (kslot < 3) sxq[par * TQ * 3 + (qb + 8 * i) * 3 + kslot] = kslot == 0 ? xq[i] : (kslot == 1 ? yq[i] : zq[i]);
       }
-      for (int c = 0; c < nch; c++, gcs++) {
-        const int slot = (int)(gcs % D);
-        mbar_wait(empty + slot, (unsigned)(((gcs / D) & 1) ^ 1));
+      // two chunks per pass: 2 QPG independent evaluation chains in flight per thread - the chain (distance, conversion,
+      // rsqrt seed, two Newton steps, cubic) is latency-bound, and the generators pace the kernel whenever they fall behind
+      for (int c = 0; c < nch; c += 2, gcs += 2) {
+        const bool two = c + 1 < nch;
+        const int slot0 = (int)(gcs % D), slot1 = (int)((gcs + 1) % D);
+        mbar_wait(empty + slot0, (unsigned)(((gcs / D) & 1) ^ 1));
+        if (two) mbar_wait(empty + slot1, (unsigned)((((gcs + 1) / D) & 1) ^ 1));
         if (gt == 0) {
-          mbar_expect_tx_only(full + slot, SLAB);
-          const char* src = reinterpret_cast<const char*>(Pslab) + (size_t)c * SLAB;
-          char* dst = reinterpret_cast<char*>(Bs) + (size_t)slot * SLAB;
-          for (unsigned off = 0; off < SLAB; off += 16384u) tma_bulk_g2s(dst + off, src + off, min(16384u, SLAB - off), full + slot);
+          for (int h = 0; h < (two ? 2 : 1); h++) {
+            const int slot = h ? slot1 : slot0;
+            mbar_expect_tx_only(full + slot, SLAB);
+            const char* src = reinterpret_cast<const char*>(Pslab) + (size_t)(c + h) * SLAB;
+            char* dst = reinterpret_cast<char*>(Bs) + (size_t)slot * SLAB;
+            for (unsigned off = 0; off < SLAB; off += 16384u) tma_bulk_g2s(dst + off, src + off, min(16384u, SLAB - off), full + slot);
+          }
         }
-        const int j = c * TK + kslot;
-        const double2 p0 = Xa2[2 * j], p1 = Xa2[2 * j + 1];
-        double* arow = As + (size_t)slot * TQ * XW_LA + kslot;
-        double sq[QPG], kv[QPG];
+        const int j0 = c * TK + kslot, j1 = two ? j0 + TK : j0;
+        const double2 p0 = Xa2[2 * j0], p1 = Xa2[2 * j0 + 1], r0 = Xa2[2 * j1], r1 = Xa2[2 * j1 + 1];
+        double sq[2 * QPG], kv[2 * QPG];
 #pragma unroll
         for (int i = 0; i < QPG; i++) {
           const double dx = xq[i] - p0.x, dy = yq[i] - p0.y, dz = zq[i] - p1.x;
           sq[i] = fma(dx, dx, fma(dy, dy, dz * dz));
+          const double ex = xq[i] - r0.x, ey = yq[i] - r0.y, ez = zq[i] - r1.x;
+          sq[QPG + i] = fma(ex, ex, fma(ey, ey, ez * ez));
         }
-        cdx_kernel_k_batch<KERNEL, QPG>(sq, kp, kv);
+        cdx_kernel_k_batch<KERNEL, 2 * QPG>(sq, kp, kv);
+        double* arow0 = As + (size_t)slot0 * TQ * XW_LA + kslot;
 #pragma unroll
-        for (int i = 0; i < QPG; i++) arow[(qb + 8 * i) * XW_LA] = j >= N ? 0.0 : kv[i];
+        for (int i = 0; i < QPG; i++) arow0[(qb + 8 * i) * XW_LA] = j0 >= N ? 0.0 : kv[i];
         __syncwarp();
-        if (lane == 0) mbar_arrive(full + slot);
+        if (lane == 0) mbar_arrive(full + slot0);
+        if (two) {
+          double* arow1 = As + (size_t)slot1 * TQ * XW_LA + kslot;
+#pragma unroll
+          for (int i = 0; i < QPG; i++) arow1[(qb + 8 * i) * XW_LA] = j1 >= N ? 0.0 : kv[QPG + i];
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full + slot1);
+        }
       }
+      if (nch & 1) gcs--;        // the last pass of an odd tile produced one chunk
     }
     return;
   }
