@@ -38,7 +38,10 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
 
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int fr = lane >> 2, fk = lane & 3;
-  const int wm = warp >> 2, wn = warp & 3;
+  // row group wm (32 query rows) / column group wn (TN/4 columns) of this warp's accumulators.  The row group is the fast index:
+  // a scheduler (warp % 4) then holds all four column groups, whose work differs on a diagonal tile of the unit query (below)
+  constexpr int RG = TQ / 32;
+  const int wm = warp % RG, wn = warp / RG;
   const int64_t q0 = (int64_t)blockIdx.x * TQ;
 
   constexpr int NTHR = TQ * 4;
@@ -126,6 +129,9 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
       }
       const double* a_s = As + (c % NA) * TQ * LDS + (wm * 32 + fr) * LDS + fk;
       const double* b_s = Bs + (c % NBq) * TN * LDS + (wn * WN + fr) * LDS + fk;
+      // unit query, diagonal tile: U is lower triangular, so a chunk of training points past this warp's last column meets
+      // only exact zeros of U - the warp skips its DMMAs (the accumulators would not change)
+      if (!EXT && c * TK >= n0 + (wn + 1) * WN) continue;
 #pragma unroll
       for (int ks = 0; ks < TK; ks += 4) {
         double a[4], b[NBW];

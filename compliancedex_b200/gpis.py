@@ -247,16 +247,27 @@ class GPIS:
     def get_visualization_data(self, lb, ub, steps=100):
         """gpis.py:113-125: the grid driver; one fused query over all steps^3 points instead of `steps` slabs."""
         dev = self.X1.device
-        grid = torch.stack(torch.meshgrid(torch.linspace(lb[0], ub[0], steps), torch.linspace(lb[1], ub[1], steps),
-                                          torch.linspace(lb[2], ub[2], steps), indexing="xy"), dim=3).double().to(dev)
-        X = grid.reshape(-1, 3).contiguous()
-        mean = torch.empty(X.shape[0], dtype=torch.float64, device=dev)
+        # the three float32 axis vectors come from the host's linspace (the reference's values bit for bit); only they
+        # cross the bus (3*steps floats), the steps^3 x 3 grid is expanded on the device
+        axes = torch.stack([torch.linspace(lb[a], ub[a], steps) for a in range(3)]).to(dev)
+        X = torch.stack(torch.meshgrid(axes[0], axes[1], axes[2], indexing="xy"), dim=3).double().reshape(-1, 3)
+        M = X.shape[0]
+        mean = torch.empty(M, dtype=torch.float64, device=dev)
         std = torch.empty_like(mean)
-        g = torch.empty(X.shape[0], 3, dtype=torch.float64, device=dev)
+        g = torch.empty(M, 3, dtype=torch.float64, device=dev)
         self._query(X, mean, g, std, None)
-        n = g / (torch.norm(g, dim=1, keepdim=True) + 1e-8)
-        return (mean.view(steps, steps, steps).float().cpu().numpy(), std.view(steps, steps, steps).float().cpu().numpy(),
-                n.view(steps, steps, steps, 3).float().cpu().numpy(), np.asarray(lb), np.asarray(ub))
+        # float32 results packed as planes [mean | std | normals] -> ONE device-to-host copy into pinned memory; the
+        # returned arrays are contiguous views of that buffer (it lives as long as any of them does)
+        packed = torch.empty(5 * M, dtype=torch.float32, device=dev)
+        packed[:M].copy_(mean)
+        packed[M:2 * M].copy_(std)
+        packed[2 * M:].view(M, 3).copy_(g / (torch.norm(g, dim=1, keepdim=True) + 1e-8))
+        host = torch.empty(5 * M, dtype=torch.float32, pin_memory=True)
+        host.copy_(packed, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        out = host.numpy()
+        return (out[:M].reshape(steps, steps, steps), out[M:2 * M].reshape(steps, steps, steps),
+                out[2 * M:].reshape(steps, steps, steps, 3), np.asarray(lb), np.asarray(ub))
 
     def topcd(self, test_mean, test_normal, lb, ub, steps=100):
         """gpis.py:127-150: surface point cloud of a mean grid - voxels with mean < 0 that have a 6-neighbour with
