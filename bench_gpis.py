@@ -205,7 +205,7 @@ def run_gpis_c1(args, rank, world, local):
             "e2e": {"value": M / (ms_e2e * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": int(3 * steps * 4),
                     "d2h_bytes_per_step": int(M * 5 * 4)},
             "gpu_launches": int(launches), "clocks": clocks,
-            "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,64,unit,128> (FP64 DMMA)", "achieved": achieved,
+            "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,128,unit,128> (FP64 DMMA)", "achieved": achieved,
                          "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                          "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench",
                          "flop_per_query": flop, "queries_per_launch": M, "kernel_ms": ms_step, "traffic": None}}

@@ -132,6 +132,7 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
       // unit query, diagonal tile: U is lower triangular, so a chunk of training points past this warp's last column meets
       // only exact zeros of U - the warp skips its DMMAs (the accumulators would not change)
       if (!EXT && c * TK >= n0 + (wn + 1) * WN) continue;
+      if (n0 + wn * WN >= Np) continue;        // partial last tile: this warp's columns lie past the matrix (zero-filled rows)
 #pragma unroll
       for (int ks = 0; ks < TK; ks += 4) {
         double a[4], b[NBW];
@@ -864,10 +865,17 @@ int query_dispatch(cdx_ctx* ctx, const double* X, int64_t M, double* mean, doubl
       if ((mean || gmean) && !mean_done) return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
       return CDX_OK;
     }
-    if (small_batch) return big ? launch_var<KERNEL, 128, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st)
-                                : launch_var<KERNEL, 64, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st);
-    return big ? launch_var<KERNEL, 128, false, 128>(ctx, X, M, mean, gmean, stdv, nullptr, st)
-               : launch_var<KERNEL, 64, false, 128>(ctx, X, M, mean, gmean, stdv, nullptr, st);
+    // unit query: 128-column tiles whenever they divide the padded size.  Tile nt regenerates the k* chunks 0 .. n0 + TN, so
+    // halving the tile count takes ~40 % off the FP64 generation that shares the pipe with the DMMAs, and the per-warp skips
+    // of a diagonal tile keep the tensor work at that of 64-column tiles (262,144 queries: banana N = 361 2.04 -> 1.80 ms,
+    // mug N = 196 0.92 -> 0.81 ms; 4,608 queries on mug 42 -> 29 us).  With a partial last tile (Np = 320, 448) large batches
+    // gain 4-6 % as well but the clustered small-batch launch loses 10-18 % (fewer, longer CTAs: 1.5 waves), and the tile must
+    // depend on the state alone - so those states keep 64.
+    const bool ubig = g.Np % 128 == 0;
+    if (small_batch) return ubig ? launch_var<KERNEL, 128, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st)
+                                 : launch_var<KERNEL, 64, false, 32>(ctx, X, M, mean, gmean, stdv, nullptr, st);
+    return ubig ? launch_var<KERNEL, 128, false, 128>(ctx, X, M, mean, gmean, stdv, nullptr, st)
+                : launch_var<KERNEL, 64, false, 128>(ctx, X, M, mean, gmean, stdv, nullptr, st);
   }
   return launch_mean<KERNEL>(ctx, g.Xa, X, M, g.bias, mean, gmean, st);
 }
