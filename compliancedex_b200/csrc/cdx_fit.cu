@@ -17,12 +17,14 @@ extern "C" int cdx_version(void) { return 100; }
 
 namespace {
 
-__global__ void pairmax_kernel(const double* __restrict__ X, int N, unsigned long long* out) {
+__global__ void pairmax_kernel(const double* __restrict__ X, int N, int jlen, unsigned long long* out) {
+  // thread = point i, blockIdx.y = a range of jlen partners (the maximum does not depend on the order: same R bit for bit)
   int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j0 = blockIdx.y * jlen, j1 = min(N, j0 + jlen);
   double best = 0.0;
   if (i < N) {
     double x = X[3 * i], y = X[3 * i + 1], z = X[3 * i + 2];
-    for (int j = 0; j < N; j++) {
+    for (int j = j0; j < j1; j++) {
       double dx = x - X[3 * j], dy = y - X[3 * j + 1], dz = z - X[3 * j + 2];
       best = fmax(best, fma(dx, dx, fma(dy, dy, dz * dz)));
     }
@@ -160,14 +162,32 @@ __global__ void trmv_lower_kernel(const double* __restrict__ U, int Np, const do
   for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane == 0) out[row] = s;
 }
-// out[j] = sum_{i>=j} U[i][j] v[i]   (one thread per column, coalesced over columns)
-__global__ void trmv_lower_t_kernel(const double* __restrict__ U, int Np, const double* __restrict__ v,
-                                    double* __restrict__ out) {
-  int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= Np) return;
-  double s = 0.0;
-  for (int i = j; i < Np; i++) s = fma(U[(int64_t)i * Np + j], v[i], s);
-  out[j] = s;
+// out[j] = sum_{i>=j} U[i][j] v[i]: a CTA owns 32 columns; thread (r, c) of its 8 x 32 threads walks the rows j0 + r, j0 + r + 8, ...
+// of column j0 + c (256-byte row segments, four independent chains per thread), the 8 x 4 partial sums of a column are added
+// in a fixed order.  (One thread per column walking all rows took 4.4 ms at N = 16,384: 128 CTAs of serial 16 k-row loops.)
+__global__ void __launch_bounds__(256) trmv_lower_t_kernel(const double* __restrict__ U, int Np, const double* __restrict__ v,
+                                                           double* __restrict__ out) {
+  __shared__ double part[8][33];
+  const int c = threadIdx.x & 31, r = threadIdx.x >> 5, j0 = blockIdx.x * 32, j = j0 + c;
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+  if (j < Np) {
+    int i = j0 + r;
+    for (; i + 24 < Np; i += 32) {
+      const double* u = U + (int64_t)i * Np + j;
+      const double u0 = i >= j ? u[0] : 0.0, u1 = i + 8 >= j ? u[(int64_t)8 * Np] : 0.0;
+      const double u2 = i + 16 >= j ? u[(int64_t)16 * Np] : 0.0, u3 = i + 24 >= j ? u[(int64_t)24 * Np] : 0.0;
+      s0 = fma(u0, v[i], s0); s1 = fma(u1, v[i + 8], s1); s2 = fma(u2, v[i + 16], s2); s3 = fma(u3, v[i + 24], s3);
+    }
+    for (; i < Np; i += 8)
+      if (i >= j) s0 = fma(U[(int64_t)i * Np + j], v[i], s0);
+  }
+  part[r][c] = (s0 + s1) + (s2 + s3);
+  __syncthreads();
+  if (r == 0 && j < Np) {
+    double t = part[0][c];
+    for (int k = 1; k < 8; k++) t += part[k][c];
+    out[j] = t;
+  }
 }
 __global__ void pack_xa_kernel(const double* __restrict__ X, const double* __restrict__ alpha, int N, int Np,
                                double* __restrict__ Xa) {
@@ -347,7 +367,7 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   // alpha = U^T (U y1)
   trmv_lower_kernel<<<(Np + 7) / 8, 256, 0, st>>>(g.U, Np, g.y1, g.tmp);
   CDX_CHECK_LAUNCH(ctx);
-  trmv_lower_t_kernel<<<(Np + 127) / 128, 128, 0, st>>>(g.U, Np, g.tmp, g.tmp + Np);
+  trmv_lower_t_kernel<<<(Np + 31) / 32, 256, 0, st>>>(g.U, Np, g.tmp, g.tmp + Np);
   CDX_CHECK_LAUNCH(ctx);
   pack_xa_kernel<<<(Np + 255) / 256, 256, 0, st>>>(X1, g.tmp + Np, N, Np, g.Xa);
   CDX_CHECK_LAUNCH(ctx);
@@ -439,7 +459,8 @@ extern "C" int cdx_gpis_fit(cdx_ctx* ctx, const double* X1, const double* y1, co
   fit_mark(g, 0, st);
   if (kernel != CDX_KERNEL_RBF) {  // gpis.py:35-36
     CDX_CUDA(cudaMemsetAsync(g.dR2, 0, sizeof(double), st));
-    pairmax_kernel<<<((int)N + 127) / 128, 128, 0, st>>>(X1, (int)N, (unsigned long long*)g.dR2);
+    const int jsplit = (int)((N + 511) / 512) < 64 ? (int)((N + 511) / 512) : 64, jlen = ((int)N + jsplit - 1) / jsplit;
+    pairmax_kernel<<<dim3(((int)N + 127) / 128, jsplit), 128, 0, st>>>(X1, (int)N, jlen, (unsigned long long*)g.dR2);
     CDX_CHECK_LAUNCH(ctx);
     double r2 = 0;
     CDX_CUDA(cudaMemcpyAsync(&r2, g.dR2, sizeof(double), cudaMemcpyDeviceToHost, st));
