@@ -2,6 +2,7 @@
    python scripts/ncu_target.py ext  [state] [M]     extended GPIS query (gpis_ext_kernel) on a shipped state
    python scripts/ncu_target.py i8   [waves]         INT8 std kernel (gpis_std_i8x_kernel) at N = 4096, `waves` waves of 74 CTA pairs
    python scripts/ncu_target.py fit  [N]             GPIS fit (dgemm_kernel, potrf_diag_kernel)
+   python scripts/ncu_target.py unit [state] [M]     unit GPIS query {mean, grad mean, std} (gpis_var_kernel<unit>) on a shipped state
    python scripts/ncu_target.py c5   [B] [iters]     pregrasp iterations at the C5 per-GPU shape (Allegro, hammer)"""
 import ctypes
 import sys
@@ -23,6 +24,18 @@ if what == "ext":
     X = ((torch.rand(M, 3, generator=torch.Generator().manual_seed(1), dtype=torch.float64) * 2 - 1) * 0.18).cuda()
     for _ in range(4):
         out = g.pred_with_grads(X)
+    torch.cuda.synchronize()
+elif what == "unit":
+    name = sys.argv[2] if len(sys.argv) > 2 else "banana"
+    M = int(sys.argv[3]) if len(sys.argv) > 3 else 262144
+    g = GPIS(0.08, 1.0)
+    g.load_state_data(state_path(f"{name}_state"))
+    X = ((torch.rand(M, 3, generator=torch.Generator().manual_seed(1), dtype=torch.float64) * 2 - 1) * 0.15).cuda()
+    std = torch.empty(M, dtype=torch.float64, device="cuda")
+    mean = torch.empty(M, dtype=torch.float64, device="cuda")
+    gm = torch.empty(M, 3, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        _lib.check(lib.cdx_gpis_query(g._ctx, X.data_ptr(), M, mean.data_ptr(), gm.data_ptr(), std.data_ptr(), None, st))
     torch.cuda.synchronize()
 elif what == "i8":
     from compliancedex_b200.synthetic import synthetic_queries, synthetic_training_set
