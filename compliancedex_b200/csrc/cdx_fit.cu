@@ -65,10 +65,15 @@ __global__ void unpad_copy_kernel(const double* __restrict__ src, int N, int Np,
   if (j < N) dst[(int64_t)i * N + j] = src[(int64_t)i * Np + j];
 }
 
-// Cholesky of one 64x64 diagonal block in shared memory + its triangular inverse.  This kernel is the head of the serial
-// chain of every 64-column sub-step, so its latency counts in full:
-//   * factorisation: two barriers per column - every thread of column j takes sqrt(a[j][j]) itself (the raw diagonal stays
-//     in place until the end, the root goes to the padding column), so no thread waits for a broadcast;
+// Cholesky of one 64x64 diagonal block + its triangular inverse.  This kernel is the head of the serial chain of every
+// 64-column sub-step, so its latency counts in full (N = 4,096: the whole Cholesky phase is this chain):
+//   * factorisation in REGISTERS: thread (row r = t % 64, column group t / 64) holds the 16 entries a[r][16 cg .. 16 cg + 15];
+//     per column j the owners publish the raw column through a double-buffered 64-entry line of shared memory (ONE barrier per
+//     column), every thread forms 1 / sqrt(a[j][j]) itself (rsqrt + the diagonal by one Newton step: no sqrt / division chain,
+//     no wait for a broadcast) and updates its own entries right of j with broadcast reads; the j loop is unrolled, so all
+//     register subscripts are compile-time.  Entries above the diagonal carry dead values and are zeroed at the write-back.
+//     (The shared-memory version - two barriers, an IEEE sqrt and a division per column, 16 predicated passes over the whole
+//     block per column - took ~50 us of the ~100 us sub-step.)
 //   * inverse: recursive doubling, inv([L11 0; L21 L22]) = [X11 0; -X22 L21 X11, X22], all 256 threads at every level (six
 //     levels, two barriers each) instead of 64 serial forward substitutions; the s x s temporaries T = L21 X11 live in the
 //     mirror-image block of `a`'s upper triangle, which is dead (zeroed before the write-back).
@@ -78,33 +83,51 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A,
   extern __shared__ double potrf_smem[];
   double (*a)[65] = reinterpret_cast<double (*)[65]>(potrf_smem);
   double (*x)[65] = a + 64;
+  __shared__ __align__(16) double colbuf[2][64];
   const int t = threadIdx.x;
-  for (int e = t; e < 4096; e += 256) a[e >> 6][e & 63] = A[(int64_t)(e >> 6) * ld + (e & 63)];
-  __syncthreads();
+  const int r = t & 63, cg = t >> 6;
+  double ar[16];
+  {
+    const double2* src = reinterpret_cast<const double2*>(A + (int64_t)r * ld + cg * 16);   // ld and the block origin are even
+#pragma unroll
+    for (int k = 0; k < 8; k++) { const double2 v = src[k]; ar[2 * k] = v.x; ar[2 * k + 1] = v.y; }
+  }
+#pragma unroll
   for (int j = 0; j < 64; j++) {
-    if (t >= j && t < 64) {
-      const double d = a[j][j];
-      const double r = sqrt(d);
-      if (t == j) {
-        if (!(d > 0.0)) atomicCAS(flag, 0, col0 + j + 1);
-        a[j][64] = r;                              // the padding column holds the roots until the loop is over
-      } else {
-        a[t][j] /= r;
+    const int cgj = j >> 4, jj = j & 15;
+    double* cb = colbuf[j & 1];
+    if (cg == cgj) cb[r] = ar[jj];
+    __syncthreads();          // one barrier per column: the line written for column j + 1 is the one column j - 1 used, and every
+                              // thread has left column j - 1 before any thread passes this barrier
+    const double d = cb[j];
+    const double rinv = rsqrt(d);
+    double root = d * rinv;
+    root = fma(0.5 * rinv, fma(-root, root, d), root);     // sqrt(d) to the last bit or two
+    if (t == cgj * 64 + j && !(d > 0.0)) atomicCAS(flag, 0, col0 + j + 1);
+    const double lr = cb[r] * rinv;
+    if (cg > cgj) {
+#pragma unroll
+      for (int k = 0; k < 16; k += 2) {
+        const double2 c2 = *reinterpret_cast<const double2*>(cb + cg * 16 + k);
+        ar[k] = fma(-lr, c2.x * rinv, ar[k]);
+        ar[k + 1] = fma(-lr, c2.y * rinv, ar[k + 1]);
       }
+    } else if (cg == cgj) {
+#pragma unroll
+      for (int k = 0; k < 16; k++)
+        if (k > jj) ar[k] = fma(-lr, cb[cgj * 16 + k] * rinv, ar[k]);
+      ar[jj] = (r == j) ? root : lr;
     }
-    __syncthreads();
-    // trailing update of the lower triangle right of column j: thread -> column c = j+1+(t&63) strided, rows from c down
-    for (int e = t; e < 4096; e += 256) {
-      int r = e >> 6, c = e & 63;
-      if (c > j && r >= c) a[r][c] = fma(-a[r][j], a[c][j], a[r][c]);
-    }
-    __syncthreads();
   }
+#pragma unroll
+  for (int k = 0; k < 16; k++) a[r][cg * 16 + k] = ar[k];
+  __syncthreads();
+  if (t < 64) colbuf[0][t] = 1.0 / a[t][t];       // (all threads left the last column's line at the barrier above)
+  __syncthreads();
   for (int e = t; e < 4096; e += 256) {
-    int r = e >> 6, c = e & 63;
-    x[r][c] = r == c ? 1.0 / a[r][64] : 0.0;
+    int rr = e >> 6, c = e & 63;
+    x[rr][c] = rr == c ? colbuf[0][rr] : 0.0;
   }
-  if (t < 64) a[t][t] = a[t][64];
   __syncthreads();
   for (int s = 1; s < 64; s *= 2) {
     const int ss = s * s, nout = 32 * s;           // (32 / s) pairs x s x s outputs
