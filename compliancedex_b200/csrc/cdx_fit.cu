@@ -287,11 +287,11 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   const int nb = Np / 64;
   const size_t potrf_smem_bytes = sizeof(double) * 2 * 64 * 65;
   CDX_CUDA(cudaFuncSetAttribute(potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)potrf_smem_bytes));
-  // Right-looking over 256-column outer panels.  Inside a panel the four 64-column sub-steps (64x64 factorisation + inverse,
+  // Right-looking over 256- or 512-column outer panels.  Inside a panel the 64-column sub-steps (64x64 factorisation + inverse,
   // panel solve as a GEMM with the block inverse, update of the panel's own remaining columns) touch only the panel; the
-  // trailing matrix is updated ONCE per panel with K = 256 - a quarter of the read-modify-write traffic of 64-wide steps and
+  // trailing matrix is updated ONCE per panel with K = 256 / 512 - a quarter / an eighth of the read-modify-write traffic of 64-wide steps and
   // four times the work per tile launch (with K = 64 every tile's prologue / epilogue outweighed its four k-chunks: 0.29 of
-  // the DMMA peak).  One panel of look-ahead: the next panel's 256 columns are updated first, so that the next panel's
+  // the DMMA peak).  One panel of look-ahead: the next panel's columns are updated first, so that the next panel's
   // serial sub-steps run while the rest of the trailing update executes.  The serial chain (sub-steps + look-ahead update)
   // runs on the library's own HIGH-PRIORITY stream `hi`, the bulk update on the caller's stream: the chain's small grids
   // must not queue behind the thousands of CTAs of a bulk update, or the overlap is lost (with equal priorities the phase
@@ -306,7 +306,9 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   cudaStream_t hi = g.fit_side;
   CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, st));
   CDX_CUDA(cudaStreamWaitEvent(hi, g.fit_ev_trsm, 0));              // the chain starts after everything queued so far
-  constexpr int PW = 256;
+  // outer panel width: 512 from Np = 12,288 up (K = 512 halves the trailing update's per-tile prologue / epilogue share: Cholesky
+  // phase 68.8 -> 65.8 ms at N = 16,384), 256 below (N = 8,192: 13.2 ms against 13.9 - the longer in-panel chain is exposed there)
+  const int PW = Np >= 12288 ? 512 : 256;
   bool rest_pending = false;
   for (int c0 = 0; c0 < Np; c0 += PW) {
     const int w = Np - c0 < PW ? Np - c0 : PW;                       // panel width (a multiple of 64)

@@ -130,13 +130,13 @@ __global__ void __launch_bounds__(128) dgemm_kernel(int M, int N, int K, double 
 
 // ------------------------------------------------------------------------------------------ 128 x 128 tiles, cp.async ring
 // The large products of the fit (trailing updates of the Cholesky with K = 256, the recursive-doubling levels of L^-1,
-// E11^-1 = U^T U): 128x128x16 CTA tiles, 16 warps (4 x 4, each a 32x32 tile = 4x4 DMMA blocks), operands brought in with
-// 16-byte cp.async through a 4-stage shared-memory ring - a DMMA holds its warp for several cycles, so it takes four warps per
+// E11^-1 = U^T U): 128x128x32 CTA tiles, 16 warps (4 x 4, each a 32x32 tile = 4x4 DMMA blocks), operands brought in with
+// 16-byte cp.async through a 2-stage shared-memory ring (147 KB: a potrf / panel CTA of the chain must fit beside it) - a DMMA holds its warp for several cycles, so it takes four warps per
 // scheduler and loads that never wait on the math to keep the pipe fed (the 64x64 single-buffered kernel above reached
 // 0.40-0.50 of the DMMA peak).  Operand tiles keep the layout they have in memory: k-contiguous sources as [row][20]
 // (conflict-free for the fragment pattern row = T/4, k = T%4), row-contiguous sources (ta / tb) as [k][132].
-constexpr int GM = 128, GN = 128, GK = 16, GST = 4, LDT = 132;
-constexpr int G_TILE = GM * LDS > GK * LDT ? GM * LDS : GK * LDT;   // doubles per operand tile and stage
+constexpr int GM = 128, GN = 128, GK = 32, GST = 2, LDT = 132, LDG = GK + 4;
+constexpr int G_TILE = GM * LDG > GK * LDT ? GM * LDG : GK * LDT;   // doubles per operand tile and stage
 
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(512, 1) dgemm128_kernel(int M, int N, int K, double alpha, const double* __restrict__ A,
@@ -164,13 +164,13 @@ __global__ void __launch_bounds__(512, 1) dgemm128_kernel(int M, int N, int K, d
   // one operand tile of chunk c into ring slot `buf`: 16-byte cp.async, rows outside the matrix are zero-filled
   auto load_tile = [&](const double* __restrict__ P, int64_t ld, bool trans, int r0, int R, double* dst, int k0) {
     if (!trans) {                         // P[rows, K]: 128 rows x 8 segments of 2 doubles
-      for (int p = t; p < GM * 8; p += 512) {
-        const int row = p >> 3, seg = p & 7;
-        double* d = dst + row * LDS + seg * 2;
+      for (int p = t; p < GM * (GK / 2); p += 512) {
+        const int row = p / (GK / 2), seg = p % (GK / 2);
+        double* d = dst + row * LDG + seg * 2;
         if (r0 + row < R && k0 + seg * 2 < kend) cdx_cp_async16(d, P + (int64_t)(r0 + row) * ld + k0 + seg * 2);
         else { d[0] = 0.0; d[1] = 0.0; }
       }
-    } else {                              // P[K, rows]: 16 k x 64 segments of 2 doubles
+    } else {                              // P[K, rows]: GK k x 64 segments of 2 doubles
       for (int p = t; p < GK * 64; p += 512) {
         const int kk = p >> 6, seg = p & 63;
         double* d = dst + kk * LDT + seg * 2;
@@ -207,10 +207,10 @@ __global__ void __launch_bounds__(512, 1) dgemm128_kernel(int M, int N, int K, d
       double a[4], b[4];
 #pragma unroll
       for (int i = 0; i < 4; i++)
-        a[i] = TA ? a_s[(ks + fk) * LDT + wm * 32 + i * 8 + fr] : a_s[(wm * 32 + i * 8 + fr) * LDS + ks + fk];
+        a[i] = TA ? a_s[(ks + fk) * LDT + wm * 32 + i * 8 + fr] : a_s[(wm * 32 + i * 8 + fr) * LDG + ks + fk];
 #pragma unroll
       for (int j = 0; j < 4; j++)
-        b[j] = TB ? b_s[(ks + fk) * LDT + wn * 32 + j * 8 + fr] : b_s[(wn * 32 + j * 8 + fr) * LDS + ks + fk];
+        b[j] = TB ? b_s[(ks + fk) * LDT + wn * 32 + j * 8 + fr] : b_s[(wn * 32 + j * 8 + fr) * LDG + ks + fk];
 #pragma unroll
       for (int i = 0; i < 4; i++)
 #pragma unroll
