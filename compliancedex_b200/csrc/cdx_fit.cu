@@ -65,6 +65,32 @@ __global__ void unpad_copy_kernel(const double* __restrict__ src, int N, int Np,
   if (j < N) dst[(int64_t)i * N + j] = src[(int64_t)i * Np + j];
 }
 
+// One level of the recursive-doubling inverse of a 64x64 lower-triangular block (a = L, x = the inverse so far: the diagonal
+// S x S blocks are done): X21 = -X22 (L21 X11) for the 32 / S block pairs.  S is a compile-time constant and the dot products
+// run over the FULL block width with four independent accumulators - the triangular halves they could skip are exact zeros of
+// x, and a fixed trip count lets the loads pipeline; the run-time version (trip counts j..S, one dependent FMA chain per
+// output, integer divisions for the indices) took 32 k of the kernel's 70 k cycles.
+template <int S>
+__device__ __forceinline__ void potrf_inv_level(double (*a)[65], double (*x)[65], int t) {
+  constexpr int NOUT = 32 * S, SS = S * S;
+  for (int e = t; e < NOUT; e += 256) {          // T = L21 X11 -> a[upper mirror block] (dead storage)
+    const int p = e / SS, i = (e / S) % S, j = e % S, base = 2 * p * S;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < S; k++) acc[k & 3] = fma(a[base + S + i][base + k], x[base + k][base + j], acc[k & 3]);
+    a[base + i][base + S + j] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+  }
+  __syncthreads();
+  for (int e = t; e < NOUT; e += 256) {          // X21 = -X22 T
+    const int p = e / SS, i = (e / S) % S, j = e % S, base = 2 * p * S;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < S; k++) acc[k & 3] = fma(x[base + S + i][base + S + k], a[base + k][base + S + j], acc[k & 3]);
+    x[base + S + i][base + j] = -((acc[0] + acc[1]) + (acc[2] + acc[3]));
+  }
+  __syncthreads();
+}
+
 // Cholesky of one 64x64 diagonal block + its triangular inverse.  This kernel is the head of the serial chain of every
 // 64-column sub-step, so its latency counts in full (N = 4,096: the whole Cholesky phase is this chain):
 //   * factorisation in REGISTERS: thread (row r = t % 64, column group t / 64) holds the 16 entries a[r][16 cg .. 16 cg + 15];
@@ -75,8 +101,8 @@ __global__ void unpad_copy_kernel(const double* __restrict__ src, int N, int Np,
 //     (The shared-memory version - two barriers, an IEEE sqrt and a division per column, 16 predicated passes over the whole
 //     block per column - took ~50 us of the ~100 us sub-step.)
 //   * inverse: recursive doubling, inv([L11 0; L21 L22]) = [X11 0; -X22 L21 X11, X22], all 256 threads at every level (six
-//     levels, two barriers each) instead of 64 serial forward substitutions; the s x s temporaries T = L21 X11 live in the
-//     mirror-image block of `a`'s upper triangle, which is dead (zeroed before the write-back).
+//     levels, two barriers each, potrf_inv_level above) instead of 64 serial forward substitutions; the s x s temporaries
+//     T = L21 X11 live in the mirror-image block of `a`'s upper triangle, which is dead (zeroed before the write-back).
 // Shared memory stays at 2 x 64 x 65 doubles: one of these CTAs must fit on an SM next to a 160 KB dgemm128 CTA.
 __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A, int64_t ld, double* __restrict__ Dinv,
                                                          double* __restrict__ Udiag, int* flag, int col0) {
@@ -129,23 +155,8 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A,
     x[rr][c] = rr == c ? colbuf[0][rr] : 0.0;
   }
   __syncthreads();
-  for (int s = 1; s < 64; s *= 2) {
-    const int ss = s * s, nout = 32 * s;           // (32 / s) pairs x s x s outputs
-    for (int e = t; e < nout; e += 256) {          // T = L21 X11 (X11 lower triangular) -> a[upper mirror block]
-      const int p = e / ss, i = (e / s) % s, j = e % s, base = 2 * p * s;
-      double acc = 0.0;
-      for (int k = j; k < s; k++) acc = fma(a[base + s + i][base + k], x[base + k][base + j], acc);
-      a[base + i][base + s + j] = acc;
-    }
-    __syncthreads();
-    for (int e = t; e < nout; e += 256) {          // X21 = -X22 T (X22 lower triangular)
-      const int p = e / ss, i = (e / s) % s, j = e % s, base = 2 * p * s;
-      double acc = 0.0;
-      for (int k = 0; k <= i; k++) acc = fma(x[base + s + i][base + s + k], a[base + k][base + s + j], acc);
-      x[base + s + i][base + j] = -acc;
-    }
-    __syncthreads();
-  }
+  potrf_inv_level<1>(a, x, t);  potrf_inv_level<2>(a, x, t);  potrf_inv_level<4>(a, x, t);
+  potrf_inv_level<8>(a, x, t);  potrf_inv_level<16>(a, x, t); potrf_inv_level<32>(a, x, t);
   for (int e = t; e < 4096; e += 256) {
     int r = e >> 6, c = e & 63;
     const double v = c > r ? 0.0 : a[r][c];
