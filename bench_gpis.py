@@ -145,7 +145,7 @@ def run_gpis_c3(args, rank, world, local):
                    "l2_policy": "inputs+outputs (%.0f MB per rank) and the sliced L^-1 operand (%.0f MB) exceed L2; no flush needed"
                                 % (M * 64 / 1e6, (5 * Np * Np if i8 else 8 * N * N) / 1e6),
                    "fit_seconds": fit_s},
-        "e2e": {"value": total_q / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(3 * steps * 4), "d2h_bytes_per_step": int(M * 40),
+        "e2e": {"value": total_q / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(M * 24), "d2h_bytes_per_step": int(M * 40),
                 "value_including_one_fit": total_q / (e2e_s + fit_s)},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
     }
