@@ -126,3 +126,35 @@ def test_completion_assembly_matches_reference_script(tag, golden_dir):
     X1b, _, _ = assemble_training_set(g[f"{tag}_observed"], g[f"{tag}_completed"], int(num_obs), int(num_gen), float(obs_noise),
                                       float(gen_noise), int(num_internals), float(boundary), generator=gen)
     assert np.array_equal(X1b.numpy(), g[f"{tag}_X1"])
+
+
+def test_driver_scripts_reference_only_defined_globals():
+    """bench.py / __graft_entry__.py run unattended on the GPU box: a name that no scope defines is a NameError there, minutes into the
+    run.  Static check over every function scope: each implicitly-global name must be bound at module level or be a builtin."""
+    import builtins
+    import glob
+    import os
+    import symtable
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    files = (glob.glob(os.path.join(root, "bench*.py")) + [os.path.join(root, "__graft_entry__.py")]
+             + glob.glob(os.path.join(root, "compliancedex_b200", "*.py")) + glob.glob(os.path.join(root, "scripts", "*.py"))
+             + glob.glob(os.path.join(root, "oracle", "*.py")))
+    assert len(files) > 20
+    bad = []
+    for path in files:
+        src = open(path).read()
+        top = symtable.symtable(src, path, "exec")
+        module_names = {s.get_name() for s in top.get_symbols() if s.is_assigned() or s.is_imported() or s.is_namespace()}
+        star_import = "import *" in src
+
+        def walk(scope):
+            for child in scope.get_children():
+                for s in child.get_symbols():
+                    n = s.get_name()
+                    if s.is_referenced() and s.is_global() and not s.is_assigned() and not s.is_imported():
+                        if n not in module_names and not hasattr(builtins, n) and not star_import and n not in ("__file__", "__name__", "__doc__"):
+                            bad.append((os.path.relpath(path, root), child.get_name(), n))
+                walk(child)
+        walk(top)
+    assert not bad, bad
