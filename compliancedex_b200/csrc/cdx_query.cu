@@ -132,7 +132,7 @@ gpis_var_kernel(const double* __restrict__ Xq, int64_t M, const double* __restri
       // unit query, diagonal tile: U is lower triangular, so a chunk of training points past this warp's last column meets
       // only exact zeros of U - the warp skips its DMMAs (the accumulators would not change)
       if (!EXT && c * TK >= n0 + (wn + 1) * WN) continue;
-      if (n0 + wn * WN >= Np) continue;        // partial last tile: this warp's columns lie past the matrix (zero-filled rows)
+      if (n0 + wn * WN >= N) continue;         // this warp's columns are all padding (identity rows of the factor meet k* = 0: exact zeros)
 #pragma unroll
       for (int ks = 0; ks < TK; ks += 4) {
         double a[4], b[NBW];
