@@ -208,7 +208,8 @@ def run_gpis_c1(args, rank, world, local):
             "roofline": {"bound": "tensor", "kernel": "gpis_var_kernel<TPS,128,unit,128> (FP64 DMMA)", "achieved": achieved,
                          "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                          "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench",
-                         "flop_per_query": flop, "queries_per_launch": M, "kernel_ms": ms_step, "traffic": None}}
+                         "flop_per_query": flop, "queries_per_launch": M, "kernel_ms": ms_step,
+                         "traffic": ncu_traffic("r02_ncu_unit_c1_summary.json", "gpis_var_kernel")}}
 
 
 # ------------------------------------------------------------------------------------------ fit_c4 (GPU)
