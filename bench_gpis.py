@@ -271,7 +271,8 @@ def run_fit_c4(args, rank, world, local):
                          "peak_source": "FP64 DMMA m8n8k4 rate measured in this run by csrc/cdx_pipebench",
                          "flop_per_phase": third, "phase_ms": phase_ms, "phase_tflops": phase_tf,
                          "phase_frac_of_dmma_peak": {k: (v / peak if (v and peak) else None) for k, v in phase_tf.items()},
-                         "whole_fit_tflops_over_N3": 3 * third / (ms_step * 1e-3) / 1e12, "traffic": None}}
+                         "whole_fit_tflops_over_N3": 3 * third / (ms_step * 1e-3) / 1e12,
+                         "traffic": ncu_traffic("r02_ncu_fit16k_summary.json", "trailing update")}}
 
 
 # ------------------------------------------------------------------------------------------ CPU legs (reference arm)
