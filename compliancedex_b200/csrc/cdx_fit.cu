@@ -317,12 +317,13 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   cudaStream_t hi = g.fit_side;
   CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, st));
   CDX_CUDA(cudaStreamWaitEvent(hi, g.fit_ev_trsm, 0));              // the chain starts after everything queued so far
-  // outer panel width: 512 from Np = 12,288 up (K = 512 halves the trailing update's per-tile prologue / epilogue share: Cholesky
-  // phase 68.8 -> 65.8 ms at N = 16,384), 256 below (N = 8,192: 13.2 ms against 13.9 - the longer in-panel chain is exposed there)
-  const int PW = Np >= 12288 ? 512 : 256;
+  // outer panel width: 512 while more than 8,192 columns are left (K = 512 halves the trailing update's per-tile prologue /
+  // epilogue share: Cholesky phase 68.8 -> 65.8 ms at N = 16,384), 256 below (N = 8,192: 13.2 ms against 13.9 - the longer
+  // in-panel chain is exposed there, and the same holds for the tail of a larger matrix)
+  auto panel_width = [&](int c) { const int left = Np - c, pw = left > 8192 ? 512 : 256; return left < pw ? left : pw; };
   bool rest_pending = false;
-  for (int c0 = 0; c0 < Np; c0 += PW) {
-    const int w = Np - c0 < PW ? Np - c0 : PW;                       // panel width (a multiple of 64)
+  for (int c0 = 0, w = 0; c0 < Np; c0 += w) {
+    w = panel_width(c0);                                             // a multiple of 64
     for (int j0 = c0; j0 < c0 + w; j0 += 64) {
       double* Ajj = g.L + (int64_t)j0 * (ld + 1);
       potrf_diag_kernel<<<1, 256, potrf_smem_bytes, hi>>>(Ajj, ld, g.Dinv + (int64_t)(j0 / 64) * 4096, g.U + (int64_t)j0 * (ld + 1), g.flag, j0);
@@ -347,7 +348,7 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
     CDX_CUDA(cudaEventRecord(g.fit_ev_trsm, hi));                    // this panel's columns are final
     if (rest_pending) CDX_CUDA(cudaStreamWaitEvent(hi, g.fit_ev_rest, 0));   // the previous bulk update touched the next panel's columns
     // next panel's columns first (chain stream), K = w
-    const int wn = m2 < PW ? m2 : PW;
+    const int wn = panel_width(c0 + w);                              // the next panel's width
     int rc = cdx_dgemm(ctx, false, false, m2, wn, w, -1.0, L21, ld, L21, ld, 1.0, A22, ld, false, 0, 1, 0, 0, 0, hi);
     if (rc) return rc;
     // the rest (rows / columns >= c0 + w + 256, lower tiles only) on the caller's stream
