@@ -288,6 +288,7 @@ static inline void fit_mark(cdx_gpis_state& g, int i, cudaStream_t st) {
 // factorise g.E11 (padded) -> L, U, P, alpha, Xa.  X1 is [N,3] device.
 int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
+  ctx->gemm_deep = false;
   fit_mark(g, 1, st);
   const int Np = (int)g.Np, N = (int)g.N;
   const int64_t ld = Np;
@@ -368,6 +369,7 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   zero_upper_kernel<<<g2, 256, 0, st>>>(g.L, Np);
   CDX_CHECK_LAUNCH(ctx);
   fit_mark(g, 2, st);
+  ctx->gemm_deep = true;      // inverse phases: no chain CTA to keep room for - the 3-stage mbarrier-pipelined GEMM (cdx_gemm.cu)
   // U = L^-1 by doubling: inv([L11 0; L21 L22]) = [U11 0; -U22 L21 U11, U22]; P is scratch for T = L21 U11
   for (int s = 64; s < Np; s *= 2) {
     int npairs = (Np + 2 * s - 1) / (2 * s);
@@ -400,6 +402,7 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
     pack_slab_kernel<<<g2, 256, 0, st>>>(g.P, Np, g.Pslab);
     CDX_CHECK_LAUNCH(ctx);
   }
+  ctx->gemm_deep = false;
   fit_mark(g, 4, st);
   // alpha = U^T (U y1)
   trmv_lower_kernel<<<(Np + 7) / 8, 256, 0, st>>>(g.U, Np, g.y1, g.tmp);

@@ -232,6 +232,139 @@ __global__ void __launch_bounds__(512, 1) dgemm128_kernel(int M, int N, int K, d
     }
 }
 
+
+// ------------------------------------------------------------------------------------------ 128 x 128 tiles, mbarrier pipeline
+// The same tile and fragment layout as dgemm128_kernel, but three ring stages and NO CTA-wide barrier in the k loop: every
+// thread's cp.async copies of a chunk arrive on the stage's `full` mbarrier (cp.async.mbarrier.arrive.noinc; rows outside the
+// matrix are zero-filled by cp.async with a source size of 0, so every write of a stage is tracked), a warp releases a stage
+// on its `empty` mbarrier when its DMMAs have consumed the last fragments, and a chunk is prefetched ONE iteration ahead into the
+// stage that chunk c - 2 used - so a warp may run a whole chunk ahead of the slowest one instead of meeting it at every chunk
+// (ncu of dgemm128_kernel: 8 % of the stall samples on the barrier, DMMA sub-pipe 83 %).  221 KB of shared memory: used for
+// the inverse phases of the fit, where no chain CTA needs room beside a GEMM CTA.
+constexpr int GST3 = 3;
+
+__device__ __forceinline__ void g_mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void g_mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void g_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void g_cp_async_arrive(uint64_t* bar) {   // arrives when this thread's earlier cp.async copies have landed
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void g_cp_async16_zfill(void* smem, const void* gmem, bool valid) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  int bytes = valid ? 16 : 0;                                        // 0: nothing is read, the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(bytes));
+}
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(512, 1) dgemm128mb_kernel(int M, int N, int K, double alpha, const double* __restrict__ A,
+                                                            int64_t lda, const double* __restrict__ B, int64_t ldb, double beta,
+                                                            double* __restrict__ C, int64_t ldc, int lower_only, int ktri,
+                                                            int64_t sA, int64_t sB, int64_t sC) {
+  const int tm = blockIdx.y, tn = blockIdx.x;
+  if (lower_only && tn > tm) return;
+  A += (int64_t)blockIdx.z * sA;
+  B += (int64_t)blockIdx.z * sB;
+  C += (int64_t)blockIdx.z * sC;
+  extern __shared__ __align__(16) double gsm[];
+  double* As = gsm;                        // [GST3][G_TILE]
+  double* Bs = gsm + GST3 * G_TILE;        // [GST3][G_TILE]
+  uint64_t* full = reinterpret_cast<uint64_t*>(gsm + 2 * GST3 * G_TILE);
+  uint64_t* empty = full + GST3;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int wm = warp >> 2, wn = warp & 3;
+  const int fr = lane >> 2, fk = lane & 3;
+  const int m0 = tm * GM, n0 = tn * GN;
+  int kbeg = 0, kend = K;
+  if (ktri == 1) kbeg = n0;
+  if (ktri == 3) kbeg = m0;
+  if (ktri == 2) kend = min(K, m0 + GM);
+  const int nch = (kend - kbeg + GK - 1) / GK;
+  if (t == 0) {
+    for (int s = 0; s < GST3; s++) { g_mbar_init(full + s, 512); g_mbar_init(empty + s, 16); }
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+
+  auto load_tile = [&](const double* __restrict__ P, int64_t ld, bool trans, int r0, int R, double* dst, int k0) {
+    if (!trans) {
+      for (int p = t; p < GM * (GK / 2); p += 512) {
+        const int row = p / (GK / 2), seg = p % (GK / 2);
+        const bool ok = r0 + row < R && k0 + seg * 2 < kend;
+        g_cp_async16_zfill(dst + row * LDG + seg * 2, ok ? P + (int64_t)(r0 + row) * ld + k0 + seg * 2 : P, ok);
+      }
+    } else {
+      for (int p = t; p < GK * 64; p += 512) {
+        const int kk = p >> 6, seg = p & 63;
+        const bool ok = k0 + kk < kend && r0 + seg * 2 < R;
+        g_cp_async16_zfill(dst + kk * LDT + seg * 2, ok ? P + (int64_t)(k0 + kk) * ld + r0 + seg * 2 : P, ok);
+      }
+    }
+  };
+  auto issue = [&](int c) {                // c < nch
+    const int buf = c % GST3, k0 = kbeg + c * GK;
+    load_tile(A, lda, TA, m0, M, As + buf * G_TILE, k0);
+    load_tile(B, ldb, TB, n0, N, Bs + buf * G_TILE, k0);
+    g_cp_async_arrive(full + buf);
+  };
+
+  double acc[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+  if (nch > 0) issue(0);
+  for (int c = 0; c < nch; c++) {
+    if (c + 1 < nch) {
+      const int nb = (c + 1) % GST3, use = (c + 1) / GST3;             // the stage's use number `use`; chunk c - 2 was use - 1
+      if (use > 0) g_mbar_wait(empty + nb, (unsigned)((use - 1) & 1));
+      issue(c + 1);
+    }
+    g_mbar_wait(full + c % GST3, (unsigned)((c / GST3) & 1));
+    const double* a_s = As + (c % GST3) * G_TILE;
+    const double* b_s = Bs + (c % GST3) * G_TILE;
+#pragma unroll
+    for (int ks = 0; ks < GK; ks += 4) {
+      double a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+        a[i] = TA ? a_s[(ks + fk) * LDT + wm * 32 + i * 8 + fr] : a_s[(wm * 32 + i * 8 + fr) * LDG + ks + fk];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        b[j] = TB ? b_s[(ks + fk) * LDT + wn * 32 + j * 8 + fr] : b_s[(wn * 32 + j * 8 + fr) * LDG + ks + fk];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) cdx_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+    }
+    // the DMMAs above have consumed the stage's last fragments (the loads have completed): release it
+    __syncwarp();
+    if (lane == 0) g_mbar_arrive(empty + c % GST3);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int r = m0 + wm * 32 + i * 8 + fr;
+      const int c = n0 + wn * 32 + j * 8 + 2 * fk;
+      if (r < M && c < N) {
+        double2* p = reinterpret_cast<double2*>(C + (int64_t)r * ldc + c);
+        double2 v = make_double2(alpha * acc[i][j][0], alpha * acc[i][j][1]);
+        if (beta != 0.0) { const double2 o = *p; v.x += beta * o.x; v.y += beta * o.y; }
+        *p = v;
+      }
+    }
+}
+
 }  // namespace
 
 int cdx_dgemm(cdx_ctx* ctx, bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int64_t lda,
@@ -241,6 +374,21 @@ int cdx_dgemm(cdx_ctx* ctx, bool ta, bool tb, int M, int N, int K, double alpha,
   // large, aligned products go to the 128x128 cp.async kernel; thin / in-place panel operations keep the 64x64 one
   if (M >= 128 && N >= 128 && (M % 2) == 0 && (N % 2) == 0 && (K % 2) == 0 && (lda % 2) == 0 && (ldb % 2) == 0 && (ldc % 2) == 0 &&
       A != C && B != C) {
+    if (ctx->gemm_deep) {
+      const size_t smem3 = sizeof(double) * 2 * GST3 * G_TILE + 2 * GST3 * sizeof(uint64_t);
+      dim3 gridmb((N + GN - 1) / GN, (M + GM - 1) / GM, batch);
+      const int lomb = lower_only ? 1 : 0;
+#define CDX_G128MB(TA_, TB_)                                                                                                 \
+      do {                                                                                                                   \
+        if (int rc = cdx_smem_attr(ctx, dgemm128mb_kernel<TA_, TB_>, smem3)) return rc;                                       \
+        dgemm128mb_kernel<TA_, TB_><<<gridmb, 512, smem3, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lomb, ktri, sA, sB, sC); \
+      } while (0)
+      if (!ta && !tb) CDX_G128MB(false, false); else if (!ta && tb) CDX_G128MB(false, true);
+      else if (ta && !tb) CDX_G128MB(true, false); else CDX_G128MB(true, true);
+#undef CDX_G128MB
+      CDX_CHECK_LAUNCH(ctx);
+      return CDX_OK;
+    }
     const size_t smem = sizeof(double) * 2 * GST * G_TILE;
     dim3 grid128((N + GN - 1) / GN, (M + GM - 1) / GM, batch);
     int lo128 = lower_only ? 1 : 0;
