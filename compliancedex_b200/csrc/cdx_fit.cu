@@ -103,7 +103,7 @@ __device__ __forceinline__ void potrf_inv_level(double (*a)[65], double (*x)[65]
 //   * inverse: recursive doubling, inv([L11 0; L21 L22]) = [X11 0; -X22 L21 X11, X22], all 256 threads at every level (six
 //     levels, two barriers each, potrf_inv_level above) instead of 64 serial forward substitutions; the s x s temporaries
 //     T = L21 X11 live in the mirror-image block of `a`'s upper triangle, which is dead (zeroed before the write-back).
-// Shared memory stays at 2 x 64 x 65 doubles: one of these CTAs must fit on an SM next to a 160 KB dgemm128 CTA.
+// Shared memory: 2 x 64 x 65 doubles (+ the 1 KB column line).
 __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A, int64_t ld, double* __restrict__ Dinv,
                                                          double* __restrict__ Udiag, int* flag, int col0) {
   extern __shared__ double potrf_smem[];
@@ -288,7 +288,6 @@ static inline void fit_mark(cdx_gpis_state& g, int i, cudaStream_t st) {
 // factorise g.E11 (padded) -> L, U, P, alpha, Xa.  X1 is [N,3] device.
 int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   cdx_gpis_state& g = ctx->g;
-  ctx->gemm_deep = false;
   fit_mark(g, 1, st);
   const int Np = (int)g.Np, N = (int)g.N;
   const int64_t ld = Np;
@@ -369,7 +368,6 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
   zero_upper_kernel<<<g2, 256, 0, st>>>(g.L, Np);
   CDX_CHECK_LAUNCH(ctx);
   fit_mark(g, 2, st);
-  ctx->gemm_deep = true;      // inverse phases: no chain CTA to keep room for - the 3-stage mbarrier-pipelined GEMM (cdx_gemm.cu)
   // U = L^-1 by doubling: inv([L11 0; L21 L22]) = [U11 0; -U22 L21 U11, U22]; P is scratch for T = L21 U11
   for (int s = 64; s < Np; s *= 2) {
     int npairs = (Np + 2 * s - 1) / (2 * s);
@@ -402,7 +400,6 @@ int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
     pack_slab_kernel<<<g2, 256, 0, st>>>(g.P, Np, g.Pslab);
     CDX_CHECK_LAUNCH(ctx);
   }
-  ctx->gemm_deep = false;
   fit_mark(g, 4, st);
   // alpha = U^T (U y1)
   trmv_lower_kernel<<<(Np + 7) / 8, 256, 0, st>>>(g.U, Np, g.y1, g.tmp);

@@ -128,120 +128,25 @@ __global__ void __launch_bounds__(128) dgemm_kernel(int M, int N, int K, double 
     }
 }
 
-// ------------------------------------------------------------------------------------------ 128 x 128 tiles, cp.async ring
-// The large products of the fit (trailing updates of the Cholesky with K = 256, the recursive-doubling levels of L^-1,
-// E11^-1 = U^T U): 128x128x32 CTA tiles, 16 warps (4 x 4, each a 32x32 tile = 4x4 DMMA blocks), operands brought in with
-// 16-byte cp.async through a 2-stage shared-memory ring (147 KB: a potrf / panel CTA of the chain must fit beside it) - a DMMA holds its warp for several cycles, so it takes four warps per
-// scheduler and loads that never wait on the math to keep the pipe fed (the 64x64 single-buffered kernel above reached
-// 0.40-0.50 of the DMMA peak).  Operand tiles keep the layout they have in memory: k-contiguous sources as [row][20]
-// (conflict-free for the fragment pattern row = T/4, k = T%4), row-contiguous sources (ta / tb) as [k][132].
-constexpr int GM = 128, GN = 128, GK = 32, GST = 2, LDT = 132, LDG = GK + 4;
+// ------------------------------------------------------------------------------------------ 128 x 128 tiles, mbarrier pipeline
+// The large products of the fit (trailing updates of the Cholesky with K = 256 / 512, the recursive-doubling levels of L^-1,
+// E11^-1 = U^T U): 128x128x32 CTA tiles, 16 warps (4 x 4, each a 32x32 tile = 4x4 DMMA blocks) - a DMMA holds its warp for
+// several cycles, so it takes four warps per scheduler to keep the pipe fed.  Operand tiles keep the layout they have in
+// memory: k-contiguous sources as [row][36] (conflict-free for the fragment pattern row = T/4, k = T%4), row-contiguous
+// sources (ta / tb) as [k][132].  Three ring stages and NO CTA-wide barrier in the k loop: every thread's 16-byte cp.async
+// copies of a chunk arrive on the stage's `full` mbarrier (cp.async.mbarrier.arrive.noinc; rows outside the matrix are
+// zero-filled by cp.async with a source size of 0, so every write of a stage is tracked), a warp releases a stage on its
+// `empty` mbarrier when its DMMAs have consumed the last fragments, and a chunk is prefetched ONE iteration ahead into the
+// stage that chunk c - 2 used - so a warp may run a whole chunk ahead of the slowest one instead of meeting it at every chunk.
+// History (fit at N = 16,384): 64x64 single-buffered kernel 0.40-0.50 of the DMMA peak; 128x128x16, 4-stage cp.async ring with
+// a __syncthreads per chunk 0.76-0.77 in the inverse phases; 32-deep chunks (2 stages, half the barriers) 0.79-0.80, ncu: 8 % of
+// the stall samples on the barrier, DMMA sub-pipe 83 %; this version 0.87-0.90 (L^-1 49.8 -> 45.1 ms, E11^-1 49.2 -> 44.1 ms,
+// Cholesky 61.9 -> 58.0 ms).  221 KB of shared memory, 120 registers x 512 threads: nothing else fits on the SM beside it - the
+// chain kernels of the Cholesky get their SMs from the stream priority as tiles retire, which is what happened before as well
+// (61 k of the 64 k registers were taken already).
+constexpr int GM = 128, GN = 128, GK = 32, GST = 3, LDT = 132, LDG = GK + 4;
 constexpr int G_TILE = GM * LDG > GK * LDT ? GM * LDG : GK * LDT;   // doubles per operand tile and stage
 
-template <bool TA, bool TB>
-__global__ void __launch_bounds__(512, 1) dgemm128_kernel(int M, int N, int K, double alpha, const double* __restrict__ A,
-                                                          int64_t lda, const double* __restrict__ B, int64_t ldb, double beta,
-                                                          double* __restrict__ C, int64_t ldc, int lower_only, int ktri,
-                                                          int64_t sA, int64_t sB, int64_t sC) {
-  const int tm = blockIdx.y, tn = blockIdx.x;
-  if (lower_only && tn > tm) return;
-  A += (int64_t)blockIdx.z * sA;
-  B += (int64_t)blockIdx.z * sB;
-  C += (int64_t)blockIdx.z * sC;
-  extern __shared__ __align__(16) double gsm[];
-  double* As = gsm;                       // [GST][G_TILE]
-  double* Bs = gsm + GST * G_TILE;        // [GST][G_TILE]
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int wm = warp >> 2, wn = warp & 3;
-  const int fr = lane >> 2, fk = lane & 3;
-  const int m0 = tm * GM, n0 = tn * GN;
-  int kbeg = 0, kend = K;
-  if (ktri == 1) kbeg = n0;
-  if (ktri == 3) kbeg = m0;
-  if (ktri == 2) kend = min(K, m0 + GM);
-  const int nch = (kend - kbeg + GK - 1) / GK;
-
-  // one operand tile of chunk c into ring slot `buf`: 16-byte cp.async, rows outside the matrix are zero-filled
-  auto load_tile = [&](const double* __restrict__ P, int64_t ld, bool trans, int r0, int R, double* dst, int k0) {
-    if (!trans) {                         // P[rows, K]: 128 rows x 8 segments of 2 doubles
-      for (int p = t; p < GM * (GK / 2); p += 512) {
-        const int row = p / (GK / 2), seg = p % (GK / 2);
-        double* d = dst + row * LDG + seg * 2;
-        if (r0 + row < R && k0 + seg * 2 < kend) cdx_cp_async16(d, P + (int64_t)(r0 + row) * ld + k0 + seg * 2);
-        else { d[0] = 0.0; d[1] = 0.0; }
-      }
-    } else {                              // P[K, rows]: GK k x 64 segments of 2 doubles
-      for (int p = t; p < GK * 64; p += 512) {
-        const int kk = p >> 6, seg = p & 63;
-        double* d = dst + kk * LDT + seg * 2;
-        if (k0 + kk < kend && r0 + seg * 2 < R) cdx_cp_async16(d, P + (int64_t)(k0 + kk) * ld + r0 + seg * 2);
-        else { d[0] = 0.0; d[1] = 0.0; }
-      }
-    }
-  };
-  auto issue = [&](int c) {
-    if (c < nch) {
-      const int buf = c % GST, k0 = kbeg + c * GK;
-      load_tile(A, lda, TA, m0, M, As + buf * G_TILE, k0);
-      load_tile(B, ldb, TB, n0, N, Bs + buf * G_TILE, k0);
-    }
-    cdx_cp_async_commit();
-  };
-
-  double acc[4][4][2];
-#pragma unroll
-  for (int i = 0; i < 4; i++)
-#pragma unroll
-    for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
-
-#pragma unroll
-  for (int c = 0; c < GST - 1; c++) issue(c);
-  for (int c = 0; c < nch; c++) {
-    cdx_cp_async_wait<GST - 2>();         // chunk c has landed
-    __syncthreads();                      // ... for every thread; and every warp is done with chunk c - 1
-    issue(c + GST - 1);                   // into the slot chunk c - 1 has just left
-    const double* a_s = As + (c % GST) * G_TILE;
-    const double* b_s = Bs + (c % GST) * G_TILE;
-#pragma unroll
-    for (int ks = 0; ks < GK; ks += 4) {
-      double a[4], b[4];
-#pragma unroll
-      for (int i = 0; i < 4; i++)
-        a[i] = TA ? a_s[(ks + fk) * LDT + wm * 32 + i * 8 + fr] : a_s[(wm * 32 + i * 8 + fr) * LDG + ks + fk];
-#pragma unroll
-      for (int j = 0; j < 4; j++)
-        b[j] = TB ? b_s[(ks + fk) * LDT + wn * 32 + j * 8 + fr] : b_s[(wn * 32 + j * 8 + fr) * LDG + ks + fk];
-#pragma unroll
-      for (int i = 0; i < 4; i++)
-#pragma unroll
-        for (int j = 0; j < 4; j++) cdx_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 4; i++)
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const int r = m0 + wm * 32 + i * 8 + fr;
-      const int c = n0 + wn * 32 + j * 8 + 2 * fk;
-      if (r < M && c < N) {               // N is even for every caller (multiples of 64): the pair never straddles the edge
-        double2* p = reinterpret_cast<double2*>(C + (int64_t)r * ldc + c);
-        double2 v = make_double2(alpha * acc[i][j][0], alpha * acc[i][j][1]);
-        if (beta != 0.0) { const double2 o = *p; v.x += beta * o.x; v.y += beta * o.y; }
-        *p = v;
-      }
-    }
-}
-
-
-// ------------------------------------------------------------------------------------------ 128 x 128 tiles, mbarrier pipeline
-// The same tile and fragment layout as dgemm128_kernel, but three ring stages and NO CTA-wide barrier in the k loop: every
-// thread's cp.async copies of a chunk arrive on the stage's `full` mbarrier (cp.async.mbarrier.arrive.noinc; rows outside the
-// matrix are zero-filled by cp.async with a source size of 0, so every write of a stage is tracked), a warp releases a stage
-// on its `empty` mbarrier when its DMMAs have consumed the last fragments, and a chunk is prefetched ONE iteration ahead into the
-// stage that chunk c - 2 used - so a warp may run a whole chunk ahead of the slowest one instead of meeting it at every chunk
-// (ncu of dgemm128_kernel: 8 % of the stall samples on the barrier, DMMA sub-pipe 83 %).  221 KB of shared memory: used for
-// the inverse phases of the fit, where no chain CTA needs room beside a GEMM CTA.
-constexpr int GST3 = 3;
 
 __device__ __forceinline__ void g_mbar_init(uint64_t* bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
@@ -265,7 +170,7 @@ __device__ __forceinline__ void g_cp_async16_zfill(void* smem, const void* gmem,
 }
 
 template <bool TA, bool TB>
-__global__ void __launch_bounds__(512, 1) dgemm128mb_kernel(int M, int N, int K, double alpha, const double* __restrict__ A,
+__global__ void __launch_bounds__(512, 1) dgemm128_kernel(int M, int N, int K, double alpha, const double* __restrict__ A,
                                                             int64_t lda, const double* __restrict__ B, int64_t ldb, double beta,
                                                             double* __restrict__ C, int64_t ldc, int lower_only, int ktri,
                                                             int64_t sA, int64_t sB, int64_t sC) {
@@ -275,10 +180,10 @@ __global__ void __launch_bounds__(512, 1) dgemm128mb_kernel(int M, int N, int K,
   B += (int64_t)blockIdx.z * sB;
   C += (int64_t)blockIdx.z * sC;
   extern __shared__ __align__(16) double gsm[];
-  double* As = gsm;                        // [GST3][G_TILE]
-  double* Bs = gsm + GST3 * G_TILE;        // [GST3][G_TILE]
-  uint64_t* full = reinterpret_cast<uint64_t*>(gsm + 2 * GST3 * G_TILE);
-  uint64_t* empty = full + GST3;
+  double* As = gsm;                        // [GST][G_TILE]
+  double* Bs = gsm + GST * G_TILE;        // [GST][G_TILE]
+  uint64_t* full = reinterpret_cast<uint64_t*>(gsm + 2 * GST * G_TILE);
+  uint64_t* empty = full + GST;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int wm = warp >> 2, wn = warp & 3;
   const int fr = lane >> 2, fk = lane & 3;
@@ -289,7 +194,7 @@ __global__ void __launch_bounds__(512, 1) dgemm128mb_kernel(int M, int N, int K,
   if (ktri == 2) kend = min(K, m0 + GM);
   const int nch = (kend - kbeg + GK - 1) / GK;
   if (t == 0) {
-    for (int s = 0; s < GST3; s++) { g_mbar_init(full + s, 512); g_mbar_init(empty + s, 16); }
+    for (int s = 0; s < GST; s++) { g_mbar_init(full + s, 512); g_mbar_init(empty + s, 16); }
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   __syncthreads();
@@ -310,7 +215,7 @@ __global__ void __launch_bounds__(512, 1) dgemm128mb_kernel(int M, int N, int K,
     }
   };
   auto issue = [&](int c) {                // c < nch
-    const int buf = c % GST3, k0 = kbeg + c * GK;
+    const int buf = c % GST, k0 = kbeg + c * GK;
     load_tile(A, lda, TA, m0, M, As + buf * G_TILE, k0);
     load_tile(B, ldb, TB, n0, N, Bs + buf * G_TILE, k0);
     g_cp_async_arrive(full + buf);
@@ -325,13 +230,13 @@ __global__ void __launch_bounds__(512, 1) dgemm128mb_kernel(int M, int N, int K,
   if (nch > 0) issue(0);
   for (int c = 0; c < nch; c++) {
     if (c + 1 < nch) {
-      const int nb = (c + 1) % GST3, use = (c + 1) / GST3;             // the stage's use number `use`; chunk c - 2 was use - 1
+      const int nb = (c + 1) % GST, use = (c + 1) / GST;             // the stage's use number `use`; chunk c - 2 was use - 1
       if (use > 0) g_mbar_wait(empty + nb, (unsigned)((use - 1) & 1));
       issue(c + 1);
     }
-    g_mbar_wait(full + c % GST3, (unsigned)((c / GST3) & 1));
-    const double* a_s = As + (c % GST3) * G_TILE;
-    const double* b_s = Bs + (c % GST3) * G_TILE;
+    g_mbar_wait(full + c % GST, (unsigned)((c / GST) & 1));
+    const double* a_s = As + (c % GST) * G_TILE;
+    const double* b_s = Bs + (c % GST) * G_TILE;
 #pragma unroll
     for (int ks = 0; ks < GK; ks += 4) {
       double a[4], b[4];
@@ -348,7 +253,7 @@ __global__ void __launch_bounds__(512, 1) dgemm128mb_kernel(int M, int N, int K,
     }
     // the DMMAs above have consumed the stage's last fragments (the loads have completed): release it
     __syncwarp();
-    if (lane == 0) g_mbar_arrive(empty + c % GST3);
+    if (lane == 0) g_mbar_arrive(empty + c % GST);
   }
 #pragma unroll
   for (int i = 0; i < 4; i++)
@@ -371,30 +276,15 @@ int cdx_dgemm(cdx_ctx* ctx, bool ta, bool tb, int M, int N, int K, double alpha,
               const double* B, int64_t ldb, double beta, double* C, int64_t ldc, bool lower_only, int ktri, int batch,
               int64_t sA, int64_t sB, int64_t sC, cudaStream_t st) {
   if (M <= 0 || N <= 0 || batch <= 0) return CDX_OK;
-  // large, aligned products go to the 128x128 cp.async kernel; thin / in-place panel operations keep the 64x64 one
+  // large, aligned products go to the 128x128 mbarrier-pipelined kernel; thin / in-place panel operations keep the 64x64 one
   if (M >= 128 && N >= 128 && (M % 2) == 0 && (N % 2) == 0 && (K % 2) == 0 && (lda % 2) == 0 && (ldb % 2) == 0 && (ldc % 2) == 0 &&
       A != C && B != C) {
-    if (ctx->gemm_deep) {
-      const size_t smem3 = sizeof(double) * 2 * GST3 * G_TILE + 2 * GST3 * sizeof(uint64_t);
-      dim3 gridmb((N + GN - 1) / GN, (M + GM - 1) / GM, batch);
-      const int lomb = lower_only ? 1 : 0;
-#define CDX_G128MB(TA_, TB_)                                                                                                 \
-      do {                                                                                                                   \
-        if (int rc = cdx_smem_attr(ctx, dgemm128mb_kernel<TA_, TB_>, smem3)) return rc;                                       \
-        dgemm128mb_kernel<TA_, TB_><<<gridmb, 512, smem3, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lomb, ktri, sA, sB, sC); \
-      } while (0)
-      if (!ta && !tb) CDX_G128MB(false, false); else if (!ta && tb) CDX_G128MB(false, true);
-      else if (ta && !tb) CDX_G128MB(true, false); else CDX_G128MB(true, true);
-#undef CDX_G128MB
-      CDX_CHECK_LAUNCH(ctx);
-      return CDX_OK;
-    }
-    const size_t smem = sizeof(double) * 2 * GST * G_TILE;
+    const size_t smem = sizeof(double) * 2 * GST * G_TILE + 2 * GST * sizeof(uint64_t);
     dim3 grid128((N + GN - 1) / GN, (M + GM - 1) / GM, batch);
-    int lo128 = lower_only ? 1 : 0;
-#define CDX_G128(TA_, TB_)                                                                                                   \
-    do {                                                                                                                     \
-      if (int rc = cdx_smem_attr(ctx, dgemm128_kernel<TA_, TB_>, smem)) return rc;                                           \
+    const int lo128 = lower_only ? 1 : 0;
+#define CDX_G128(TA_, TB_)                                                                                                 \
+    do {                                                                                                                   \
+      if (int rc = cdx_smem_attr(ctx, dgemm128_kernel<TA_, TB_>, smem)) return rc;                                       \
       dgemm128_kernel<TA_, TB_><<<grid128, 512, smem, st>>>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lo128, ktri, sA, sB, sC); \
     } while (0)
     if (!ta && !tb) CDX_G128(false, false); else if (!ta && tb) CDX_G128(false, true);

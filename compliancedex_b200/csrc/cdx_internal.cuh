@@ -109,9 +109,6 @@ struct cdx_ctx {
   double* hx = nullptr; double* hout = nullptr; int64_t hcap = 0;
   // kernels whose dynamic shared-memory limit has been raised ON THIS DEVICE (the attribute is per device, one ctx per device)
   std::vector<const void*> smem_attr_done;
-  // cdx_dgemm: large products through the 3-stage mbarrier-pipelined kernel (221 KB of shared memory: only where no chain CTA
-  // has to fit beside a GEMM CTA, i.e. outside the Cholesky phase)
-  bool gemm_deep = false;
 };
 
 template <class F>
