@@ -281,3 +281,43 @@ def test_extended_query_tiny_and_boundary_states(N):
         for a, b in zip(outs[0], outs[1]):
             assert torch.isfinite(a).all()
             assert (a - b).abs().max() <= 1e-9 * max(1.0, float(b.abs().max())), (N, M)
+
+
+@pytest.mark.gpu
+def test_fit_is_bit_reproducible_across_runs_and_streams():
+    """The 128 x 128 GEMM of the fit synchronises its shared-memory ring with full / empty mbarriers (no CTA barrier in the k
+    loop) and the Cholesky runs its serial chain on a second stream: a race would show as run-to-run differences.  Five fits of
+    the same N = 2,304 set (one on a side stream) must give the same factor, inverse factor and inverse bit for bit, and the
+    factor must satisfy L L^T = E11."""
+    from compliancedex_b200 import GPIS, _lib
+    from compliancedex_b200.synthetic import synthetic_training_set
+    lib = _lib.load()
+    X1, y1, noise = synthetic_training_set(2304, seed=3)
+    X1, y1, noise = X1.cuda(), y1.cuda(), noise.cuda()
+    N = X1.shape[0]
+
+    def mats(g):
+        out = []
+        for which in (_lib.MAT_CHOL, _lib.MAT_CHOL_INV, _lib.MAT_E11_INV):
+            t = torch.empty(N, N, dtype=torch.float64, device="cuda")
+            _lib.check(lib.cdx_gpis_get(g._ctx, which, ctypes.c_void_p(t.data_ptr()), None))
+            out.append(t)
+        torch.cuda.synchronize()
+        return out
+
+    g = GPIS(0.08, 1.0)
+    g.fit(X1, y1, noise)
+    ref = mats(g)
+    E = g.E11
+    assert (ref[0] @ ref[0].T - E).abs().max() <= 1e-13 * E.abs().max()
+    side = torch.cuda.Stream()
+    for rep in range(4):
+        if rep == 2:
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                g.fit(X1, y1, noise)
+            torch.cuda.current_stream().wait_stream(side)
+        else:
+            g.fit(X1, y1, noise)
+        for a, b in zip(ref, mats(g)):
+            assert torch.equal(a, b)
