@@ -35,7 +35,7 @@ __global__ void pairmax_kernel(const double* __restrict__ X, int N, int jlen, un
 
 template <int KERNEL>
 __global__ void assemble_kernel(const double* __restrict__ X, const double* __restrict__ noise, double noise_scalar,
-                                int N, int Np, cdx_kparams kp, double* __restrict__ E) {
+                                int N, int Np, cdx_kparams kp, double* __restrict__ E, double* __restrict__ Lcopy) {
   int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
   if (j >= Np) return;
   double v;
@@ -52,6 +52,7 @@ __global__ void assemble_kernel(const double* __restrict__ X, const double* __re
     v = (i == j) ? 1.0 : 0.0;
   }
   E[(int64_t)i * Np + j] = v;
+  Lcopy[(int64_t)i * Np + j] = v;      // the factorisation works in place on this copy (saves a 2 x Np^2 x 8 B device copy)
 }
 
 __global__ void pad_copy_kernel(const double* __restrict__ src, int N, int Np, double* __restrict__ dst) {
@@ -286,13 +287,13 @@ static inline void fit_mark(cdx_gpis_state& g, int i, cudaStream_t st) {
 }
 
 // factorise g.E11 (padded) -> L, U, P, alpha, Xa.  X1 is [N,3] device.
-int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st) {
+int gpis_factorise(cdx_ctx* ctx, const double* X1, cudaStream_t st, bool l_holds_e11) {
   cdx_gpis_state& g = ctx->g;
   fit_mark(g, 1, st);
   const int Np = (int)g.Np, N = (int)g.N;
   const int64_t ld = Np;
   const size_t mat = sizeof(double) * (size_t)Np * (size_t)Np;
-  CDX_CUDA(cudaMemcpyAsync(g.L, g.E11, mat, cudaMemcpyDeviceToDevice, st));
+  if (!l_holds_e11) CDX_CUDA(cudaMemcpyAsync(g.L, g.E11, mat, cudaMemcpyDeviceToDevice, st));   // the assembly kernel writes both
   CDX_CUDA(cudaMemsetAsync(g.U, 0, mat, st));
   CDX_CUDA(cudaMemsetAsync(g.flag, 0, sizeof(int), st));
   const int nb = Np / 64;
@@ -508,11 +509,11 @@ extern "C" int cdx_gpis_fit(cdx_ctx* ctx, const double* X1, const double* y1, co
   CDX_CHECK_LAUNCH(ctx);
   cdx_kparams kp = cdx_make_kparams(g);
   dim3 g2((Np + 255) / 256, Np);
-  if (kernel == CDX_KERNEL_TPS) assemble_kernel<CDX_KERNEL_TPS><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11);
-  else if (kernel == CDX_KERNEL_RBF) assemble_kernel<CDX_KERNEL_RBF><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11);
-  else assemble_kernel<CDX_KERNEL_JOINT><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11);
+  if (kernel == CDX_KERNEL_TPS) assemble_kernel<CDX_KERNEL_TPS><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11, g.L);
+  else if (kernel == CDX_KERNEL_RBF) assemble_kernel<CDX_KERNEL_RBF><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11, g.L);
+  else assemble_kernel<CDX_KERNEL_JOINT><<<g2, 256, 0, st>>>(X1, noise, noise_scalar, (int)N, Np, kp, g.E11, g.L);
   CDX_CHECK_LAUNCH(ctx);
-  return gpis_factorise(ctx, X1, st);
+  return gpis_factorise(ctx, X1, st, true);
 }
 
 extern "C" int cdx_gpis_set_state(cdx_ctx* ctx, const double* X1, const double* y1, const double* E11, double R,
@@ -532,7 +533,7 @@ extern "C" int cdx_gpis_set_state(cdx_ctx* ctx, const double* X1, const double* 
   dim3 g2((Np + 255) / 256, Np);
   pad_copy_kernel<<<g2, 256, 0, st>>>(E11, (int)N, Np, g.E11);
   CDX_CHECK_LAUNCH(ctx);
-  return gpis_factorise(ctx, X1, st);
+  return gpis_factorise(ctx, X1, st, false);
 }
 
 extern "C" int cdx_gpis_info(cdx_ctx* ctx, int64_t* N, double* R, double* bias, double* prior, int* not_spd_col, void* stream) {
