@@ -97,7 +97,7 @@ __device__ __forceinline__ void potrf_inv_level(double (*a)[65], double (*x)[65]
 //   * factorisation in REGISTERS: thread (row r = t % 64, column group t / 64) holds the 16 entries a[r][16 cg .. 16 cg + 15];
 //     per column j the owners publish the raw column through a double-buffered 64-entry line of shared memory (ONE barrier per
 //     column), every thread forms 1 / sqrt(a[j][j]) itself (rsqrt + the diagonal by one Newton step: no sqrt / division chain,
-//     no wait for a broadcast) and updates its own entries right of j with broadcast reads; the j loop is unrolled, so all
+//     no wait for a broadcast) and updates its own entries right of j with broadcast reads; the 16 columns of a group are unrolled, so all
 //     register subscripts are compile-time.  Entries above the diagonal carry dead values and are zeroed at the write-back.
 //     (The shared-memory version - two barriers, an IEEE sqrt and a division per column, 16 predicated passes over the whole
 //     block per column - took ~50 us of the ~100 us sub-step.)
@@ -119,10 +119,15 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A,
 #pragma unroll
     for (int k = 0; k < 8; k++) { const double2 v = src[k]; ar[2 * k] = v.x; ar[2 * k + 1] = v.y; }
   }
+  // the 16 columns of a column group are unrolled (compile-time register subscripts), the four groups are a real loop: the
+  // body is fetched once and re-run from the instruction cache (fully unrolled, the kernel was 7.5 k instructions walked once,
+  // cold, per launch: ncu put half of its stall cycles on instruction fetch)
+#pragma unroll 1
+  for (int cgj = 0; cgj < 4; cgj++) {
 #pragma unroll
-  for (int j = 0; j < 64; j++) {
-    const int cgj = j >> 4, jj = j & 15;
-    double* cb = colbuf[j & 1];
+  for (int jj = 0; jj < 16; jj++) {
+    const int j = cgj * 16 + jj;
+    double* cb = colbuf[jj & 1];
     if (cg == cgj) cb[r] = ar[jj];
     __syncthreads();          // one barrier per column: the line written for column j + 1 is the one column j - 1 used, and every
                               // thread has left column j - 1 before any thread passes this barrier
@@ -145,6 +150,7 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* __restrict__ A,
         if (k > jj) ar[k] = fma(-lr, cb[cgj * 16 + k] * rinv, ar[k]);
       ar[jj] = (r == j) ? root : lr;
     }
+  }
   }
 #pragma unroll
   for (int k = 0; k < 16; k++) a[r][cg * 16 + k] = ar[k];
