@@ -1,6 +1,6 @@
 // GPIS fit: covariance assembly (gpis.py:33-40) and the in-house blocked FP64 factorisation that replaces the
 // reference's per-call LU (gpis.py:53) / explicit inverse (gpis.py:77):
-//   E11 = L L^T (right-looking, 64-wide panels, DMMA SYRK trailing updates)
+//   E11 = L L^T (right-looking: 256 / 512-column outer panels of 64-column sub-steps, one DMMA SYRK trailing update per panel)
 //   U = L^-1 (block-recursive doubling, DMMA GEMMs),  P = U^T U = E11^-1,  alpha = U^T (U y1).
 #include <stdarg.h>
 #include "cdx_internal.cuh"

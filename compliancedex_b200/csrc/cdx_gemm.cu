@@ -1,7 +1,9 @@
 // Generic FP64 GEMM on the DMMA tensor path (mma.sync m8n8k4 f64) used by the one-time fit:
 // Cholesky trailing updates (SYRK), panel solves, the block-recursive triangular inverse and E11^-1 = U^T U.
-// 64x64x16 CTA tile, 4 warps (2x2), each warp a 32x32 tile = 4x4 DMMA blocks; operands staged in shared memory
-// as [row][k] with a 20-double row stride (conflict-free for the DMMA fragment pattern row=T/4, k=T%4).
+// Two kernels: dgemm128_kernel (128x128x32 CTA tiles, 16 warps, 3-stage cp.async ring on full / empty mbarriers) for the large
+// products, dgemm_kernel (64x64x16 CTA tile, 4 warps (2x2), each warp a 32x32 tile = 4x4 DMMA blocks) for the thin / in-place
+// panel operations; operands staged in shared memory as [row][k] with a padded row stride (conflict-free for the DMMA fragment
+// pattern row=T/4, k=T%4).
 #include "cdx_internal.cuh"
 
 namespace {
